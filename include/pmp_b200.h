@@ -1,0 +1,161 @@
+/*
+ * pmp_b200.h -- C ABI of libpmp_b200.so: B200 (sm_100a) grid graph search behind the
+ * python_motion_planning planner API.
+ *
+ * The reference (Slenderman00/python_motion_planning) is pure Python and has no FFI; its seam
+ * is the planner class contract.  Each entry point below names the reference code it replaces
+ * (paths relative to /root/reference/src/python_motion_planning/).  The Python host layer
+ * (python_motion_planning_b200/) binds these with ctypes; INTEGRATION.md shows the stub a
+ * reference maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 on error; pmp_last_error() gives the text of the
+ *     last error raised on the calling thread.  No exceptions cross the ABI.
+ *   - "dev" pointers are CUDA device pointers owned by the caller (the Python layer carries
+ *     them in torch tensors); "host" pointers are ordinary host memory.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Calls are
+ *     asynchronous on that stream unless stated otherwise.
+ *   - coordinates are int32 triples (x, y, z); z = 0 for 2D grids.
+ *   - "no path" is data, not an error: cost = +inf, reached = 0.
+ *   - a handle is not thread-safe; use one handle per host thread / stream.
+ *
+ * Cell indexing.  The device grid is padded up to whole tiles: dims (X, Y, Z) -> (PX, PY, PZ),
+ * multiples of the tile (32 x 32 in 2D, 16 x 8 x 8 in 3D).  A "padded cell index" is
+ * (z * PY + y) * PX + x.  Cost fields (g) are dense arrays over padded cells, one per query.
+ * Cells outside the original box are permanently blocked (the reference's default walls seal
+ * the box: utils/environment/env.py:68-74, env3d.py:84-97).
+ */
+#ifndef PMP_B200_H
+#define PMP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PMP_B200_ABI_VERSION 1
+
+typedef struct pmp_grid pmp_grid; /* opaque: occupancy bitmask + motion table on one device */
+
+enum pmp_algo { PMP_ASTAR = 0, PMP_DIJKSTRA = 1, PMP_GBFS = 2 };
+enum pmp_heuristic { PMP_H_EUCLIDEAN = 0, PMP_H_MANHATTAN = 1 };
+enum pmp_weight { PMP_W_F64 = 0, PMP_W_U32 = 1 };
+
+/* per-query status written by pmp_sssp */
+enum pmp_status {
+    PMP_ST_RUNNING = 0,
+    PMP_ST_EXHAUSTED = 1, /* every reachable cell settled; goal (if any) not reached */
+    PMP_ST_REACHED = 2,   /* g[goal] is final */
+    PMP_ST_BAD_QUERY = 3  /* start or goal outside the box or on an obstacle */
+};
+
+const char *pmp_last_error(void);
+int pmp_abi_version(void);
+/* number of CUDA devices visible; <0 if the CUDA runtime cannot initialise */
+int pmp_device_count(void);
+
+/* ---- environment: replaces Grid / Grid3D occupancy (utils/environment/env.py:41-80,
+ *      env3d.py:43-103: a Python set of coordinate tuples + a cKDTree rebuilt per update) ---- */
+
+/* Creates an empty (all-free inside the box) grid on the current CUDA device.
+ * ndim 2 or 3; dims = {X, Y, Z} (Z ignored for ndim 2).  Installs the reference's default
+ * motion table (env.py:52-55: 8 moves, 1 / sqrt 2; env3d.py:56-70: 26 moves, 1 / sqrt 2 / sqrt 3). */
+int pmp_grid_create(int ndim, const int32_t *dims, pmp_grid **out);
+int pmp_grid_destroy(pmp_grid *g);
+/* out[0..2] = padded dims, out[3..5] = tile dims, out[6] = number of tiles, out[7] = words per
+ * bitmask row */
+int pmp_grid_layout(const pmp_grid *g, int64_t *out8);
+
+/* Grid.update(obstacles) (env.py:78-80 / env3d.py:101-103): replace the occupancy by the
+ * given obstacle set.  coords_dev: n x 3 int32 on the device; coordinates outside the box are
+ * ignored (the default Grid3D writes its side walls at z = -1, env3d.py:86-92). */
+int pmp_grid_set_cells(pmp_grid *g, const int32_t *coords_dev, int64_t n, void *stream);
+/* Same from a dense device array occ_dev[(z*Y + y)*X + x] != 0 (unpadded box). */
+int pmp_grid_set_dense(pmp_grid *g, const uint8_t *occ_dev, void *stream);
+/* Toggle single cells without rebuilding (obstacle edits between plans). value: 1 block, 0 free */
+int pmp_grid_edit_cells(pmp_grid *g, const int32_t *coords_dev, int64_t n, int value, void *stream);
+/* Copy the device bitmask to host: words_per_row * PY * PZ uint32 (bit x%32 of word x/32). Synchronous. */
+int pmp_grid_read_bits(const pmp_grid *g, uint32_t *bits_host, int64_t n_words);
+/* number of free cells inside the box (synchronous) */
+int pmp_grid_count_free(const pmp_grid *g, int64_t *n_free);
+
+/* env.motions (env.py:52-55, env3d.py:56-70; planners alias it at construction,
+ * global_planner/graph_search/graph_search.py:26): k <= 26 offsets in {-1,0,1}^3 (host, k x 3)
+ * with positive costs (host, k).  The 2D planners accumulate motion.g (node.py:41); the 3D
+ * planners use the Euclidean length of the offset (a_star3d.py:67) -- the host layer passes the
+ * right numbers.  Returns <0 for offsets outside {-1,0,1}. */
+int pmp_grid_set_motions(pmp_grid *g, int k, const int32_t *offsets_host, const double *cost_host);
+
+/* ---- search: replaces AStar/Dijkstra(.plan) expansion loops
+ *      (global_planner/graph_search/a_star.py:39-83, dijkstra.py:36-85, a_star3d.py:33-78,
+ *      dijkstra3d.py:39-87) incl. getNeighbor + isCollision (graph_search.py:61-87,
+ *      graph_search_3d.py:66-107) ---- */
+
+typedef struct pmp_sssp_params {
+    int32_t algo;       /* PMP_ASTAR: bucket/prune by g + h;  PMP_DIJKSTRA: by g */
+    int32_t heuristic;  /* pmp_heuristic; only admissible forms are used for ordering/pruning */
+    int32_t weight;     /* PMP_W_F64, or PMP_W_U32 (all motion costs must be integers) */
+    int32_t full_field; /* 1: ignore goals, settle every reachable cell (cost-to-go field) */
+    double window;      /* width of the global key window (delta); <= 0 picks a default */
+    int32_t max_rounds; /* safety bound on relaxation rounds; <= 0 = unlimited */
+    int32_t reserved;
+} pmp_sssp_params;
+
+/* bytes of one query's cost field and of the scratch workspace for nq concurrent queries */
+int pmp_sssp_sizes(const pmp_grid *g, int64_t nq, int weight, int64_t *g_bytes_per_query,
+                   int64_t *ws_bytes);
+
+/* Runs nq independent single-source searches that share the grid.
+ *   starts_dev, goals_dev : nq x 3 int32 (goals_dev may be NULL with full_field = 1)
+ *   g_dev      : nq cost fields (padded cells; f64 or u32).  Overwritten.  Unreached = +inf
+ *                (f64: all-ones bit pattern is used internally and converted by
+ *                pmp_field_finalize; u32: 0xFFFFFFFF).
+ *   ws_dev     : scratch of >= ws_bytes from pmp_sssp_sizes
+ *   gcost_dev  : nq doubles, g[goal] (+inf if not reached);  status_dev : nq pmp_status
+ *   stats_dev  : optional 8 x uint64: rounds, tile activations, cells expanded, edges relaxed,
+ *                worklist high-water, reserved...
+ * Fields are bit-exact to a sequential Dijkstra on the same directed graph: every value is the
+ * minimum over in-edges of fl(g(u) + w). */
+int pmp_sssp(pmp_grid *g, const pmp_sssp_params *params, int64_t nq,
+             const int32_t *starts_dev, const int32_t *goals_dev,
+             void *g_dev, void *ws_dev, int64_t ws_bytes,
+             double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream);
+
+/* f64 fields only: rewrite the internal "unreached" pattern to IEEE +inf so the field can be
+ * read as doubles.  n_cells = nq * padded cells. */
+int pmp_field_finalize(void *g_dev, int64_t n_cells, void *stream);
+
+/* counts cells with a finite value per query (N_settled of the GTEPS metric); if
+ * gcost_dev != NULL only cells with g + h <= gcost (A-star's closed region) are counted. */
+int pmp_count_settled(const pmp_grid *g, int weight, int64_t nq, const void *g_dev,
+                      const int32_t *goals_dev, const double *gcost_dev, int heuristic,
+                      uint64_t *counts_dev, void *stream);
+
+/* ---- path extraction: replaces extractPath (a_star.py:98-117, a_star3d.py:91-106) ----
+ * Descends the cost field from each goal: at v pick the in-neighbour u (legal edge u->v under
+ * the same directed rule) minimising g(u) + w(u->v), lowest motion index on ties.
+ *   path_dev     : nq x path_cap uint32 padded cell indices, goal first
+ *   path_len_dev : nq int32 (0 = no path, -1 = path_cap too small)
+ *   cost_dev     : nq doubles, sum of Euclidean step lengths accumulated goal->start, the
+ *                  reference's summation order (a_star.py:109-116) */
+int pmp_extract_paths(const pmp_grid *g, int weight, int64_t nq,
+                      const int32_t *starts_dev, const int32_t *goals_dev, const void *g_dev,
+                      uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
+                      double *cost_dev, void *stream);
+
+/* ---- greedy best-first: replaces GBFS.plan / GBFS3D.plan (gbfs.py:36-86, gbfs3d.py:34-82) ----
+ * One warp per query runs the reference's sequential loop (binary heap keyed by h, FIFO
+ * counter as in gbfs3d.py:46).  family: 2 = 2D record/tie rule, 3 = 3D.
+ *   parent_dev  : nq x padded cells uint32 scratch (closed set + parents); heap_dev: nq x heap_cap x 16 B
+ *   outputs as pmp_extract_paths, plus n_expand_dev (len(CLOSED)). */
+int pmp_gbfs(const pmp_grid *g, int heuristic, int64_t nq,
+             const int32_t *starts_dev, const int32_t *goals_dev,
+             uint32_t *parent_dev, void *heap_dev, int64_t heap_cap,
+             uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
+             double *cost_dev, int32_t *n_expand_dev, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

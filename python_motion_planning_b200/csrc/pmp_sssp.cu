@@ -1,0 +1,678 @@
+// pmp_sssp.cu -- tiled, windowed label-correcting shortest paths on the occupancy bitmask.
+//
+// Replaces the expansion loops of the reference planners (global_planner/graph_search/
+// a_star.py:39-83, dijkstra.py:36-85, a_star3d.py:33-78, dijkstra3d.py:39-87) together with
+// getNeighbor (a_star.py:85-96, a_star3d.py:80-89, dijkstra3d.py:89-126) and isCollision
+// (graph_search.py:61-87, graph_search_3d.py:66-107).
+//
+// Scheme (DESIGN.md has the long form):
+//   * the grid is cut into tiles (32x32 cells in 2D, 16x8x8 in 3D); a cost field g is a dense
+//     array per query; per (query, tile) there is a `minkey` (smallest key of a cell that still
+//     has to propagate) and a 1024-bit `dirty` mask of those cells;
+//   * one persistent cooperative kernel runs rounds: SCAN every (query, tile), collect those
+//     whose minkey lies inside the query's key window [min, min + delta) into a worklist;
+//     PROCESS each listed tile in one CTA: stage g (tile + 1-cell halo) and the occupancy rows in
+//     shared memory, settle cells in key order with sub-buckets of the smallest edge cost
+//     (ballot-compacted frontier, shared-memory atomic min), then publish: changed cells go
+//     back with an atomic min, improved halo cells additionally raise the neighbour tile's
+//     dirty bit and minkey.  Global g only ever decreases, every value is fl(g(u) + w) for a
+//     legal edge, and a cell stays dirty until it has propagated, so the fixed point is the
+//     same field a sequential Dijkstra produces -- bit for bit, also for the sqrt(2)/sqrt(3)
+//     weights.
+//   * A-star = the same with key g + h (h an admissible round-down heuristic), pruning by the best
+//     g[goal] seen, and termination once no pending key is below g[goal].
+#include <cooperative_groups.h>
+
+#include "pmp_common.cuh"
+
+namespace cg = cooperative_groups;
+
+#define NT 256
+
+template <int TX_, int TY_, int TZ_, typename W_>
+struct TileCfg {
+    typedef W_ W;
+    typedef typename W_::G G;
+    static constexpr int TX = TX_, TY = TY_, TZ = TZ_;
+    static constexpr int ZH = TZ_ > 1 ? 1 : 0; // halo width in z (0 for 2D)
+    static constexpr int HX = TX_ + 2, HY = TY_ + 2, HZ = TZ_ + 2 * ZH;
+    static constexpr int NCELL = TX_ * TY_ * TZ_;
+    static constexpr int NPW = NCELL / 32; // words of the pending mask
+    static constexpr int HC = HX * HY * HZ;
+    static constexpr int NCW = (HC + 31) / 32; // words of the changed mask
+    static constexpr int NROWS = HY * HZ;
+    static_assert(NCELL == 1024, "tiles hold 1024 cells (dirty mask = 32 words)");
+};
+
+template <class C>
+struct TileSmem {
+    typename C::G g[C::HC]; // cost of tile + halo
+    u64 rows[C::NROWS];     // occupancy bits of the TX+2 cells of each (y,z) row
+    u64 nbrmin[27];         // smallest key pushed into each neighbour tile
+    u64 kmin_rest[3];       // min key of pending cells outside the current sub-bucket
+    u64 T, U;
+    u32 count[3];
+    u32 pend[C::NPW];
+    u32 chg[C::NCW];
+    u32 item;
+    u32 n_exp, n_edge;
+    u32 s_live, s_wl_base;
+    uint16_t list[C::NCELL];
+};
+
+struct SsspArgs {
+    GridDev G;
+    Motions M;
+    u32 nq;
+    const int32_t *starts, *goals;
+    void *g;
+    u64 *minkey;
+    u32 *dirty;
+    u32 *wl[2];
+    u64 *qmin[2];
+    u64 *T[2];
+    int *done;
+    u32 *goalcell; // padded cell index of each goal (0xFFFFFFFF = none)
+    u32 *ctr;      // [0,1] worklist counts, [2,3] worklist heads, [4,5] live tiles
+    u64 *stats;    // rounds, tile activations, cells expanded, edges relaxed, wl high-water
+    double window, sub, he, hm;
+    int use_h, full_field, max_rounds;
+};
+
+__device__ static inline bool smem_min(u64 *p, u64 v) {
+    u64 old = *(volatile u64 *)p;
+    while (v < old) {
+        const u64 assumed = old;
+        old = atomicCAS(p, assumed, v);
+        if (old == assumed) return true;
+    }
+    return false;
+}
+__device__ static inline bool smem_min(u32 *p, u32 v) { return atomicMin(p, v) > v; }
+
+__device__ static inline u64 warp_min_u64(u64 v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        const u64 other = __shfl_xor_sync(0xFFFFFFFFu, v, o);
+        v = other < v ? other : v;
+    }
+    return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// one tile activation
+// ---------------------------------------------------------------------------------------------
+template <class C>
+__device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, TileSmem<C> &S) {
+    typedef typename C::W W;
+    typedef typename C::G G;
+    const GridDev &Gd = A.G;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const u32 q = gt / Gd.ntiles, t = gt - q * Gd.ntiles;
+    const int ttx = t % Gd.ntx, tty = (t / Gd.ntx) % Gd.nty, ttz = t / (Gd.ntx * Gd.nty);
+    const int ox = ttx * C::TX, oy = tty * C::TY, oz = ttz * C::TZ;
+    G *gq = (G *)A.g + (size_t)q * Gd.pcells;
+    u32 *dq = A.dirty + (size_t)gt * C::NPW;
+    const int use_h = A.use_h;
+    int gx = 0, gy = 0, gz = 0;
+    if (use_h) {
+        gx = A.goals[3 * q]; gy = A.goals[3 * q + 1]; gz = Gd.ndim == 3 ? A.goals[3 * q + 2] : 0;
+    }
+
+    if (tid == 0) {
+        atomicExch(&A.minkey[gt], KEY_INF); // claim: later pushes re-arm the tile
+        __threadfence();
+        S.T = ld_cg(&A.T[cur][q]);
+        u64 U = KEY_INF;
+        const u32 gc = A.full_field ? 0xFFFFFFFFu : A.goalcell[q];
+        if (gc != 0xFFFFFFFFu) {
+            const G gg = ld_cg(gq + gc);
+            if (gg != W::inf()) U = W::key(gg, 0.0);
+        }
+        S.U = U;
+        S.count[0] = S.count[1] = S.count[2] = 0;
+        S.kmin_rest[0] = S.kmin_rest[1] = S.kmin_rest[2] = KEY_INF;
+        S.n_exp = 0; S.n_edge = 0;
+    }
+    if (tid < 27) S.nbrmin[tid] = KEY_INF;
+    for (int i = tid; i < C::NCW; i += NT) S.chg[i] = 0;
+    __syncthreads();
+
+    if (tid < C::NPW) {
+        u32 v = ld_cg(dq + tid);
+        if (v) v = atomicExch(dq + tid, 0u);
+        S.pend[tid] = v;
+    }
+    for (int i = tid; i < C::HC; i += NT) {
+        const int hx = i % C::HX, hy = (i / C::HX) % C::HY, hz = i / (C::HX * C::HY);
+        const int x = ox + hx - 1, y = oy + hy - 1, z = oz + hz - C::ZH;
+        G v = W::inf();
+        if ((unsigned)x < (unsigned)Gd.PX && (unsigned)y < (unsigned)Gd.PY && (unsigned)z < (unsigned)Gd.PZ)
+            v = ld_cg(gq + ((size_t)z * Gd.PY + y) * Gd.PX + x);
+        S.g[i] = v;
+    }
+    for (int i = tid; i < C::NROWS; i += NT) {
+        const int hy = i % C::HY, hz = i / C::HY;
+        S.rows[i] = row_bits(Gd, ox - 1, oy + hy - 1, oz + hz - C::ZH, C::HX);
+    }
+    __syncthreads();
+
+    const u64 T = S.T, U = S.U;
+    u64 B = 0; // exclusive upper key of the current sub-bucket; first scan only finds the min
+    u64 km_final = KEY_INF;
+    for (int it = 0;; ++it) {
+        const int p = it % 3;
+        // ---- scan the pending mask: compact cells with key < B, track the min of the rest ----
+        u64 lmin = KEY_INF;
+        for (int w = warp; w < C::NPW; w += NT / 32) {
+            const u32 bits = S.pend[w];
+            if (!bits) continue;
+            const bool has = (bits >> lane) & 1u;
+            bool act = false;
+            const int c = w * 32 + lane;
+            if (has) {
+                const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
+                const int hi = ((lz + C::ZH) * C::HY + (ly + 1)) * C::HX + (lx + 1);
+                const G gv = S.g[hi];
+                const double h = use_h ? heuristic_lo(ox + lx - gx, oy + ly - gy, oz + lz - gz, A.he, A.hm) : 0.0;
+                const u64 k = W::key(gv, h);
+                if (k < B) act = true;
+                else lmin = k < lmin ? k : lmin;
+            }
+            const u32 m = __ballot_sync(0xFFFFFFFFu, act);
+            if (m) {
+                u32 base = 0;
+                if (lane == 0) {
+                    base = atomicAdd(&S.count[p], (u32)__popc(m));
+                    S.pend[w] = bits & ~m;
+                }
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                if (act) S.list[base + __popc(m & ((1u << lane) - 1u))] = (uint16_t)c;
+            }
+        }
+        lmin = warp_min_u64(lmin);
+        if (lane == 0 && lmin != KEY_INF) atomicMin(&S.kmin_rest[p], lmin);
+        __syncthreads();
+        const u32 n = S.count[p];
+        const u64 km = S.kmin_rest[p];
+        if (tid == 0) { // recycle the buffer last used two iterations ago
+            const int r = (it + 2) % 3;
+            S.count[r] = 0;
+            S.kmin_rest[r] = KEY_INF;
+            S.n_exp += n;
+        }
+        if (n == 0) {
+            if (km >= T) { km_final = km; break; }
+            u64 nb = W::key_add(km, A.sub);
+            B = nb < T ? nb : T;
+            continue;
+        }
+        // ---- relax the out-edges of the compacted frontier (push) ----
+        u32 my_edges = 0;
+        for (u32 i = tid; i < n; i += NT) {
+            const int c = S.list[i];
+            const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
+            const int hi = ((lz + C::ZH) * C::HY + (ly + 1)) * C::HX + (lx + 1);
+            const G gu = ((volatile G *)S.g)[hi];
+            u32 occ27 = 0;
+#pragma unroll
+            for (int dzz = -C::ZH; dzz <= C::ZH; ++dzz)
+#pragma unroll
+                for (int dyy = -1; dyy <= 1; ++dyy) {
+                    const u64 r = S.rows[(lz + C::ZH + dzz) * C::HY + (ly + 1 + dyy)];
+                    occ27 |= (u32)((r >> lx) & 7ull) << ((dzz + 1) * 9 + (dyy + 1) * 3);
+                }
+            const u32 F = ~occ27;
+            for (int m = 0; m < A.M.k; ++m) {
+                const u32 need = A.M.need[m];
+                if ((F & need) != need) continue;
+                ++my_edges;
+                const int dx = A.M.dx[m], dy = A.M.dy[m], dz = A.M.dz[m];
+                const int vhi = hi + (dz * C::HY + dy) * C::HX + dx;
+                const G cand = W::add(gu, A.M, m);
+                if (cand >= ((volatile G *)S.g)[vhi]) continue;
+                const int vx = lx + dx, vy = ly + dy, vz = lz + dz;
+                const double hv = use_h ? heuristic_lo(ox + vx - gx, oy + vy - gy, oz + vz - gz, A.he, A.hm) : 0.0;
+                if (W::key(cand, hv) > U) continue; // cannot be on a better path to the goal
+                if (!smem_min(&S.g[vhi], cand)) continue;
+                atomicOr(&S.chg[vhi >> 5], 1u << (vhi & 31));
+                if ((unsigned)vx < (unsigned)C::TX && (unsigned)vy < (unsigned)C::TY && (unsigned)vz < (unsigned)C::TZ) {
+                    const int cv = (vz * C::TY + vy) * C::TX + vx;
+                    atomicOr(&S.pend[cv >> 5], 1u << (cv & 31));
+                }
+            }
+        }
+        if (my_edges) atomicAdd(&S.n_edge, my_edges);
+        {
+            u64 nb = W::key_add(B, A.sub);
+            B = nb < T ? nb : T;
+        }
+        __syncthreads();
+    }
+
+    // ---- publish.  A: values (atomic min: a neighbour may have lowered a border cell meanwhile)
+    for (int w = tid; w < C::NCW; w += NT) {
+        u32 bits = S.chg[w];
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const int i = w * 32 + b;
+            const int hx = i % C::HX, hy = (i / C::HX) % C::HY, hz = i / (C::HX * C::HY);
+            const int x = ox + hx - 1, y = oy + hy - 1, z = oz + hz - C::ZH;
+            red_min(gq + ((size_t)z * Gd.PY + y) * Gd.PX + x, S.g[i]);
+        }
+    }
+    __threadfence();
+    __syncthreads();
+    // B: dirty bits of improved halo cells (in the neighbour tiles) and of our own leftovers
+    for (int w = tid; w < C::NCW; w += NT) {
+        u32 bits = S.chg[w];
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const int i = w * 32 + b;
+            const int hx = i % C::HX, hy = (i / C::HX) % C::HY, hz = i / (C::HX * C::HY);
+            const int sx = hx == 0 ? -1 : (hx == C::HX - 1 ? 1 : 0);
+            const int sy = hy == 0 ? -1 : (hy == C::HY - 1 ? 1 : 0);
+            const int sz = C::ZH ? (hz == 0 ? -1 : (hz == C::HZ - 1 ? 1 : 0)) : 0;
+            if ((sx | sy | sz) == 0) continue; // interior cell
+            const int nlx = hx - 1 - sx * C::TX, nly = hy - 1 - sy * C::TY, nlz = hz - C::ZH - sz * C::TZ;
+            const int cv = (nlz * C::TY + nly) * C::TX + nlx;
+            const u32 ngt = q * Gd.ntiles + (u32)(((ttz + sz) * Gd.nty + (tty + sy)) * Gd.ntx + (ttx + sx));
+            atomicOr(A.dirty + (size_t)ngt * C::NPW + (cv >> 5), 1u << (cv & 31));
+            const double hv = use_h ? heuristic_lo(ox + hx - 1 - gx, oy + hy - 1 - gy, oz + hz - C::ZH - gz, A.he, A.hm) : 0.0;
+            atomicMin(&S.nbrmin[(sz + 1) * 9 + (sy + 1) * 3 + (sx + 1)], W::key(S.g[i], hv));
+        }
+    }
+    if (tid < C::NPW && S.pend[tid]) atomicOr(dq + tid, S.pend[tid]);
+    __threadfence();
+    __syncthreads();
+    // C: arm the tiles that received work
+    if (tid < 27) {
+        const u64 k = S.nbrmin[tid];
+        if (k != KEY_INF) {
+            const int sx = tid % 3 - 1, sy = (tid / 3) % 3 - 1, sz = tid / 9 - 1;
+            const u32 ngt = q * Gd.ntiles + (u32)(((ttz + sz) * Gd.nty + (tty + sy)) * Gd.ntx + (ttx + sx));
+            atomicMin(&A.minkey[ngt], k);
+        }
+    }
+    if (tid == 32) {
+        if (km_final != KEY_INF) atomicMin(&A.minkey[gt], km_final);
+        atomicAdd(&A.stats[1], 1ull);
+        atomicAdd(&A.stats[2], (u64)S.n_exp);
+        atomicAdd(&A.stats[3], (u64)S.n_edge);
+    }
+    __syncthreads();
+}
+
+// ---------------------------------------------------------------------------------------------
+// persistent round loop
+// ---------------------------------------------------------------------------------------------
+template <class C>
+__global__ void __launch_bounds__(NT) k_sssp(const __grid_constant__ SsspArgs A) {
+    typedef typename C::W W;
+    typedef typename C::G G;
+    cg::grid_group grid = cg::this_grid();
+    __shared__ TileSmem<C> S;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const u32 ntiles = A.G.ntiles;
+    const u32 total = A.nq * ntiles;
+    const u32 gstride = gridDim.x * NT;
+
+    for (int r = 0;; ++r) {
+        const int cur = r & 1, nxt = cur ^ 1;
+        // ---- SCAN: which (query, tile) pairs fall inside their query's key window ----
+        if (tid == 0) S.s_live = 0;
+        __syncthreads();
+        u32 my_live = 0;
+        for (u32 base = blockIdx.x * NT; base < total; base += gstride) {
+            const u32 gt = base + tid;
+            bool live = false, take = false;
+            if (gt < total) {
+                const u64 k = ld_cg(&A.minkey[gt]);
+                if (k != KEY_INF) {
+                    const u32 q = gt / ntiles;
+                    if (ld_cg(&A.done[q]) == 0) {
+                        live = true;
+                        if (k < ld_cg(&A.qmin[cur][q])) atomicMin(&A.qmin[cur][q], k);
+                        take = k < ld_cg(&A.T[cur][q]);
+                    }
+                }
+            }
+            my_live += live;
+            const u32 m = __ballot_sync(0xFFFFFFFFu, take);
+            if (m) {
+                u32 pos = 0;
+                if (lane == 0) pos = atomicAdd(&A.ctr[cur], (u32)__popc(m));
+                pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
+                if (take) A.wl[cur][pos + __popc(m & ((1u << lane) - 1u))] = gt;
+            }
+        }
+        if (my_live) atomicAdd(&S.s_live, my_live);
+        __syncthreads();
+        if (tid == 0 && S.s_live) atomicAdd(&A.ctr[4 + cur], S.s_live);
+        grid.sync();
+
+        const u32 live = ld_cg(&A.ctr[4 + cur]);
+        const u32 nwl = ld_cg(&A.ctr[cur]);
+        if (live == 0) break;
+        if (A.max_rounds > 0 && r >= A.max_rounds) break;
+
+        // ---- per-query bookkeeping: termination, next window ----
+        for (u32 q = blockIdx.x * NT + tid; q < A.nq; q += gstride) {
+            const u64 k = ld_cg(&A.qmin[cur][q]);
+            if (ld_cg(&A.done[q]) == 0) {
+                int st = 0;
+                if (k == KEY_INF) {
+                    st = PMP_ST_EXHAUSTED;
+                } else if (!A.full_field) {
+                    const u32 gc = A.goalcell[q];
+                    if (gc != 0xFFFFFFFFu) {
+                        const G gg = ld_cg((const G *)A.g + (size_t)q * A.G.pcells + gc);
+                        // every pending key is >= k, keys never decrease along an edge: g[goal] is final
+                        if (gg != W::inf() && W::key(gg, 0.0) <= k) st = PMP_ST_REACHED;
+                    }
+                }
+                if (st) A.done[q] = st;
+            }
+            A.T[nxt][q] = (k == KEY_INF) ? KEY_INF : W::key_add(k, A.window);
+            A.qmin[nxt][q] = KEY_INF;
+        }
+        if (blockIdx.x == 0 && tid == 0) {
+            A.ctr[nxt] = 0; A.ctr[2 + nxt] = 0; A.ctr[4 + nxt] = 0;
+            A.stats[0] = (u64)(r + 1);
+            if ((u64)nwl > A.stats[4]) A.stats[4] = nwl;
+        }
+
+        // ---- PROCESS the worklist ----
+        for (;;) {
+            if (tid == 0) S.item = atomicAdd(&A.ctr[2 + cur], 1u);
+            __syncthreads();
+            const u32 it = S.item;
+            __syncthreads();
+            if (it >= nwl) break;
+            process_tile<C>(A, ld_cg(&A.wl[cur][it]), cur, S);
+        }
+        grid.sync();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// init / finalize / statistics kernels
+// ---------------------------------------------------------------------------------------------
+template <class C>
+__global__ void k_sssp_init(SsspArgs A) {
+    typedef typename C::W W;
+    typedef typename C::G G;
+    const GridDev &Gd = A.G;
+    for (u32 q = blockIdx.x * blockDim.x + threadIdx.x; q < A.nq; q += gridDim.x * blockDim.x) {
+        const int sx = A.starts[3 * q], sy = A.starts[3 * q + 1], sz = Gd.ndim == 3 ? A.starts[3 * q + 2] : 0;
+        bool ok = sx >= 0 && sy >= 0 && sz >= 0 && sx < Gd.X && sy < Gd.Y && sz < Gd.Z && !cell_blocked(Gd, sx, sy, sz);
+        u32 gc = 0xFFFFFFFFu;
+        int gx = 0, gy = 0, gz = 0;
+        if (A.goals && !A.full_field) {
+            gx = A.goals[3 * q]; gy = A.goals[3 * q + 1]; gz = Gd.ndim == 3 ? A.goals[3 * q + 2] : 0;
+            if (gx >= 0 && gy >= 0 && gz >= 0 && gx < Gd.X && gy < Gd.Y && gz < Gd.Z)
+                gc = (u32)(((size_t)gz * Gd.PY + gy) * Gd.PX + gx);
+            else
+                ok = false;
+        }
+        A.goalcell[q] = gc;
+        A.qmin[0][q] = KEY_INF; A.qmin[1][q] = KEY_INF;
+        A.T[0][q] = KEY_INF; A.T[1][q] = KEY_INF;
+        if (!ok) { A.done[q] = PMP_ST_BAD_QUERY; continue; }
+        A.done[q] = 0;
+        G *gq = (G *)A.g + (size_t)q * Gd.pcells;
+        gq[((size_t)sz * Gd.PY + sy) * Gd.PX + sx] = 0;
+        const int tx = sx / C::TX, ty = sy / C::TY, tz = sz / C::TZ;
+        const int lx = sx - tx * C::TX, ly = sy - ty * C::TY, lz = sz - tz * C::TZ;
+        const u32 t = (u32)((tz * Gd.nty + ty) * Gd.ntx + tx);
+        const u32 gt = q * Gd.ntiles + t;
+        const int c = (lz * C::TY + ly) * C::TX + lx;
+        A.dirty[(size_t)gt * C::NPW + (c >> 5)] = 1u << (c & 31);
+        const double h = A.use_h ? heuristic_lo(sx - gx, sy - gy, sz - gz, A.he, A.hm) : 0.0;
+        const u64 k0 = W::key((G)0, h);
+        A.minkey[gt] = k0;
+        A.T[0][q] = W::key_add(k0, A.window);
+    }
+}
+
+template <class W>
+__global__ void k_sssp_finish(SsspArgs A, double *gcost, int32_t *status) {
+    typedef typename W::G G;
+    for (u32 q = blockIdx.x * blockDim.x + threadIdx.x; q < A.nq; q += gridDim.x * blockDim.x) {
+        int st = A.done[q];
+        double c = __longlong_as_double(0x7ff0000000000000LL);
+        const u32 gc = A.goalcell[q];
+        if (st != PMP_ST_BAD_QUERY && gc != 0xFFFFFFFFu) {
+            const G gg = ((const G *)A.g)[(size_t)q * A.G.pcells + gc];
+            if (gg != W::inf()) {
+                c = W::to_double(gg);
+                if (st == PMP_ST_EXHAUSTED) st = PMP_ST_REACHED;
+            } else if (st == PMP_ST_REACHED) {
+                st = PMP_ST_EXHAUSTED;
+            }
+        }
+        if (gcost) gcost[q] = c;
+        if (status) status[q] = st;
+    }
+}
+
+__global__ void k_field_finalize(u64 *g, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        if (g[i] == ~0ull) g[i] = 0x7ff0000000000000ull;
+}
+
+template <class W>
+__global__ void k_count_settled(GridDev Gd, u32 nq, const typename W::G *g, const int32_t *goals,
+                                const double *gcost, double he, double hm, u64 *counts) {
+    typedef typename W::G G;
+    const u32 q = blockIdx.y;
+    if (q >= nq) return;
+    const G *gq = g + (size_t)q * Gd.pcells;
+    double bound = 0.0;
+    int gx = 0, gy = 0, gz = 0;
+    const bool use_bound = gcost != nullptr && goals != nullptr;
+    if (use_bound) {
+        bound = gcost[q];
+        gx = goals[3 * q]; gy = goals[3 * q + 1]; gz = Gd.ndim == 3 ? goals[3 * q + 2] : 0;
+    }
+    u64 local = 0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < Gd.pcells; i += (size_t)gridDim.x * blockDim.x) {
+        const G v = gq[i];
+        if (v == W::inf()) continue;
+        if (use_bound) {
+            const int x = (int)(i % Gd.PX), y = (int)((i / Gd.PX) % Gd.PY), z = (int)(i / ((size_t)Gd.PX * Gd.PY));
+            const double f = W::to_double(v) + heuristic_lo(x - gx, y - gy, z - gz, he, hm);
+            if (f > bound) continue;
+        }
+        ++local;
+    }
+    for (int o = 16; o; o >>= 1) local += __shfl_down_sync(0xFFFFFFFFu, local, o);
+    if ((threadIdx.x & 31) == 0 && local) atomicAdd(&counts[q], local);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+typedef TileCfg<32, 32, 1, WF64> C2F;
+typedef TileCfg<32, 32, 1, WU32> C2U;
+typedef TileCfg<16, 8, 8, WF64> C3F;
+typedef TileCfg<16, 8, 8, WU32> C3U;
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct WsLayout {
+    size_t minkey, dirty, wl0, wl1, qmin0, qmin1, T0, T1, done, goalcell, ctr, stats, total;
+};
+
+static WsLayout ws_layout(const pmp_grid *g, int64_t nq) {
+    WsLayout L;
+    const size_t nt = (size_t)nq * g->d.ntiles;
+    size_t o = 0;
+    L.minkey = o; o = align_up(o + nt * 8, 256);
+    L.dirty = o; o = align_up(o + nt * 32 * 4, 256);
+    L.wl0 = o; o = align_up(o + nt * 4, 256);
+    L.wl1 = o; o = align_up(o + nt * 4, 256);
+    L.qmin0 = o; o = align_up(o + (size_t)nq * 8, 256);
+    L.qmin1 = o; o = align_up(o + (size_t)nq * 8, 256);
+    L.T0 = o; o = align_up(o + (size_t)nq * 8, 256);
+    L.T1 = o; o = align_up(o + (size_t)nq * 8, 256);
+    L.done = o; o = align_up(o + (size_t)nq * 4, 256);
+    L.goalcell = o; o = align_up(o + (size_t)nq * 4, 256);
+    L.ctr = o; o = align_up(o + 16 * 4, 256);
+    L.stats = o; o = align_up(o + 8 * 8, 256);
+    L.total = o;
+    return L;
+}
+
+extern "C" int pmp_sssp_sizes(const pmp_grid *g, int64_t nq, int weight, int64_t *g_bytes_per_query,
+                              int64_t *ws_bytes) {
+    if (!g || nq < 1 || (weight != PMP_W_F64 && weight != PMP_W_U32)) {
+        pmp_set_error("pmp_sssp_sizes: bad arguments");
+        return -1;
+    }
+    if ((u64)nq * g->d.ntiles >= 0xFFFFFFFFull) {
+        pmp_set_error("nq * tiles = %llu exceeds 2^32-2; split the batch", (unsigned long long)((u64)nq * g->d.ntiles));
+        return -1;
+    }
+    if (g_bytes_per_query) *g_bytes_per_query = (int64_t)(g->d.pcells * (weight == PMP_W_F64 ? 8 : 4));
+    if (ws_bytes) *ws_bytes = (int64_t)ws_layout(g, nq).total;
+    return 0;
+}
+
+template <class C>
+static int launch_sssp(pmp_grid *g, SsspArgs &A, double *gcost_dev, int32_t *status_dev, cudaStream_t s) {
+    typedef typename C::W W;
+    static int blocks_per_sm = 0, n_sm = 0;
+    if (!blocks_per_sm) {
+        PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_sssp<C>, NT, 0));
+        int dev = 0;
+        PMP_CHECK_CUDA(cudaGetDevice(&dev));
+        PMP_CHECK_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+        if (blocks_per_sm < 1) { pmp_set_error("k_sssp does not fit on an SM"); return -2; }
+    }
+    const unsigned ib = (unsigned)((A.nq + 255) / 256);
+    k_sssp_init<C><<<ib > 1024 ? 1024 : ib, 256, 0, s>>>(A);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    // persistent grid: every CTA resident (cooperative launch), a multiple of the SM count
+    dim3 grid((unsigned)(blocks_per_sm * n_sm)), block(NT);
+    void *args[] = {(void *)&A};
+    PMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void *)k_sssp<C>, grid, block, args, 0, s));
+    k_sssp_finish<W><<<ib > 1024 ? 1024 : ib, 256, 0, s>>>(A, gcost_dev, status_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
+                        const int32_t *starts_dev, const int32_t *goals_dev,
+                        void *g_dev, void *ws_dev, int64_t ws_bytes,
+                        double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream) {
+    if (!g || !P || nq < 1 || !starts_dev || !g_dev || !ws_dev) {
+        pmp_set_error("pmp_sssp: bad arguments");
+        return -1;
+    }
+    if (!goals_dev && !P->full_field) {
+        pmp_set_error("pmp_sssp: goals_dev is NULL but full_field is 0");
+        return -1;
+    }
+    if (P->weight != PMP_W_F64 && P->weight != PMP_W_U32) { pmp_set_error("pmp_sssp: bad weight type"); return -1; }
+    if (P->weight == PMP_W_U32 && !g->integer_costs) {
+        pmp_set_error("pmp_sssp: PMP_W_U32 needs integer motion costs");
+        return -1;
+    }
+    if (P->algo != PMP_ASTAR && P->algo != PMP_DIJKSTRA) {
+        pmp_set_error("pmp_sssp: algo must be PMP_ASTAR or PMP_DIJKSTRA (GBFS: pmp_gbfs)");
+        return -1;
+    }
+    if ((u64)nq * g->d.ntiles >= 0xFFFFFFFFull) { pmp_set_error("pmp_sssp: nq * tiles too large"); return -1; }
+    const WsLayout L = ws_layout(g, nq);
+    if ((size_t)ws_bytes < L.total) {
+        pmp_set_error("pmp_sssp: workspace %lld B < required %zu B", (long long)ws_bytes, L.total);
+        return -1;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    char *ws = (char *)ws_dev;
+    SsspArgs A;
+    memset(&A, 0, sizeof A);
+    A.G = g->d;
+    A.M = g->mot;
+    A.nq = (u32)nq;
+    A.starts = starts_dev;
+    A.goals = goals_dev;
+    A.g = g_dev;
+    A.minkey = (u64 *)(ws + L.minkey);
+    A.dirty = (u32 *)(ws + L.dirty);
+    A.wl[0] = (u32 *)(ws + L.wl0); A.wl[1] = (u32 *)(ws + L.wl1);
+    A.qmin[0] = (u64 *)(ws + L.qmin0); A.qmin[1] = (u64 *)(ws + L.qmin1);
+    A.T[0] = (u64 *)(ws + L.T0); A.T[1] = (u64 *)(ws + L.T1);
+    A.done = (int *)(ws + L.done);
+    A.goalcell = (u32 *)(ws + L.goalcell);
+    A.ctr = (u32 *)(ws + L.ctr);
+    A.stats = (u64 *)(ws + L.stats);
+    A.full_field = P->full_field ? 1 : 0;
+    A.max_rounds = P->max_rounds;
+    A.sub = g->wmin;
+    // The heuristic only orders and prunes; it must be admissible for the motion table, so the
+    // requested type is scaled by the largest admissible factor (manhattan on 8/26-connected
+    // grids over-estimates in the reference, graph_search.py:41-42 -- see DESIGN.md).
+    A.use_h = (P->algo == PMP_ASTAR && !A.full_field) ? 1 : 0;
+    A.he = g->he_scale;
+    A.hm = g->hm_scale;
+    if (P->weight == PMP_W_U32) { // integer keys: floor the factors so h stays an integer lower bound
+        A.he = 0.0;
+        A.hm = floor(g->hm_scale);
+        A.sub = floor(g->wmin) < 1.0 ? 1.0 : floor(g->wmin);
+    }
+    double window = P->window;
+    if (!(window > 0.0)) window = (g->d.ndim == 2 ? 24.0 : 10.0) * g->wmin;
+    if (P->weight == PMP_W_U32 && window < 1.0) window = 1.0;
+    A.window = window;
+
+    const size_t gsz = (size_t)nq * g->d.pcells * (P->weight == PMP_W_F64 ? 8 : 4);
+    PMP_CHECK_CUDA(cudaMemsetAsync(g_dev, 0xFF, gsz, s));
+    const size_t nt = (size_t)nq * g->d.ntiles;
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, nt * 8, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.dirty, 0, nt * 32 * 4, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 8 * 8, s));
+
+    int rc;
+    if (g->d.ndim == 2) rc = P->weight == PMP_W_F64 ? launch_sssp<C2F>(g, A, gcost_dev, status_dev, s)
+                                                    : launch_sssp<C2U>(g, A, gcost_dev, status_dev, s);
+    else rc = P->weight == PMP_W_F64 ? launch_sssp<C3F>(g, A, gcost_dev, status_dev, s)
+                                     : launch_sssp<C3U>(g, A, gcost_dev, status_dev, s);
+    if (rc) return rc;
+    if (stats_dev)
+        PMP_CHECK_CUDA(cudaMemcpyAsync(stats_dev, A.stats, 8 * 8, cudaMemcpyDeviceToDevice, s));
+    return 0;
+}
+
+extern "C" int pmp_field_finalize(void *g_dev, int64_t n_cells, void *stream) {
+    if (!g_dev || n_cells < 0) { pmp_set_error("pmp_field_finalize: bad arguments"); return -1; }
+    if (n_cells == 0) return 0;
+    size_t b = ((size_t)n_cells + 255) / 256;
+    if (b > 148 * 32) b = 148 * 32;
+    k_field_finalize<<<(unsigned)b, 256, 0, (cudaStream_t)stream>>>((u64 *)g_dev, (size_t)n_cells);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pmp_count_settled(const pmp_grid *g, int weight, int64_t nq, const void *g_dev,
+                                 const int32_t *goals_dev, const double *gcost_dev, int heuristic,
+                                 uint64_t *counts_dev, void *stream) {
+    (void)heuristic;
+    if (!g || !g_dev || !counts_dev || nq < 1 || nq > 65535) { pmp_set_error("pmp_count_settled: bad arguments (nq <= 65535)"); return -1; }
+    cudaStream_t s = (cudaStream_t)stream;
+    PMP_CHECK_CUDA(cudaMemsetAsync(counts_dev, 0, (size_t)nq * 8, s));
+    size_t bx = (g->d.pcells + 255) / 256;
+    const size_t cap = nq >= 148 ? 8 : (148 * 8) / (size_t)nq;
+    if (bx > cap) bx = cap;
+    dim3 grid((unsigned)bx, (unsigned)nq);
+    if (weight == PMP_W_F64)
+        k_count_settled<WF64><<<grid, 256, 0, s>>>(g->d, (u32)nq, (const u64 *)g_dev, goals_dev, gcost_dev, g->he_scale, g->hm_scale, (u64 *)counts_dev);
+    else
+        k_count_settled<WU32><<<grid, 256, 0, s>>>(g->d, (u32)nq, (const u32 *)g_dev, goals_dev, gcost_dev, 0.0, floor(g->hm_scale), (u64 *)counts_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
