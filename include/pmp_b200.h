@@ -127,7 +127,8 @@ int pmp_sssp(pmp_grid *g, const pmp_sssp_params *params, int64_t nq,
 int pmp_field_finalize(void *g_dev, int64_t n_cells, void *stream);
 
 /* counts cells with a finite value per query (N_settled of the GTEPS metric); if
- * gcost_dev != NULL only cells with g + h <= gcost (A-star's closed region) are counted. */
+ * gcost_dev != NULL only cells with g + h <= gcost (A-star's closed region) are counted;
+ * heuristic < 0 means h = 0 (Dijkstra: cells with g <= gcost). */
 int pmp_count_settled(const pmp_grid *g, int weight, int64_t nq, const void *g_dev,
                       const int32_t *goals_dev, const double *gcost_dev, int heuristic,
                       uint64_t *counts_dev, void *stream);
@@ -154,6 +155,27 @@ int pmp_gbfs(const pmp_grid *g, int heuristic, int64_t nq,
              uint32_t *parent_dev, void *heap_dev, int64_t heap_cap,
              uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
              double *cost_dev, int32_t *n_expand_dev, void *stream);
+
+/* ---- slab mode: one z-slab (plus one ghost plane per interior side) of a large 3D grid per
+ *      GPU; the cost-to-go field of BASELINE.json config 5.  The handle describes the LOCAL slab.
+ *      Host loop (python_motion_planning_b200/slab.py): begin; repeat { run(bound); exchange
+ *      boundary planes with the z+-1 ranks (NCCL send/recv); merge; all-reduce(min) of the
+ *      pending keys -> next bound } until no key is pending anywhere. ---- */
+
+/* Resets field + scratch; start_dev = local coordinates of the source if it lies in this slab,
+ * else NULL. */
+int pmp_slab_begin(pmp_grid *g, const pmp_sssp_params *params, const int32_t *start_dev,
+                   void *g_dev, void *ws_dev, int64_t ws_bytes, void *stream);
+/* Processes every pending key < key_bound to local convergence (+inf: everything).
+ * out_dev: 8 x uint64; [0] = smallest key still pending here (f64: bit pattern; all-ones = none),
+ * [1] rounds, [2] tile activations, [3] cells expanded; [4] is used by pmp_slab_merge. */
+int pmp_slab_run(pmp_grid *g, const pmp_sssp_params *params, void *g_dev, void *ws_dev,
+                 int64_t ws_bytes, double key_bound, uint64_t *out_dev, void *stream);
+/* Element-wise min of a received plane (PX*PY values) into local plane z_local.  mark = 1:
+ * improved cells become pending (their key is min-combined into out_dev[0], their count added
+ * to out_dev[4]); mark = 0: values only (refreshing a ghost plane). */
+int pmp_slab_merge(pmp_grid *g, int weight, void *g_dev, void *ws_dev, int64_t ws_bytes,
+                   int z_local, int mark, const void *plane_dev, uint64_t *out_dev, void *stream);
 
 #ifdef __cplusplus
 }

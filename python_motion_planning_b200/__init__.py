@@ -1,0 +1,18 @@
+"""B200-native grid graph search behind python_motion_planning's planner API.
+
+    import python_motion_planning_b200 as pmp
+    env = pmp.Grid(51, 31); ...; env.update(obstacles)
+    cost, path, expand = pmp.AStar(start=(5, 5), goal=(45, 25), env=env).plan()
+
+Importing the package needs neither the shared library nor a GPU; every compute call does and
+raises loudly otherwise (there is no CPU fallback).
+"""
+from .environment import Env, Env3D, Grid, Grid3D, Node, Node3D
+from .planner import (AStar, AStar3D, Dijkstra, Dijkstra3D, GBFS, GBFS3D, GraphSearcher,
+                      GraphSearcher3D, Planner, Planner3D, SearchFactory, ExpandView)
+from .batch import plan_batch, cost_field
+from ._lib import PmpError
+
+__all__ = ["Env", "Env3D", "Grid", "Grid3D", "Node", "Node3D", "AStar", "AStar3D", "Dijkstra",
+           "Dijkstra3D", "GBFS", "GBFS3D", "GraphSearcher", "GraphSearcher3D", "Planner",
+           "Planner3D", "SearchFactory", "ExpandView", "plan_batch", "cost_field", "PmpError"]

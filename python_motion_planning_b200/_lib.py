@@ -1,0 +1,112 @@
+"""ctypes binding of libpmp_b200.so (include/pmp_b200.h).
+
+There is no CPU fallback: if the shared library or a CUDA device is missing, every compute
+entry point raises.  PyTorch is used only to own device buffers and streams.
+"""
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpmp_b200.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+ASTAR, DIJKSTRA, GBFS = 0, 1, 2
+H_EUCLIDEAN, H_MANHATTAN = 0, 1
+W_F64, W_U32 = 0, 1
+ST_RUNNING, ST_EXHAUSTED, ST_REACHED, ST_BAD_QUERY = 0, 1, 2, 3
+
+# every symbol include/pmp_b200.h declares (tests/test_abi.py checks the header against this)
+SYMBOLS = (
+    "pmp_last_error", "pmp_abi_version", "pmp_device_count",
+    "pmp_grid_create", "pmp_grid_destroy", "pmp_grid_layout", "pmp_grid_set_cells",
+    "pmp_grid_set_dense", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
+    "pmp_grid_set_motions", "pmp_sssp_sizes", "pmp_sssp", "pmp_field_finalize",
+    "pmp_count_settled", "pmp_extract_paths", "pmp_gbfs",
+    "pmp_slab_begin", "pmp_slab_run", "pmp_slab_merge",
+)
+
+
+class PmpError(RuntimeError):
+    pass
+
+
+class SsspParams(ctypes.Structure):
+    _fields_ = [("algo", ctypes.c_int32), ("heuristic", ctypes.c_int32), ("weight", ctypes.c_int32),
+                ("full_field", ctypes.c_int32), ("window", ctypes.c_double),
+                ("max_rounds", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+
+
+def build(force=False, verbose=False):
+    """Compile csrc/*.cu for sm_100a into libpmp_b200.so (nvcc cross-compiles without a GPU)."""
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))]
+    srcs.append(os.path.join(_HERE, "..", "include", "pmp_b200.h"))
+    if (not force and os.path.exists(LIB_PATH)
+            and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs)):
+        return LIB_PATH
+    cmd = ["make", "-C", CSRC, "-j4"] + (["-B"] if force else [])
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if verbose or res.returncode != 0:
+        print(res.stdout)
+    if res.returncode != 0:
+        raise PmpError("building libpmp_b200.so failed")
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    """The loaded library.  Raises PmpError when it is absent (no fallback path exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise PmpError(f"{LIB_PATH} not found: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                       "(or make -C python_motion_planning_b200/csrc). There is no CPU fallback.")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, i32, i64, dbl = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_double
+    L.pmp_last_error.restype = ctypes.c_char_p
+    L.pmp_last_error.argtypes = []
+    L.pmp_abi_version.restype = i32
+    L.pmp_device_count.restype = i32
+    sig = {
+        "pmp_grid_create": [i32, vp, ctypes.POINTER(vp)],
+        "pmp_grid_destroy": [vp],
+        "pmp_grid_layout": [vp, vp],
+        "pmp_grid_set_cells": [vp, vp, i64, vp],
+        "pmp_grid_set_dense": [vp, vp, vp],
+        "pmp_grid_edit_cells": [vp, vp, i64, i32, vp],
+        "pmp_grid_read_bits": [vp, vp, i64],
+        "pmp_grid_count_free": [vp, vp],
+        "pmp_grid_set_motions": [vp, i32, vp, vp],
+        "pmp_sssp_sizes": [vp, i64, i32, vp, vp],
+        "pmp_sssp": [vp, ctypes.POINTER(SsspParams), i64, vp, vp, vp, vp, i64, vp, vp, vp, vp],
+        "pmp_field_finalize": [vp, i64, vp],
+        "pmp_count_settled": [vp, i32, i64, vp, vp, vp, i32, vp, vp],
+        "pmp_extract_paths": [vp, i32, i64, vp, vp, vp, vp, i64, vp, vp, vp],
+        "pmp_gbfs": [vp, i32, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp, vp],
+        "pmp_slab_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, i64, vp],
+        "pmp_slab_run": [vp, ctypes.POINTER(SsspParams), vp, vp, i64, dbl, vp, vp],
+        "pmp_slab_merge": [vp, i32, vp, vp, i64, i32, i32, vp, vp, vp],
+    }
+    for name, argtypes in sig.items():
+        fn = getattr(L, name)
+        fn.restype = i32
+        fn.argtypes = argtypes
+    _lib = L
+    return L
+
+
+def check(rc, what):
+    if rc != 0:
+        raise PmpError(f"{what} failed ({rc}): {lib().pmp_last_error().decode(errors='replace')}")
+
+
+def require_cuda():
+    """torch + a visible CUDA device, or a loud failure."""
+    import torch
+    if not torch.cuda.is_available():
+        raise PmpError("python_motion_planning_b200 needs a CUDA device (B200, sm_100a); "
+                       "there is no CPU fallback")
+    return torch

@@ -1,0 +1,116 @@
+"""Batched queries and full cost-to-go fields: the data-parallel entry points that have no
+counterpart in the reference's one-query-at-a-time API but run the same planners' arithmetic
+(BASELINE.json configs 3-5).  Independent queries share one occupancy bitmask and are
+processed concurrently by one persistent kernel."""
+import math
+
+import numpy as np
+
+from . import _lib, engine
+from .environment import motion_table
+
+_ALGO = {"a_star": _lib.ASTAR, "astar": _lib.ASTAR, "dijkstra": _lib.DIJKSTRA}
+
+
+class BatchResult:
+    """costs: (nq,) float64 (+inf = no path); paths: list of (n_i, ndim) int arrays in
+    goal->start order (None when not requested); stats: kernel counters; timing in ms."""
+
+    def __init__(self):
+        self.costs = None
+        self.gcosts = None
+        self.status = None
+        self.paths = None
+        self.path_len = None
+        self.stats = np.zeros(8, dtype=np.int64)
+        self.settled = None
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+
+def _wave_size(dg, nq, weight, max_bytes):
+    esz = 8 if weight == _lib.W_F64 else 4
+    per_q = dg.pcells * esz + dg.ntiles * (8 + 128 + 8)
+    w = max(1, int(max_bytes // per_q))
+    w = min(w, nq, max(1, (2 ** 32 - 2) // max(dg.ntiles, 1) - 1))
+    return w
+
+
+def plan_batch(env, starts, goals, algo="dijkstra", heuristic_type="euclidean", weight="f64",
+               want_paths=True, want_settled=False, window=0.0, max_concurrent=None,
+               max_field_bytes=48 << 30, path_cap=None):
+    """Plan nq independent (start, goal) queries on one environment.
+
+    starts, goals: (nq, ndim) integer arrays.  Returns a BatchResult.  Costs follow the
+    reference's convention (sum of step lengths accumulated goal->start along the returned
+    path); paths are goal->start coordinate arrays."""
+    ndim = env._ndim
+    starts = np.asarray(starts, dtype=np.int32).reshape(-1, ndim)
+    goals = np.asarray(goals, dtype=np.int32).reshape(-1, ndim)
+    nq = len(starts)
+    dg = env.device_grid()
+    dg.set_motions(*motion_table(env, ndim))
+    t = dg.torch
+    wt = _lib.W_U32 if weight == "u32" else _lib.W_F64
+    wave = _wave_size(dg, nq, wt, max_field_bytes)
+    if max_concurrent:
+        wave = min(wave, int(max_concurrent))
+    res = BatchResult()
+    res.costs = np.full(nq, np.inf)
+    res.gcosts = np.full(nq, np.inf)
+    res.status = np.zeros(nq, dtype=np.int32)
+    res.path_len = np.zeros(nq, dtype=np.int32)
+    if want_paths:
+        res.paths = [None] * nq
+    if want_settled:
+        res.settled = np.zeros(nq, dtype=np.int64)
+    hid = _lib.H_MANHATTAN if heuristic_type == "manhattan" else _lib.H_EUCLIDEAN
+    cap = path_cap or int(min(dg.pcells, 6 * sum(dg.dims) + 4096))
+    for q0 in range(0, nq, wave):
+        n = min(wave, nq - q0)
+        ws = engine.get_workspace(dg, n, wt)
+        res.h2d_bytes += engine.upload_queries(ws, starts[q0:q0 + n], goals[q0:q0 + n], ndim)
+        engine.sssp(ws, _ALGO[algo], hid, window=window)
+        engine.extract_paths(ws, cap)
+        plen = ws.path_len.cpu().numpy()
+        if (plen == -1).any():                      # rare: a path longer than the first guess
+            cap = int(dg.pcells)
+            engine.extract_paths(ws, cap)
+            plen = ws.path_len.cpu().numpy()
+        res.costs[q0:q0 + n] = ws.cost.cpu().numpy()
+        res.gcosts[q0:q0 + n] = ws.gcost.cpu().numpy()
+        res.status[q0:q0 + n] = ws.status.cpu().numpy()
+        res.path_len[q0:q0 + n] = plen
+        res.stats += ws.stats.cpu().numpy()
+        res.d2h_bytes += n * (8 + 8 + 4 + 4) + 64
+        if want_settled:
+            res.settled[q0:q0 + n] = engine.count_settled(ws, bounded=True, use_h=_ALGO[algo] == _lib.ASTAR).cpu().numpy()
+        if want_paths:
+            # one compacted D2H of all path cells of the wave
+            lens = np.maximum(plen, 0)
+            mask = t.arange(ws.path_cap, device=dg.device)[None, :] < t.from_numpy(lens).to(dg.device)[:, None]
+            flat = ws.path[mask].cpu().numpy()
+            res.d2h_bytes += flat.nbytes
+            coords = engine.cells_to_coords(flat, dg)
+            off = np.concatenate([[0], np.cumsum(lens)])
+            for i in range(n):
+                res.paths[q0 + i] = coords[off[i]:off[i + 1]]
+    res.costs[res.path_len <= 0] = np.inf
+    return res
+
+
+def cost_field(env, source, weight="f64", window=0.0, to_host=True):
+    """Full single-source cost-to-go field (Dijkstra run to exhaustion, as Dijkstra3D.plan()
+    does when the goal is unreachable, dijkstra3d.py:86-87).  Returns a float64 numpy array
+    indexed [x, y(, z)] with +inf for unreachable cells, or (Workspace, stats) with
+    to_host=False (the field stays on the device: Workspace.g[0], padded layout)."""
+    ndim = env._ndim
+    dg = env.device_grid()
+    dg.set_motions(*motion_table(env, ndim))
+    wt = _lib.W_U32 if weight == "u32" else _lib.W_F64
+    ws = engine.get_workspace(dg, 1, wt)
+    engine.upload_queries(ws, [tuple(source)], None, ndim)
+    engine.sssp(ws, _lib.DIJKSTRA, 0, full_field=True, window=window, have_goals=False)
+    if not to_host:
+        return ws, ws.stats
+    return engine.field_to_numpy(ws, 0)

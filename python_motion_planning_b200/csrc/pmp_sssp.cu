@@ -76,6 +76,7 @@ struct SsspArgs {
     u32 *ctr;      // [0,1] worklist counts, [2,3] worklist heads, [4,5] live tiles
     u64 *stats;    // rounds, tile activations, cells expanded, edges relaxed, wl high-water
     double window, sub, he, hm;
+    u64 key_cap; // slab mode: only keys below this bound are processed (KEY_INF otherwise)
     int use_h, full_field, max_rounds;
 };
 
@@ -333,9 +334,11 @@ __global__ void __launch_bounds__(NT) k_sssp(const __grid_constant__ SsspArgs A)
                 if (k != KEY_INF) {
                     const u32 q = gt / ntiles;
                     if (ld_cg(&A.done[q]) == 0) {
-                        live = true;
                         if (k < ld_cg(&A.qmin[cur][q])) atomicMin(&A.qmin[cur][q], k);
-                        take = k < ld_cg(&A.T[cur][q]);
+                        if (k < A.key_cap) {
+                            live = true;
+                            take = k < ld_cg(&A.T[cur][q]);
+                        }
                     }
                 }
             }
@@ -375,7 +378,8 @@ __global__ void __launch_bounds__(NT) k_sssp(const __grid_constant__ SsspArgs A)
                 }
                 if (st) A.done[q] = st;
             }
-            A.T[nxt][q] = (k == KEY_INF) ? KEY_INF : W::key_add(k, A.window);
+            u64 tn = (k == KEY_INF) ? KEY_INF : W::key_add(k, A.window);
+            A.T[nxt][q] = tn < A.key_cap ? tn : A.key_cap;
             A.qmin[nxt][q] = KEY_INF;
         }
         if (blockIdx.x == 0 && tid == 0) {
@@ -542,7 +546,7 @@ extern "C" int pmp_sssp_sizes(const pmp_grid *g, int64_t nq, int weight, int64_t
 }
 
 template <class C>
-static int launch_sssp(pmp_grid *g, SsspArgs &A, double *gcost_dev, int32_t *status_dev, cudaStream_t s) {
+static int launch_sssp(pmp_grid *g, SsspArgs &A, double *gcost_dev, int32_t *status_dev, cudaStream_t s, int mode) {
     typedef typename C::W W;
     static int blocks_per_sm = 0, n_sm = 0;
     if (!blocks_per_sm) {
@@ -553,48 +557,38 @@ static int launch_sssp(pmp_grid *g, SsspArgs &A, double *gcost_dev, int32_t *sta
         if (blocks_per_sm < 1) { pmp_set_error("k_sssp does not fit on an SM"); return -2; }
     }
     const unsigned ib = (unsigned)((A.nq + 255) / 256);
-    k_sssp_init<C><<<ib > 1024 ? 1024 : ib, 256, 0, s>>>(A);
-    PMP_CHECK_CUDA(cudaGetLastError());
-    // persistent grid: every CTA resident (cooperative launch), a multiple of the SM count
-    dim3 grid((unsigned)(blocks_per_sm * n_sm)), block(NT);
-    void *args[] = {(void *)&A};
-    PMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void *)k_sssp<C>, grid, block, args, 0, s));
-    k_sssp_finish<W><<<ib > 1024 ? 1024 : ib, 256, 0, s>>>(A, gcost_dev, status_dev);
-    PMP_CHECK_CUDA(cudaGetLastError());
+    if (mode & 1) {
+        k_sssp_init<C><<<ib > 1024 ? 1024 : ib, 256, 0, s>>>(A);
+        PMP_CHECK_CUDA(cudaGetLastError());
+    }
+    if (mode & 2) {
+        // persistent grid: every CTA resident (cooperative launch), a multiple of the SM count
+        dim3 grid((unsigned)(blocks_per_sm * n_sm)), block(NT);
+        void *args[] = {(void *)&A};
+        PMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void *)k_sssp<C>, grid, block, args, 0, s));
+    }
+    if (mode & 4) {
+        k_sssp_finish<W><<<ib > 1024 ? 1024 : ib, 256, 0, s>>>(A, gcost_dev, status_dev);
+        PMP_CHECK_CUDA(cudaGetLastError());
+    }
     return 0;
 }
 
-extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
-                        const int32_t *starts_dev, const int32_t *goals_dev,
-                        void *g_dev, void *ws_dev, int64_t ws_bytes,
-                        double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream) {
-    if (!g || !P || nq < 1 || !starts_dev || !g_dev || !ws_dev) {
-        pmp_set_error("pmp_sssp: bad arguments");
-        return -1;
-    }
-    if (!goals_dev && !P->full_field) {
-        pmp_set_error("pmp_sssp: goals_dev is NULL but full_field is 0");
-        return -1;
-    }
-    if (P->weight != PMP_W_F64 && P->weight != PMP_W_U32) { pmp_set_error("pmp_sssp: bad weight type"); return -1; }
-    if (P->weight == PMP_W_U32 && !g->integer_costs) {
-        pmp_set_error("pmp_sssp: PMP_W_U32 needs integer motion costs");
-        return -1;
-    }
-    if (P->algo != PMP_ASTAR && P->algo != PMP_DIJKSTRA) {
-        pmp_set_error("pmp_sssp: algo must be PMP_ASTAR or PMP_DIJKSTRA (GBFS: pmp_gbfs)");
-        return -1;
-    }
-    if ((u64)nq * g->d.ntiles >= 0xFFFFFFFFull) { pmp_set_error("pmp_sssp: nq * tiles too large"); return -1; }
-    const WsLayout L = ws_layout(g, nq);
-    if ((size_t)ws_bytes < L.total) {
-        pmp_set_error("pmp_sssp: workspace %lld B < required %zu B", (long long)ws_bytes, L.total);
-        return -1;
-    }
-    cudaStream_t s = (cudaStream_t)stream;
+static int dispatch_sssp(pmp_grid *g, int weight, SsspArgs &A, double *gcost_dev, int32_t *status_dev,
+                         cudaStream_t s, int mode) {
+    if (g->d.ndim == 2)
+        return weight == PMP_W_F64 ? launch_sssp<C2F>(g, A, gcost_dev, status_dev, s, mode)
+                                   : launch_sssp<C2U>(g, A, gcost_dev, status_dev, s, mode);
+    return weight == PMP_W_F64 ? launch_sssp<C3F>(g, A, gcost_dev, status_dev, s, mode)
+                               : launch_sssp<C3U>(g, A, gcost_dev, status_dev, s, mode);
+}
+
+static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const int32_t *starts_dev,
+                      const int32_t *goals_dev, void *g_dev, void *ws_dev, const WsLayout &L, SsspArgs &A) {
     char *ws = (char *)ws_dev;
-    SsspArgs A;
     memset(&A, 0, sizeof A);
+    A.key_cap = KEY_INF;
+
     A.G = g->d;
     A.M = g->mot;
     A.nq = (u32)nq;
@@ -629,6 +623,38 @@ extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
     if (P->weight == PMP_W_U32 && window < 1.0) window = 1.0;
     A.window = window;
 
+}
+
+extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
+                        const int32_t *starts_dev, const int32_t *goals_dev,
+                        void *g_dev, void *ws_dev, int64_t ws_bytes,
+                        double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream) {
+    if (!g || !P || nq < 1 || !starts_dev || !g_dev || !ws_dev) {
+        pmp_set_error("pmp_sssp: bad arguments");
+        return -1;
+    }
+    if (!goals_dev && !P->full_field) {
+        pmp_set_error("pmp_sssp: goals_dev is NULL but full_field is 0");
+        return -1;
+    }
+    if (P->weight != PMP_W_F64 && P->weight != PMP_W_U32) { pmp_set_error("pmp_sssp: bad weight type"); return -1; }
+    if (P->weight == PMP_W_U32 && !g->integer_costs) {
+        pmp_set_error("pmp_sssp: PMP_W_U32 needs integer motion costs");
+        return -1;
+    }
+    if (P->algo != PMP_ASTAR && P->algo != PMP_DIJKSTRA) {
+        pmp_set_error("pmp_sssp: algo must be PMP_ASTAR or PMP_DIJKSTRA (GBFS: pmp_gbfs)");
+        return -1;
+    }
+    if ((u64)nq * g->d.ntiles >= 0xFFFFFFFFull) { pmp_set_error("pmp_sssp: nq * tiles too large"); return -1; }
+    const WsLayout L = ws_layout(g, nq);
+    if ((size_t)ws_bytes < L.total) {
+        pmp_set_error("pmp_sssp: workspace %lld B < required %zu B", (long long)ws_bytes, L.total);
+        return -1;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    SsspArgs A;
+    fill_args(g, P, nq, starts_dev, goals_dev, g_dev, ws_dev, L, A);
     const size_t gsz = (size_t)nq * g->d.pcells * (P->weight == PMP_W_F64 ? 8 : 4);
     PMP_CHECK_CUDA(cudaMemsetAsync(g_dev, 0xFF, gsz, s));
     const size_t nt = (size_t)nq * g->d.ntiles;
@@ -637,11 +663,7 @@ extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 8 * 8, s));
 
-    int rc;
-    if (g->d.ndim == 2) rc = P->weight == PMP_W_F64 ? launch_sssp<C2F>(g, A, gcost_dev, status_dev, s)
-                                                    : launch_sssp<C2U>(g, A, gcost_dev, status_dev, s);
-    else rc = P->weight == PMP_W_F64 ? launch_sssp<C3F>(g, A, gcost_dev, status_dev, s)
-                                     : launch_sssp<C3U>(g, A, gcost_dev, status_dev, s);
+    const int rc = dispatch_sssp(g, P->weight, A, gcost_dev, status_dev, s, 7);
     if (rc) return rc;
     if (stats_dev)
         PMP_CHECK_CUDA(cudaMemcpyAsync(stats_dev, A.stats, 8 * 8, cudaMemcpyDeviceToDevice, s));
@@ -661,7 +683,7 @@ extern "C" int pmp_field_finalize(void *g_dev, int64_t n_cells, void *stream) {
 extern "C" int pmp_count_settled(const pmp_grid *g, int weight, int64_t nq, const void *g_dev,
                                  const int32_t *goals_dev, const double *gcost_dev, int heuristic,
                                  uint64_t *counts_dev, void *stream) {
-    (void)heuristic;
+    const double he = heuristic < 0 ? 0.0 : g->he_scale, hm = heuristic < 0 ? 0.0 : g->hm_scale;
     if (!g || !g_dev || !counts_dev || nq < 1 || nq > 65535) { pmp_set_error("pmp_count_settled: bad arguments (nq <= 65535)"); return -1; }
     cudaStream_t s = (cudaStream_t)stream;
     PMP_CHECK_CUDA(cudaMemsetAsync(counts_dev, 0, (size_t)nq * 8, s));
@@ -670,9 +692,143 @@ extern "C" int pmp_count_settled(const pmp_grid *g, int weight, int64_t nq, cons
     if (bx > cap) bx = cap;
     dim3 grid((unsigned)bx, (unsigned)nq);
     if (weight == PMP_W_F64)
-        k_count_settled<WF64><<<grid, 256, 0, s>>>(g->d, (u32)nq, (const u64 *)g_dev, goals_dev, gcost_dev, g->he_scale, g->hm_scale, (u64 *)counts_dev);
+        k_count_settled<WF64><<<grid, 256, 0, s>>>(g->d, (u32)nq, (const u64 *)g_dev, goals_dev, gcost_dev, he, hm, (u64 *)counts_dev);
     else
-        k_count_settled<WU32><<<grid, 256, 0, s>>>(g->d, (u32)nq, (const u32 *)g_dev, goals_dev, gcost_dev, 0.0, floor(g->hm_scale), (u64 *)counts_dev);
+        k_count_settled<WU32><<<grid, 256, 0, s>>>(g->d, (u32)nq, (const u32 *)g_dev, goals_dev, gcost_dev, 0.0, floor(hm), (u64 *)counts_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// slab mode (one z-slab of a large grid per GPU; the host exchanges boundary planes between
+// runs -- python_motion_planning_b200/slab.py).  The handle describes the LOCAL slab including
+// its ghost planes; a run processes every key below `key_bound` to local convergence.
+// ---------------------------------------------------------------------------------------------
+__global__ void k_slab_arm(SsspArgs A, u64 cap) {
+    A.qmin[0][0] = KEY_INF; A.qmin[1][0] = KEY_INF;
+    A.T[0][0] = cap; A.T[1][0] = cap;
+    A.done[0] = 0;
+    A.goalcell[0] = 0xFFFFFFFFu;
+    for (int i = 0; i < 16; ++i) A.ctr[i] = 0;
+}
+
+__global__ void k_slab_export(SsspArgs A, u64 *out) {
+    const u64 a = A.qmin[0][0], b = A.qmin[1][0];
+    out[0] = a < b ? a : b; // smallest pending key left in this slab (KEY_INF: none)
+    out[1] = A.stats[0];
+    out[2] = A.stats[1];
+    out[3] = A.stats[2];
+}
+
+template <class C>
+__global__ void k_slab_merge(SsspArgs A, int z, const typename C::G *plane, int mark, u64 *out) {
+    typedef typename C::W W;
+    typedef typename C::G G;
+    const GridDev &Gd = A.G;
+    const size_t n = (size_t)Gd.PX * Gd.PY;
+    G *gz = (G *)A.g + (size_t)z * n;
+    u64 local_min = KEY_INF;
+    u32 improved = 0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const G v = plane[i];
+        if (v == W::inf() || v >= gz[i]) continue;
+        const int x = (int)(i % Gd.PX), y = (int)(i / Gd.PX);
+        if (cell_blocked(Gd, x, y, z)) continue;
+        gz[i] = v;
+        ++improved;
+        if (!mark) continue;
+        const int tx = x / C::TX, ty = y / C::TY, tz = z / C::TZ;
+        const int c = ((z - tz * C::TZ) * C::TY + (y - ty * C::TY)) * C::TX + (x - tx * C::TX);
+        const u32 t = (u32)((tz * Gd.nty + ty) * Gd.ntx + tx);
+        atomicOr(A.dirty + (size_t)t * C::NPW + (c >> 5), 1u << (c & 31));
+        const u64 k = W::key(v, 0.0);
+        atomicMin(&A.minkey[t], k);
+        local_min = k < local_min ? k : local_min;
+    }
+    local_min = warp_min_u64(local_min);
+    for (int o = 16; o; o >>= 1) improved += __shfl_down_sync(0xFFFFFFFFu, improved, o);
+    if ((threadIdx.x & 31) == 0) {
+        if (local_min != KEY_INF) atomicMin(&out[0], local_min);
+        if (improved) atomicAdd(&out[4], (u64)improved);
+    }
+}
+
+static int slab_check(pmp_grid *g, const pmp_sssp_params *P, void *g_dev, void *ws_dev, int64_t ws_bytes,
+                      WsLayout &L) {
+    if (!g || !P || !g_dev || !ws_dev) { pmp_set_error("pmp_slab: bad arguments"); return -1; }
+    if (P->weight != PMP_W_F64 && P->weight != PMP_W_U32) { pmp_set_error("pmp_slab: bad weight type"); return -1; }
+    if (P->weight == PMP_W_U32 && !g->integer_costs) { pmp_set_error("pmp_slab: PMP_W_U32 needs integer motion costs"); return -1; }
+    L = ws_layout(g, 1);
+    if ((size_t)ws_bytes < L.total) { pmp_set_error("pmp_slab: workspace too small"); return -1; }
+    return 0;
+}
+
+extern "C" int pmp_slab_begin(pmp_grid *g, const pmp_sssp_params *P, const int32_t *start_dev,
+                              void *g_dev, void *ws_dev, int64_t ws_bytes, void *stream) {
+    WsLayout L;
+    if (slab_check(g, P, g_dev, ws_dev, ws_bytes, L)) return -1;
+    cudaStream_t s = (cudaStream_t)stream;
+    pmp_sssp_params Q = *P;
+    Q.full_field = 1;
+    Q.algo = PMP_DIJKSTRA;
+    SsspArgs A;
+    fill_args(g, &Q, 1, start_dev, nullptr, g_dev, ws_dev, L, A);
+    PMP_CHECK_CUDA(cudaMemsetAsync(g_dev, 0xFF, (size_t)g->d.pcells * (Q.weight == PMP_W_F64 ? 8 : 4), s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, (size_t)g->d.ntiles * 8, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.dirty, 0, (size_t)g->d.ntiles * 32 * 4, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 8 * 8, s));
+    if (start_dev) return dispatch_sssp(g, Q.weight, A, nullptr, nullptr, s, 1);
+    k_slab_arm<<<1, 1, 0, s>>>(A, KEY_INF);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pmp_slab_run(pmp_grid *g, const pmp_sssp_params *P, void *g_dev, void *ws_dev,
+                            int64_t ws_bytes, double key_bound, uint64_t *out_dev, void *stream) {
+    WsLayout L;
+    if (slab_check(g, P, g_dev, ws_dev, ws_bytes, L)) return -1;
+    if (!out_dev) { pmp_set_error("pmp_slab_run: out_dev is NULL"); return -1; }
+    cudaStream_t s = (cudaStream_t)stream;
+    pmp_sssp_params Q = *P;
+    Q.full_field = 1;
+    Q.algo = PMP_DIJKSTRA;
+    SsspArgs A;
+    fill_args(g, &Q, 1, nullptr, nullptr, g_dev, ws_dev, L, A);
+    u64 cap = KEY_INF;
+    if (isfinite(key_bound)) {
+        if (Q.weight == PMP_W_F64) memcpy(&cap, &key_bound, 8);
+        else cap = (u64)key_bound;
+    }
+    A.key_cap = cap;
+    k_slab_arm<<<1, 1, 0, s>>>(A, cap);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    const int rc = dispatch_sssp(g, Q.weight, A, nullptr, nullptr, s, 2);
+    if (rc) return rc;
+    k_slab_export<<<1, 1, 0, s>>>(A, (u64 *)out_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pmp_slab_merge(pmp_grid *g, int weight, void *g_dev, void *ws_dev, int64_t ws_bytes,
+                              int z_local, int mark, const void *plane_dev, uint64_t *out_dev, void *stream) {
+    pmp_sssp_params Q;
+    memset(&Q, 0, sizeof Q);
+    Q.weight = weight; Q.full_field = 1; Q.algo = PMP_DIJKSTRA;
+    WsLayout L;
+    if (slab_check(g, &Q, g_dev, ws_dev, ws_bytes, L)) return -1;
+    if (!plane_dev || !out_dev || z_local < 0 || z_local >= g->d.PZ || g->d.ndim != 3) {
+        pmp_set_error("pmp_slab_merge: bad arguments");
+        return -1;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    SsspArgs A;
+    fill_args(g, &Q, 1, nullptr, nullptr, g_dev, ws_dev, L, A);
+    const size_t n = (size_t)g->d.PX * g->d.PY;
+    unsigned blocks = (unsigned)((n + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (weight == PMP_W_F64) k_slab_merge<C3F><<<blocks, 256, 0, s>>>(A, z_local, (const u64 *)plane_dev, mark, (u64 *)out_dev);
+    else k_slab_merge<C3U><<<blocks, 256, 0, s>>>(A, z_local, (const u32 *)plane_dev, mark, (u64 *)out_dev);
     PMP_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
