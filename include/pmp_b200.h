@@ -113,8 +113,10 @@ int pmp_sssp_sizes(const pmp_grid *g, int64_t nq, int weight, int64_t *g_bytes_p
  *                pmp_field_finalize; u32: 0xFFFFFFFF).
  *   ws_dev     : scratch of >= ws_bytes from pmp_sssp_sizes
  *   gcost_dev  : nq doubles, g[goal] (+inf if not reached);  status_dev : nq pmp_status
- *   stats_dev  : optional 8 x uint64: rounds, tile activations, cells expanded, edges relaxed,
- *                worklist high-water, reserved...
+ *   stats_dev  : optional 16 x uint64: [0] rounds, [1] tile activations, [2] cells expanded,
+ *                [3] edges relaxed, [4] worklist high-water, [5..7] SM cycles summed over tile
+ *                activations in load / settle / publish, [8] kernel ns, [9..11] ns CTA 0 spent in
+ *                scan / process / waiting at the round barrier, [12] in-tile sub-iterations
  * Fields are bit-exact to a sequential Dijkstra on the same directed graph: every value is the
  * minimum over in-edges of fl(g(u) + w). */
 int pmp_sssp(pmp_grid *g, const pmp_sssp_params *params, int64_t nq,

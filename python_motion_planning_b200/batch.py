@@ -22,7 +22,7 @@ class BatchResult:
         self.status = None
         self.paths = None
         self.path_len = None
-        self.stats = np.zeros(8, dtype=np.int64)
+        self.stats = np.zeros(16, dtype=np.int64)
         self.settled = None
         self.h2d_bytes = 0
         self.d2h_bytes = 0

@@ -55,7 +55,7 @@ struct TileSmem {
     u32 pend[C::NPW];
     u32 chg[C::NCW];
     u32 item;
-    u32 n_exp, n_edge;
+    u32 n_exp, n_edge, n_iter;
     u32 s_live, s_wl_base;
     uint16_t list[C::NCELL];
 };
@@ -74,7 +74,7 @@ struct SsspArgs {
     int *done;
     u32 *goalcell; // padded cell index of each goal (0xFFFFFFFF = none)
     u32 *ctr;      // [0,1] worklist counts, [2,3] worklist heads, [4,5] live tiles
-    u64 *stats;    // rounds, tile activations, cells expanded, edges relaxed, wl high-water
+    u64 *stats;    // 16 counters, see include/pmp_b200.h (pmp_sssp)
     double window, sub, he, hm;
     u64 key_cap; // slab mode: only keys below this bound are processed (KEY_INF otherwise)
     int use_h, full_field, max_rounds;
@@ -90,6 +90,12 @@ __device__ static inline bool smem_min(u64 *p, u64 v) {
     return false;
 }
 __device__ static inline bool smem_min(u32 *p, u32 v) { return atomicMin(p, v) > v; }
+
+__device__ static inline u64 globaltimer_ns() {
+    u64 t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 __device__ static inline u64 warp_min_u64(u64 v) {
 #pragma unroll
@@ -133,8 +139,9 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         S.U = U;
         S.count[0] = S.count[1] = S.count[2] = 0;
         S.kmin_rest[0] = S.kmin_rest[1] = S.kmin_rest[2] = KEY_INF;
-        S.n_exp = 0; S.n_edge = 0;
+        S.n_exp = 0; S.n_edge = 0; S.n_iter = 0;
     }
+    const long long t_begin = clock64();
     if (tid < 27) S.nbrmin[tid] = KEY_INF;
     for (int i = tid; i < C::NCW; i += NT) S.chg[i] = 0;
     __syncthreads();
@@ -158,6 +165,7 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     }
     __syncthreads();
 
+    const long long t_loaded = clock64();
     const u64 T = S.T, U = S.U;
     u64 B = 0; // exclusive upper key of the current sub-bucket; first scan only finds the min
     u64 km_final = KEY_INF;
@@ -201,6 +209,7 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
             S.count[r] = 0;
             S.kmin_rest[r] = KEY_INF;
             S.n_exp += n;
+            S.n_iter += 1;
         }
         if (n == 0) {
             if (km >= T) { km_final = km; break; }
@@ -251,6 +260,7 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         __syncthreads();
     }
 
+    const long long t_looped = clock64();
     // ---- publish.  A: values (atomic min: a neighbour may have lowered a border cell meanwhile)
     for (int w = tid; w < C::NCW; w += NT) {
         u32 bits = S.chg[w];
@@ -302,6 +312,11 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         atomicAdd(&A.stats[1], 1ull);
         atomicAdd(&A.stats[2], (u64)S.n_exp);
         atomicAdd(&A.stats[3], (u64)S.n_edge);
+        const long long t_end = clock64();
+        atomicAdd(&A.stats[5], (u64)(t_loaded - t_begin));
+        atomicAdd(&A.stats[6], (u64)(t_looped - t_loaded));
+        atomicAdd(&A.stats[7], (u64)(t_end - t_looped));
+        atomicAdd(&A.stats[12], (u64)S.n_iter);
     }
     __syncthreads();
 }
@@ -319,9 +334,14 @@ __global__ void __launch_bounds__(NT) k_sssp(const __grid_constant__ SsspArgs A)
     const u32 ntiles = A.G.ntiles;
     const u32 total = A.nq * ntiles;
     const u32 gstride = gridDim.x * NT;
+    const bool timer = blockIdx.x == 0 && tid == 0;
+    u64 t0 = 0, t_scan = 0, t_proc = 0, t_wait = 0;
+    if (timer) t0 = globaltimer_ns();
 
     for (int r = 0;; ++r) {
         const int cur = r & 1, nxt = cur ^ 1;
+        u64 ta = 0;
+        if (timer) ta = globaltimer_ns();
         // ---- SCAN: which (query, tile) pairs fall inside their query's key window ----
         if (tid == 0) S.s_live = 0;
         __syncthreads();
@@ -358,6 +378,8 @@ __global__ void __launch_bounds__(NT) k_sssp(const __grid_constant__ SsspArgs A)
 
         const u32 live = ld_cg(&A.ctr[4 + cur]);
         const u32 nwl = ld_cg(&A.ctr[cur]);
+        u64 tb = 0;
+        if (timer) { tb = globaltimer_ns(); t_scan += tb - ta; }
         if (live == 0) break;
         if (A.max_rounds > 0 && r >= A.max_rounds) break;
 
@@ -397,7 +419,14 @@ __global__ void __launch_bounds__(NT) k_sssp(const __grid_constant__ SsspArgs A)
             if (it >= nwl) break;
             process_tile<C>(A, ld_cg(&A.wl[cur][it]), cur, S);
         }
+        u64 tc = 0;
+        if (timer) { tc = globaltimer_ns(); t_proc += tc - tb; }
         grid.sync();
+        if (timer) t_wait += globaltimer_ns() - tc;
+    }
+    if (timer) {
+        A.stats[8] = globaltimer_ns() - t0;
+        A.stats[9] = t_scan; A.stats[10] = t_proc; A.stats[11] = t_wait;
     }
 }
 
@@ -525,7 +554,7 @@ static WsLayout ws_layout(const pmp_grid *g, int64_t nq) {
     L.done = o; o = align_up(o + (size_t)nq * 4, 256);
     L.goalcell = o; o = align_up(o + (size_t)nq * 4, 256);
     L.ctr = o; o = align_up(o + 16 * 4, 256);
-    L.stats = o; o = align_up(o + 8 * 8, 256);
+    L.stats = o; o = align_up(o + 16 * 8, 256);
     L.total = o;
     return L;
 }
@@ -661,12 +690,12 @@ extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
     PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, nt * 8, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.dirty, 0, nt * 32 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
-    PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 8 * 8, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 16 * 8, s));
 
     const int rc = dispatch_sssp(g, P->weight, A, gcost_dev, status_dev, s, 7);
     if (rc) return rc;
     if (stats_dev)
-        PMP_CHECK_CUDA(cudaMemcpyAsync(stats_dev, A.stats, 8 * 8, cudaMemcpyDeviceToDevice, s));
+        PMP_CHECK_CUDA(cudaMemcpyAsync(stats_dev, A.stats, 16 * 8, cudaMemcpyDeviceToDevice, s));
     return 0;
 }
 
@@ -777,7 +806,7 @@ extern "C" int pmp_slab_begin(pmp_grid *g, const pmp_sssp_params *P, const int32
     PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, (size_t)g->d.ntiles * 8, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.dirty, 0, (size_t)g->d.ntiles * 32 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
-    PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 8 * 8, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 16 * 8, s));
     if (start_dev) return dispatch_sssp(g, Q.weight, A, nullptr, nullptr, s, 1);
     k_slab_arm<<<1, 1, 0, s>>>(A, KEY_INF);
     PMP_CHECK_CUDA(cudaGetLastError());

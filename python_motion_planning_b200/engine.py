@@ -25,7 +25,7 @@ class Workspace:
         self.ws = t.empty(self.ws_bytes, dtype=t.uint8, device=dg.device)
         self.gcost = t.empty(nq, dtype=t.float64, device=dg.device)
         self.status = t.empty(nq, dtype=t.int32, device=dg.device)
-        self.stats = t.zeros(8, dtype=t.int64, device=dg.device)
+        self.stats = t.zeros(16, dtype=t.int64, device=dg.device)
         self.starts = t.empty((nq, 3), dtype=t.int32, device=dg.device)
         self.goals = t.empty((nq, 3), dtype=t.int32, device=dg.device)
         self.starts_host = t.empty((nq, 3), dtype=t.int32).pin_memory()

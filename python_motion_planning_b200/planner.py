@@ -251,7 +251,15 @@ class _SearchMixin:
         else:
             h = np.sqrt((d.astype(np.float64) ** 2).sum(axis=1))
         if bound is not None:
-            keep = g + (h if self._algo == _lib.ASTAR else 0.0) <= bound * (1 + 1e-12)
+            # the region the device closed: g + h_adm <= cost, h_adm the admissible heuristic
+            # the kernels order by (max of scaled euclid / manhattan; csrc/pmp_grid.cu)
+            h_adm = 0.0
+            if self._algo == _lib.ASTAR:
+                offs, costs = motion_table(self.env if self.motions is self.env.motions else self, self._ndim)
+                he = min(c / math.sqrt(sum(v * v for v in o)) for o, c in zip(offs, costs))
+                hm = min(c / sum(1 for v in o if v) for o, c in zip(offs, costs))
+                h_adm = np.maximum(he * np.sqrt((d.astype(np.float64) ** 2).sum(axis=1)), hm * d.sum(axis=1))
+            keep = g + h_adm <= bound * (1 + 1e-9)
             coords, g, h = coords[keep], g[keep], h[keep]
         order = np.lexsort((g, g + h))         # by f, then g; the start cell always first
         is_start = np.all(coords[order] == np.array(self.start.current), axis=1)
