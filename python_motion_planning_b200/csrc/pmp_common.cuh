@@ -59,6 +59,10 @@ struct WF64 {
     __device__ static inline G add(G g, const Motions &M, int m) {
         return (G)__double_as_longlong(__longlong_as_double((long long)g) + M.w[m]);
     }
+    __device__ static inline u64 wbits(const Motions &M, int m) { return (u64)__double_as_longlong(M.w[m]); }
+    __device__ static inline G addw(G g, u64 w) {
+        return (G)__double_as_longlong(__longlong_as_double((long long)g) + __longlong_as_double((long long)w));
+    }
     // ordering key of a cell: bits of (g + h)
     __device__ static inline u64 key(G g, double h) {
         return (u64)__double_as_longlong(__longlong_as_double((long long)g) + h);
@@ -77,6 +81,8 @@ struct WU32 {
     static constexpr int kind = PMP_W_U32;
     __host__ __device__ static inline G inf() { return 0xFFFFFFFFu; }
     __device__ static inline G add(G g, const Motions &M, int m) { return g + M.wi[m]; }
+    __device__ static inline u64 wbits(const Motions &M, int m) { return (u64)M.wi[m]; }
+    __device__ static inline G addw(G g, u64 w) { return g + (u32)w; }
     __device__ static inline u64 key(G g, double h) { return (u64)g + (u64)h; }
     __device__ static inline u64 key_add(u64 k, double d) { return k + (u64)d; }
     __device__ static inline double to_double(G g) {

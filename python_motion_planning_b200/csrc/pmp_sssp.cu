@@ -51,9 +51,14 @@ struct TileSmem {
     u64 nbrmin[27];         // smallest key pushed into each neighbour tile
     u64 kmin_rest[3];       // min key of pending cells outside the current sub-bucket
     u64 T, U;
+    u64 m_w[PMP_MAXM];      // motion table staged once per CTA: cost (f64 bits or integer),
+    u32 m_need[PMP_MAXM];   //   neighbourhood cells that must be free,
+    int m_off[PMP_MAXM];    //   (dx+1) | (dy+1)<<2 | (dz+1)<<4 | halo'd smem index delta << 8
     u32 count[3];
     u32 pend[C::NPW];
-    u32 chg[C::NCW];
+    u32 chgi[C::NPW];       // interior cells whose value changed (by cell index)
+    u32 chg[C::NCW];        // halo cells whose value changed (by halo'd index)
+    u32 lmask[C::NCELL];    // legal-motion mask of each compacted frontier cell
     u32 item;
     u32 n_exp, n_edge, n_iter;
     u32 s_live, s_wl_base;
@@ -144,6 +149,7 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     const long long t_begin = clock64();
     if (tid < 27) S.nbrmin[tid] = KEY_INF;
     for (int i = tid; i < C::NCW; i += NT) S.chg[i] = 0;
+    if (tid < C::NPW) S.chgi[tid] = 0;
     __syncthreads();
 
     if (tid < C::NPW) {
@@ -188,7 +194,25 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
                 if (k < B) act = true;
                 else lmin = k < lmin ? k : lmin;
             }
+            u32 legal = 0;
+            if (act) { // legal out-edges of this frontier cell, from the staged occupancy rows
+                const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
+                u32 occ27 = 0;
+#pragma unroll
+                for (int dzz = -C::ZH; dzz <= C::ZH; ++dzz)
+#pragma unroll
+                    for (int dyy = -1; dyy <= 1; ++dyy) {
+                        const u64 r = S.rows[(lz + C::ZH + dzz) * C::HY + (ly + 1 + dyy)];
+                        occ27 |= (u32)((r >> lx) & 7ull) << ((dzz + 1) * 9 + (dyy + 1) * 3);
+                    }
+                const u32 F = ~occ27;
+                for (int mm = 0; mm < A.M.k; ++mm) {
+                    const u32 need = S.m_need[mm];
+                    if ((F & need) == need) legal |= 1u << mm;
+                }
+            }
             const u32 m = __ballot_sync(0xFFFFFFFFu, act);
+            if (lane == 0) S.chgi[w] |= bits;
             if (m) {
                 u32 base = 0;
                 if (lane == 0) {
@@ -196,7 +220,11 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
                     S.pend[w] = bits & ~m;
                 }
                 base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                if (act) S.list[base + __popc(m & ((1u << lane) - 1u))] = (uint16_t)c;
+                if (act) {
+                    const u32 slot = base + __popc(m & ((1u << lane) - 1u));
+                    S.list[slot] = (uint16_t)c;
+                    S.lmask[slot] = legal;
+                }
             }
         }
         lmin = warp_min_u64(lmin);
@@ -217,39 +245,33 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
             B = nb < T ? nb : T;
             continue;
         }
-        // ---- relax the out-edges of the compacted frontier (push) ----
+        // ---- relax the out-edges of the compacted frontier (push), one (cell, motion) per thread
         u32 my_edges = 0;
-        for (u32 i = tid; i < n; i += NT) {
+        const u32 n_task = n * (u32)A.M.k;
+        for (u32 tsk = tid; tsk < n_task; tsk += NT) {
+            const u32 m = tsk / n, i = tsk - m * n;
+            if (!((S.lmask[i] >> m) & 1u)) continue;
+            ++my_edges;
             const int c = S.list[i];
             const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
             const int hi = ((lz + C::ZH) * C::HY + (ly + 1)) * C::HX + (lx + 1);
             const G gu = ((volatile G *)S.g)[hi];
-            u32 occ27 = 0;
-#pragma unroll
-            for (int dzz = -C::ZH; dzz <= C::ZH; ++dzz)
-#pragma unroll
-                for (int dyy = -1; dyy <= 1; ++dyy) {
-                    const u64 r = S.rows[(lz + C::ZH + dzz) * C::HY + (ly + 1 + dyy)];
-                    occ27 |= (u32)((r >> lx) & 7ull) << ((dzz + 1) * 9 + (dyy + 1) * 3);
-                }
-            const u32 F = ~occ27;
-            for (int m = 0; m < A.M.k; ++m) {
-                const u32 need = A.M.need[m];
-                if ((F & need) != need) continue;
-                ++my_edges;
-                const int dx = A.M.dx[m], dy = A.M.dy[m], dz = A.M.dz[m];
-                const int vhi = hi + (dz * C::HY + dy) * C::HX + dx;
-                const G cand = W::add(gu, A.M, m);
-                if (cand >= ((volatile G *)S.g)[vhi]) continue;
-                const int vx = lx + dx, vy = ly + dy, vz = lz + dz;
+            const int mo = S.m_off[m];
+            const int dx = (mo & 3) - 1, dy = ((mo >> 2) & 3) - 1, dz = ((mo >> 4) & 3) - 1;
+            const int vhi = hi + (mo >> 8);
+            const G cand = W::addw(gu, S.m_w[m]);
+            if (cand >= ((volatile G *)S.g)[vhi]) continue;
+            const int vx = lx + dx, vy = ly + dy, vz = lz + dz;
+            if (U != KEY_INF) {
                 const double hv = use_h ? heuristic_lo(ox + vx - gx, oy + vy - gy, oz + vz - gz, A.he, A.hm) : 0.0;
                 if (W::key(cand, hv) > U) continue; // cannot be on a better path to the goal
-                if (!smem_min(&S.g[vhi], cand)) continue;
+            }
+            if (!smem_min(&S.g[vhi], cand)) continue;
+            if ((unsigned)vx < (unsigned)C::TX && (unsigned)vy < (unsigned)C::TY && (unsigned)vz < (unsigned)C::TZ) {
+                const int cv = (vz * C::TY + vy) * C::TX + vx;
+                atomicOr(&S.pend[cv >> 5], 1u << (cv & 31));
+            } else {
                 atomicOr(&S.chg[vhi >> 5], 1u << (vhi & 31));
-                if ((unsigned)vx < (unsigned)C::TX && (unsigned)vy < (unsigned)C::TY && (unsigned)vz < (unsigned)C::TZ) {
-                    const int cv = (vz * C::TY + vy) * C::TX + vx;
-                    atomicOr(&S.pend[cv >> 5], 1u << (cv & 31));
-                }
             }
         }
         if (my_edges) atomicAdd(&S.n_edge, my_edges);
@@ -262,6 +284,17 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
 
     const long long t_looped = clock64();
     // ---- publish.  A: values (atomic min: a neighbour may have lowered a border cell meanwhile)
+    if (tid < C::NPW) {
+        u32 bits = S.chgi[tid];
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const int c = tid * 32 + b;
+            const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
+            const int hi = ((lz + C::ZH) * C::HY + (ly + 1)) * C::HX + (lx + 1);
+            red_min(gq + ((size_t)(oz + lz) * Gd.PY + (oy + ly)) * Gd.PX + (ox + lx), S.g[hi]);
+        }
+    }
     for (int w = tid; w < C::NCW; w += NT) {
         u32 bits = S.chg[w];
         while (bits) {
@@ -273,7 +306,8 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
             red_min(gq + ((size_t)z * Gd.PY + y) * Gd.PX + x, S.g[i]);
         }
     }
-    __threadfence();
+    __syncthreads();
+    if (tid == 0) __threadfence(); // one cumulative fence: every value above is visible before any dirty bit
     __syncthreads();
     // B: dirty bits of improved halo cells (in the neighbour tiles) and of our own leftovers
     for (int w = tid; w < C::NCW; w += NT) {
@@ -286,7 +320,6 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
             const int sx = hx == 0 ? -1 : (hx == C::HX - 1 ? 1 : 0);
             const int sy = hy == 0 ? -1 : (hy == C::HY - 1 ? 1 : 0);
             const int sz = C::ZH ? (hz == 0 ? -1 : (hz == C::HZ - 1 ? 1 : 0)) : 0;
-            if ((sx | sy | sz) == 0) continue; // interior cell
             const int nlx = hx - 1 - sx * C::TX, nly = hy - 1 - sy * C::TY, nlz = hz - C::ZH - sz * C::TZ;
             const int cv = (nlz * C::TY + nly) * C::TX + nlx;
             const u32 ngt = q * Gd.ntiles + (u32)(((ttz + sz) * Gd.nty + (tty + sy)) * Gd.ntx + (ttx + sx));
@@ -296,7 +329,8 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         }
     }
     if (tid < C::NPW && S.pend[tid]) atomicOr(dq + tid, S.pend[tid]);
-    __threadfence();
+    __syncthreads();
+    if (tid == 0) __threadfence(); // dirty bits visible before the tiles are armed
     __syncthreads();
     // C: arm the tiles that received work
     if (tid < 27) {
@@ -325,7 +359,7 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
 // persistent round loop
 // ---------------------------------------------------------------------------------------------
 template <class C>
-__global__ void __launch_bounds__(NT) k_sssp(const __grid_constant__ SsspArgs A) {
+__global__ void __launch_bounds__(NT, 4) k_sssp(const __grid_constant__ SsspArgs A) {
     typedef typename C::W W;
     typedef typename C::G G;
     cg::grid_group grid = cg::this_grid();
@@ -334,6 +368,13 @@ __global__ void __launch_bounds__(NT) k_sssp(const __grid_constant__ SsspArgs A)
     const u32 ntiles = A.G.ntiles;
     const u32 total = A.nq * ntiles;
     const u32 gstride = gridDim.x * NT;
+    if (tid < A.M.k) {
+        const int dx = A.M.dx[tid], dy = A.M.dy[tid], dz = A.M.dz[tid];
+        S.m_w[tid] = W::wbits(A.M, tid);
+        S.m_need[tid] = A.M.need[tid];
+        S.m_off[tid] = (dx + 1) | ((dy + 1) << 2) | ((dz + 1) << 4) | (((dz * C::HY + dy) * C::HX + dx) * 256);
+    }
+    __syncthreads();
     const bool timer = blockIdx.x == 0 && tid == 0;
     u64 t0 = 0, t_scan = 0, t_proc = 0, t_wait = 0;
     if (timer) t0 = globaltimer_ns();
