@@ -99,7 +99,7 @@ typedef struct pmp_sssp_params {
     int32_t full_field; /* 1: ignore goals, settle every reachable cell (cost-to-go field) */
     double window;      /* width of the global key window (delta); <= 0 picks a default */
     int32_t max_rounds; /* safety bound on relaxation rounds; <= 0 = unlimited */
-    int32_t reserved;
+    int32_t reserved;   /* tuning: in-tile sub-bucket width in units of the smallest motion cost (0/1 = 1) */
 } pmp_sssp_params;
 
 /* bytes of one query's cost field and of the scratch workspace for nq concurrent queries */
@@ -108,9 +108,8 @@ int pmp_sssp_sizes(const pmp_grid *g, int64_t nq, int weight, int64_t *g_bytes_p
 
 /* Runs nq independent single-source searches that share the grid.
  *   starts_dev, goals_dev : nq x 3 int32 (goals_dev may be NULL with full_field = 1)
- *   g_dev      : nq cost fields (padded cells; f64 or u32).  Overwritten.  Unreached = +inf
- *                (f64: all-ones bit pattern is used internally and converted by
- *                pmp_field_finalize; u32: 0xFFFFFFFF).
+ *   g_dev      : nq cost fields (padded cells; 8 B or 4 B per cell), overwritten, in the internal
+ *                word format (see pmp_field_finalize).
  *   ws_dev     : scratch of >= ws_bytes from pmp_sssp_sizes
  *   gcost_dev  : nq doubles, g[goal] (+inf if not reached);  status_dev : nq pmp_status
  *   stats_dev  : optional 16 x uint64: [0] rounds, [1] tile activations, [2] cells expanded,
@@ -124,9 +123,11 @@ int pmp_sssp(pmp_grid *g, const pmp_sssp_params *params, int64_t nq,
              void *g_dev, void *ws_dev, int64_t ws_bytes,
              double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream);
 
-/* f64 fields only: rewrite the internal "unreached" pattern to IEEE +inf so the field can be
- * read as doubles.  n_cells = nq * padded cells. */
-int pmp_field_finalize(void *g_dev, int64_t n_cells, void *stream);
+/* Cost fields are kept in an internal word format while searching (value << 1 | clean flag).
+ * This rewrites n_cells = nq * padded cells in place to plain values: IEEE doubles with +inf
+ * for unreached cells (PMP_W_F64) or uint32 with 0xFFFFFFFF (PMP_W_U32).  A finalized field can
+ * no longer be passed to pmp_extract_paths / pmp_count_settled. */
+int pmp_field_finalize(void *g_dev, int weight, int64_t n_cells, void *stream);
 
 /* counts cells with a finite value per query (N_settled of the GTEPS metric); if
  * gcost_dev != NULL only cells with g + h <= gcost (A-star's closed region) are counted;

@@ -82,7 +82,7 @@ def lib():
         "pmp_grid_set_motions": [vp, i32, vp, vp],
         "pmp_sssp_sizes": [vp, i64, i32, vp, vp],
         "pmp_sssp": [vp, ctypes.POINTER(SsspParams), i64, vp, vp, vp, vp, i64, vp, vp, vp, vp],
-        "pmp_field_finalize": [vp, i64, vp],
+        "pmp_field_finalize": [vp, i32, i64, vp],
         "pmp_count_settled": [vp, i32, i64, vp, vp, vp, i32, vp, vp],
         "pmp_extract_paths": [vp, i32, i64, vp, vp, vp, vp, i64, vp, vp, vp],
         "pmp_gbfs": [vp, i32, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp, vp],

@@ -55,7 +55,13 @@ struct pmp_grid {
 struct WF64 {
     typedef u64 G; // bit pattern of a non-negative double: orders like the double
     static constexpr int kind = PMP_W_F64;
-    __host__ __device__ static inline G inf() { return ~0ull; }
+    // Stored word = (value bits << 1) | clean; clean = 0 marks a cell that still has to
+    // propagate ("pending").  One atomicMin therefore publishes a lower value AND its pending
+    // flag; the sign bit of a non-negative double is free, so the shift is lossless.
+    __host__ __device__ static inline G ginf() { return ~0ull; }      // stored "unreached"
+    __host__ __device__ static inline G inf() { return ~0ull >> 1; }  // decoded "unreached"
+    __host__ __device__ static inline G enc(G v, bool pending) { return (v << 1) | (pending ? 0ull : 1ull); }
+    __host__ __device__ static inline G dec(G s) { return s >> 1; }
     __device__ static inline G add(G g, const Motions &M, int m) {
         return (G)__double_as_longlong(__longlong_as_double((long long)g) + M.w[m]);
     }
@@ -79,7 +85,10 @@ struct WF64 {
 struct WU32 {
     typedef u32 G;
     static constexpr int kind = PMP_W_U32;
-    __host__ __device__ static inline G inf() { return 0xFFFFFFFFu; }
+    __host__ __device__ static inline G ginf() { return 0xFFFFFFFFu; }
+    __host__ __device__ static inline G inf() { return 0x7FFFFFFFu; }
+    __host__ __device__ static inline G enc(G v, bool pending) { return (v << 1) | (pending ? 0u : 1u); }
+    __host__ __device__ static inline G dec(G s) { return s >> 1; }
     __device__ static inline G add(G g, const Motions &M, int m) { return g + M.wi[m]; }
     __device__ static inline u64 wbits(const Motions &M, int m) { return (u64)M.wi[m]; }
     __device__ static inline G addw(G g, u64 w) { return g + (u32)w; }
@@ -97,6 +106,10 @@ __device__ static inline int ld_cg(const int *p) { return __ldcg(p); }
 
 __device__ static inline void red_min(u64 *p, u64 v) { atomicMin(p, v); }
 __device__ static inline void red_min(u32 *p, u32 v) { atomicMin(p, v); }
+__device__ static inline void cas_word(u64 *p, u64 cmp, u64 v) { atomicCAS(p, cmp, v); }
+__device__ static inline void cas_word(u32 *p, u32 cmp, u32 v) { atomicCAS(p, cmp, v); }
+// release/acquire fence at device scope (cheaper than the sequentially consistent __threadfence)
+__device__ static inline void fence_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 
 // n (<= 34) occupancy bits of bitmask row (y, z) for x in [x0, x0 + n); bit i <-> x0 + i.
 // Anything outside the padded grid reads as blocked.

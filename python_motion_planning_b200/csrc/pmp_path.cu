@@ -41,7 +41,7 @@ __global__ void k_extract_paths(const GridDev G, const __grid_constant__ Motions
     const int sx = starts[3 * q], sy = starts[3 * q + 1], sz = G.ndim == 3 ? starts[3 * q + 2] : 0;
     const bool ok = vx >= 0 && vy >= 0 && vz >= 0 && vx < G.X && vy < G.Y && vz < G.Z &&
                     sx >= 0 && sy >= 0 && sz >= 0 && sx < G.X && sy < G.Y && sz < G.Z;
-    if (!ok || gq[((size_t)vz * G.PY + vy) * G.PX + vx] == W::inf()) {
+    if (!ok || gq[((size_t)vz * G.PY + vy) * G.PX + vx] == W::ginf()) {
         if (lane == 0) { plen[q] = 0; cost[q] = INF_D; }
         return;
     }
@@ -56,7 +56,7 @@ __global__ void k_extract_paths(const GridDev G, const __grid_constant__ Motions
         if (lane < M.k) {
             const int ux = vx - M.dx[lane], uy = vy - M.dy[lane], uz = vz - M.dz[lane];
             if (edge_legal(G, M, lane, ux, uy, uz)) {
-                const GT gu = gq[((size_t)uz * G.PY + uy) * G.PX + ux];
+                const GT gu = W::dec(gq[((size_t)uz * G.PY + uy) * G.PX + ux]);
                 if (gu != W::inf()) cand = W::add(gu, M, lane);
             }
         }

@@ -56,11 +56,12 @@ struct TileSmem {
     int m_off[PMP_MAXM];    //   (dx+1) | (dy+1)<<2 | (dz+1)<<4 | halo'd smem index delta << 8
     u32 count[3];
     u32 pend[C::NPW];
+    u32 ldd[C::NPW];        // cells that were pending when the tile was loaded
     u32 chgi[C::NPW];       // interior cells whose value changed (by cell index)
     u32 chg[C::NCW];        // halo cells whose value changed (by halo'd index)
-    u32 lmask[C::NCELL];    // legal-motion mask of each compacted frontier cell
-    u32 item;
-    u32 n_exp, n_edge, n_iter;
+    u32 fmask[C::NCELL];    // free cells of the 3x3x3 neighbourhood of each compacted frontier cell
+    u64 stat[16];           // per-CTA counters (flushed at kernel end)
+    u32 item, n_edge;
     u32 s_live, s_wl_base;
     uint16_t list[C::NCELL];
 };
@@ -72,7 +73,6 @@ struct SsspArgs {
     const int32_t *starts, *goals;
     void *g;
     u64 *minkey;
-    u32 *dirty;
     u32 *wl[2];
     u64 *qmin[2];
     u64 *T[2];
@@ -118,117 +118,154 @@ template <class C>
 __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, TileSmem<C> &S) {
     typedef typename C::W W;
     typedef typename C::G G;
+    constexpr int NW = NT / 32;             // warps per CTA
+    constexpr int WPW = C::NPW / NW;        // pending words per warp
+    constexpr int NLD = (C::HC + NT - 1) / NT;
     const GridDev &Gd = A.G;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const u32 q = gt / Gd.ntiles, t = gt - q * Gd.ntiles;
     const int ttx = t % Gd.ntx, tty = (t / Gd.ntx) % Gd.nty, ttz = t / (Gd.ntx * Gd.nty);
     const int ox = ttx * C::TX, oy = tty * C::TY, oz = ttz * C::TZ;
     G *gq = (G *)A.g + (size_t)q * Gd.pcells;
-    u32 *dq = A.dirty + (size_t)gt * C::NPW;
     const int use_h = A.use_h;
     int gx = 0, gy = 0, gz = 0;
     if (use_h) {
         gx = A.goals[3 * q]; gy = A.goals[3 * q + 1]; gz = Gd.ndim == 3 ? A.goals[3 * q + 2] : 0;
     }
 
+    const long long t_begin = clock64();
     if (tid == 0) {
         atomicExch(&A.minkey[gt], KEY_INF); // claim: later pushes re-arm the tile
-        __threadfence();
+        fence_gpu();
         S.T = ld_cg(&A.T[cur][q]);
         u64 U = KEY_INF;
         const u32 gc = A.full_field ? 0xFFFFFFFFu : A.goalcell[q];
         if (gc != 0xFFFFFFFFu) {
-            const G gg = ld_cg(gq + gc);
+            const G gg = W::dec(ld_cg(gq + gc));
             if (gg != W::inf()) U = W::key(gg, 0.0);
         }
         S.U = U;
         S.count[0] = S.count[1] = S.count[2] = 0;
         S.kmin_rest[0] = S.kmin_rest[1] = S.kmin_rest[2] = KEY_INF;
-        S.n_exp = 0; S.n_edge = 0; S.n_iter = 0;
     }
-    const long long t_begin = clock64();
     if (tid < 27) S.nbrmin[tid] = KEY_INF;
     for (int i = tid; i < C::NCW; i += NT) S.chg[i] = 0;
-    if (tid < C::NPW) S.chgi[tid] = 0;
+    if (tid < C::NPW) { S.chgi[tid] = 0; S.pend[tid] = 0; }
     __syncthreads();
 
-    if (tid < C::NPW) {
-        u32 v = ld_cg(dq + tid);
-        if (v) v = atomicExch(dq + tid, 0u);
-        S.pend[tid] = v;
-    }
-    for (int i = tid; i < C::HC; i += NT) {
-        const int hx = i % C::HX, hy = (i / C::HX) % C::HY, hz = i / (C::HX * C::HY);
-        const int x = ox + hx - 1, y = oy + hy - 1, z = oz + hz - C::ZH;
-        G v = W::inf();
-        if ((unsigned)x < (unsigned)Gd.PX && (unsigned)y < (unsigned)Gd.PY && (unsigned)z < (unsigned)Gd.PZ)
-            v = ld_cg(gq + ((size_t)z * Gd.PY + y) * Gd.PX + x);
-        S.g[i] = v;
-    }
-    for (int i = tid; i < C::NROWS; i += NT) {
-        const int hy = i % C::HY, hz = i / C::HY;
-        S.rows[i] = row_bits(Gd, ox - 1, oy + hy - 1, oz + hz - C::ZH, C::HX);
+    // ---- stage g (tile + halo): all loads first, then decode (keeps NLD loads in flight) ----
+    {
+        G raw[NLD];
+#pragma unroll
+        for (int k = 0; k < NLD; ++k) {
+            const int i = tid + k * NT;
+            const int hx = i % C::HX, hy = (i / C::HX) % C::HY, hz = i / (C::HX * C::HY);
+            const int x = ox + hx - 1, y = oy + hy - 1, z = oz + hz - C::ZH;
+            raw[k] = W::ginf();
+            if (i < C::HC && (unsigned)x < (unsigned)Gd.PX && (unsigned)y < (unsigned)Gd.PY && (unsigned)z < (unsigned)Gd.PZ)
+                raw[k] = ld_cg(gq + ((size_t)z * Gd.PY + y) * Gd.PX + x);
+        }
+        if (tid < C::NROWS) {
+            const int hy = tid % C::HY, hz = tid / C::HY;
+            S.rows[tid] = row_bits(Gd, ox - 1, oy + hy - 1, oz + hz - C::ZH, C::HX);
+        }
+#pragma unroll
+        for (int k = 0; k < NLD; ++k) {
+            const int i = tid + k * NT;
+            if (i < C::HC) {
+                const G sw = raw[k];
+                S.g[i] = W::dec(sw);
+                if (!(sw & 1)) { // pending flag: an interior cell that still has to propagate
+                    const int lx = i % C::HX - 1, ly = (i / C::HX) % C::HY - 1, lz = i / (C::HX * C::HY) - C::ZH;
+                    if ((unsigned)lx < (unsigned)C::TX && (unsigned)ly < (unsigned)C::TY && (unsigned)lz < (unsigned)C::TZ) {
+                        const int c = (lz * C::TY + ly) * C::TX + lx;
+                        atomicOr(&S.pend[c >> 5], 1u << (c & 31));
+                    }
+                }
+            }
+        }
     }
     __syncthreads();
 
     const long long t_loaded = clock64();
     const u64 T = S.T, U = S.U;
+    const int K = A.M.k;
     u64 B = 0; // exclusive upper key of the current sub-bucket; first scan only finds the min
     u64 km_final = KEY_INF;
+    u32 n_exp = 0, n_iter = 0, my_edges = 0;
     for (int it = 0;; ++it) {
         const int p = it % 3;
         // ---- scan the pending mask: compact cells with key < B, track the min of the rest ----
-        u64 lmin = KEY_INF;
-        for (int w = warp; w < C::NPW; w += NT / 32) {
-            const u32 bits = S.pend[w];
-            if (!bits) continue;
-            const bool has = (bits >> lane) & 1u;
-            bool act = false;
-            const int c = w * 32 + lane;
-            if (has) {
-                const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
-                const int hi = ((lz + C::ZH) * C::HY + (ly + 1)) * C::HX + (lx + 1);
-                const G gv = S.g[hi];
-                const double h = use_h ? heuristic_lo(ox + lx - gx, oy + ly - gy, oz + lz - gz, A.he, A.hm) : 0.0;
-                const u64 k = W::key(gv, h);
-                if (k < B) act = true;
-                else lmin = k < lmin ? k : lmin;
-            }
-            u32 legal = 0;
-            if (act) { // legal out-edges of this frontier cell, from the staged occupancy rows
-                const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
-                u32 occ27 = 0;
+        if (it == 0 && lane < WPW) S.ldd[warp * WPW + lane] = S.pend[warp * WPW + lane];
+        u32 bits[WPW];
+        u32 any = 0;
 #pragma unroll
-                for (int dzz = -C::ZH; dzz <= C::ZH; ++dzz)
+        for (int j = 0; j < WPW; ++j) { bits[j] = S.pend[warp * WPW + j]; any |= bits[j]; }
+        if (any) { // warps without pending cells (most of them) fall through to the barrier
+            u64 lmin = KEY_INF;
+            u32 actm[WPW], F[WPW];
+            bool act[WPW];
 #pragma unroll
-                    for (int dyy = -1; dyy <= 1; ++dyy) {
-                        const u64 r = S.rows[(lz + C::ZH + dzz) * C::HY + (ly + 1 + dyy)];
-                        occ27 |= (u32)((r >> lx) & 7ull) << ((dzz + 1) * 9 + (dyy + 1) * 3);
+            for (int j = 0; j < WPW; ++j) {
+                act[j] = false;
+                F[j] = 0;
+                if ((bits[j] >> lane) & 1u) {
+                    const int c = (warp * WPW + j) * 32 + lane;
+                    const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
+                    const int hi = ((lz + C::ZH) * C::HY + (ly + 1)) * C::HX + (lx + 1);
+                    const G gv = S.g[hi];
+                    const double h = use_h ? heuristic_lo(ox + lx - gx, oy + ly - gy, oz + lz - gz, A.he, A.hm) : 0.0;
+                    const u64 k = W::key(gv, h);
+                    if (k < B) {
+                        act[j] = true;
+                        u32 occ27 = 0; // occupancy of the 3x3(x3) neighbourhood from the staged rows
+#pragma unroll
+                        for (int dzz = -C::ZH; dzz <= C::ZH; ++dzz)
+#pragma unroll
+                            for (int dyy = -1; dyy <= 1; ++dyy) {
+                                const u64 r = S.rows[(lz + C::ZH + dzz) * C::HY + (ly + 1 + dyy)];
+                                occ27 |= (u32)((r >> lx) & 7ull) << ((dzz + 1) * 9 + (dyy + 1) * 3);
+                            }
+                        F[j] = ~occ27 & 0x7FFFFFFu;
+                    } else {
+                        lmin = k < lmin ? k : lmin;
                     }
-                const u32 F = ~occ27;
-                for (int mm = 0; mm < A.M.k; ++mm) {
-                    const u32 need = S.m_need[mm];
-                    if ((F & need) == need) legal |= 1u << mm;
                 }
             }
-            const u32 m = __ballot_sync(0xFFFFFFFFu, act);
-            if (lane == 0) S.chgi[w] |= bits;
-            if (m) {
-                u32 base = 0;
-                if (lane == 0) {
-                    base = atomicAdd(&S.count[p], (u32)__popc(m));
-                    S.pend[w] = bits & ~m;
-                }
+            u32 tot = 0;
+#pragma unroll
+            for (int j = 0; j < WPW; ++j) {
+                actm[j] = __ballot_sync(0xFFFFFFFFu, act[j]);
+                tot += __popc(actm[j]);
+            }
+            u32 base = 0;
+            if (lane == 0) {
+                if (tot) base = atomicAdd(&S.count[p], tot);
+#pragma unroll
+                for (int j = 0; j < WPW; ++j)
+                    if (bits[j]) {
+                        const int w = warp * WPW + j;
+                        S.chgi[w] |= bits[j];
+                        if (actm[j]) S.pend[w] = bits[j] & ~actm[j];
+                    }
+            }
+            if (tot) {
                 base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                if (act) {
-                    const u32 slot = base + __popc(m & ((1u << lane) - 1u));
-                    S.list[slot] = (uint16_t)c;
-                    S.lmask[slot] = legal;
+#pragma unroll
+                for (int j = 0; j < WPW; ++j) {
+                    if (act[j]) {
+                        const u32 slot = base + __popc(actm[j] & ((1u << lane) - 1u));
+                        S.list[slot] = (uint16_t)((warp * WPW + j) * 32 + lane);
+                        S.fmask[slot] = F[j];
+                    }
+                    base += __popc(actm[j]);
                 }
+            }
+            if (__any_sync(0xFFFFFFFFu, lmin != KEY_INF)) {
+                lmin = warp_min_u64(lmin);
+                if (lane == 0) atomicMin(&S.kmin_rest[p], lmin);
             }
         }
-        lmin = warp_min_u64(lmin);
-        if (lane == 0 && lmin != KEY_INF) atomicMin(&S.kmin_rest[p], lmin);
         __syncthreads();
         const u32 n = S.count[p];
         const u64 km = S.kmin_rest[p];
@@ -236,32 +273,32 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
             const int r = (it + 2) % 3;
             S.count[r] = 0;
             S.kmin_rest[r] = KEY_INF;
-            S.n_exp += n;
-            S.n_iter += 1;
         }
+        n_exp += n;
+        ++n_iter;
         if (n == 0) {
             if (km >= T) { km_final = km; break; }
-            u64 nb = W::key_add(km, A.sub);
+            const u64 nb = W::key_add(km, A.sub);
             B = nb < T ? nb : T;
             continue;
         }
         // ---- relax the out-edges of the compacted frontier (push), one (cell, motion) per thread
-        u32 my_edges = 0;
-        const u32 n_task = n * (u32)A.M.k;
+        const u32 n_task = n * (u32)K;
+        const u32 inv = 0xFFFFFFFFu / n + 1u; // tsk / n == umulhi(tsk, inv) for tsk * n < 2^32
         for (u32 tsk = tid; tsk < n_task; tsk += NT) {
-            const u32 m = tsk / n, i = tsk - m * n;
-            if (!((S.lmask[i] >> m) & 1u)) continue;
+            const u32 m = n == 1 ? tsk : __umulhi(tsk, inv), i = tsk - m * n;
+            const u32 need = S.m_need[m];
+            if ((S.fmask[i] & need) != need) continue; // isCollision: target / face cells occupied
             ++my_edges;
             const int c = S.list[i];
             const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
             const int hi = ((lz + C::ZH) * C::HY + (ly + 1)) * C::HX + (lx + 1);
             const G gu = ((volatile G *)S.g)[hi];
             const int mo = S.m_off[m];
-            const int dx = (mo & 3) - 1, dy = ((mo >> 2) & 3) - 1, dz = ((mo >> 4) & 3) - 1;
             const int vhi = hi + (mo >> 8);
             const G cand = W::addw(gu, S.m_w[m]);
             if (cand >= ((volatile G *)S.g)[vhi]) continue;
-            const int vx = lx + dx, vy = ly + dy, vz = lz + dz;
+            const int vx = lx + (mo & 3) - 1, vy = ly + ((mo >> 2) & 3) - 1, vz = lz + ((mo >> 4) & 3) - 1;
             if (U != KEY_INF) {
                 const double hv = use_h ? heuristic_lo(ox + vx - gx, oy + vy - gy, oz + vz - gz, A.he, A.hm) : 0.0;
                 if (W::key(cand, hv) > U) continue; // cannot be on a better path to the goal
@@ -274,65 +311,55 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
                 atomicOr(&S.chg[vhi >> 5], 1u << (vhi & 31));
             }
         }
-        if (my_edges) atomicAdd(&S.n_edge, my_edges);
         {
-            u64 nb = W::key_add(B, A.sub);
+            const u64 nb = W::key_add(B, A.sub);
             B = nb < T ? nb : T;
         }
         __syncthreads();
     }
 
     const long long t_looped = clock64();
-    // ---- publish.  A: values (atomic min: a neighbour may have lowered a border cell meanwhile)
-    if (tid < C::NPW) {
-        u32 bits = S.chgi[tid];
-        while (bits) {
-            const int b = __ffs(bits) - 1;
-            bits &= bits - 1;
-            const int c = tid * 32 + b;
+    // ---- publish.  Values and pending flags travel in one word, so one atomic per cell:
+    //  * own cells that changed: atomicMin(value, flag) -- a neighbour may have lowered a border
+    //    cell meanwhile, then its (lower, pending) word stays;
+    //  * own cells that were pending at load, have propagated now and kept their value: CAS
+    //    pending -> clean (fails harmlessly if somebody lowered the cell in between);
+    //  * improved halo cells: atomicMin(value, pending) into the neighbour tile.
+#pragma unroll
+    for (int k = 0; k < C::NCELL / NT; ++k) {
+        const int c = tid + k * NT;
+        const int w = c >> 5, b = c & 31;
+        if ((S.chgi[w] >> b) & 1u) {
             const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
             const int hi = ((lz + C::ZH) * C::HY + (ly + 1)) * C::HX + (lx + 1);
-            red_min(gq + ((size_t)(oz + lz) * Gd.PY + (oy + ly)) * Gd.PX + (ox + lx), S.g[hi]);
+            G *addr = gq + ((size_t)(oz + lz) * Gd.PY + (oy + ly)) * Gd.PX + (ox + lx);
+            const G v = S.g[hi];
+            const bool pending = (S.pend[w] >> b) & 1u;
+            red_min(addr, W::enc(v, pending));
+            if (!pending && ((S.ldd[w] >> b) & 1u)) cas_word(addr, W::enc(v, true), W::enc(v, false));
         }
     }
-    for (int w = tid; w < C::NCW; w += NT) {
-        u32 bits = S.chg[w];
-        while (bits) {
-            const int b = __ffs(bits) - 1;
-            bits &= bits - 1;
-            const int i = w * 32 + b;
+#pragma unroll
+    for (int k = 0; k < NLD; ++k) {
+        const int i = tid + k * NT;
+        if (i < C::HC && ((S.chg[i >> 5] >> (i & 31)) & 1u)) {
             const int hx = i % C::HX, hy = (i / C::HX) % C::HY, hz = i / (C::HX * C::HY);
             const int x = ox + hx - 1, y = oy + hy - 1, z = oz + hz - C::ZH;
-            red_min(gq + ((size_t)z * Gd.PY + y) * Gd.PX + x, S.g[i]);
-        }
-    }
-    __syncthreads();
-    if (tid == 0) __threadfence(); // one cumulative fence: every value above is visible before any dirty bit
-    __syncthreads();
-    // B: dirty bits of improved halo cells (in the neighbour tiles) and of our own leftovers
-    for (int w = tid; w < C::NCW; w += NT) {
-        u32 bits = S.chg[w];
-        while (bits) {
-            const int b = __ffs(bits) - 1;
-            bits &= bits - 1;
-            const int i = w * 32 + b;
-            const int hx = i % C::HX, hy = (i / C::HX) % C::HY, hz = i / (C::HX * C::HY);
+            const G v = S.g[i];
+            red_min(gq + ((size_t)z * Gd.PY + y) * Gd.PX + x, W::enc(v, true));
             const int sx = hx == 0 ? -1 : (hx == C::HX - 1 ? 1 : 0);
             const int sy = hy == 0 ? -1 : (hy == C::HY - 1 ? 1 : 0);
             const int sz = C::ZH ? (hz == 0 ? -1 : (hz == C::HZ - 1 ? 1 : 0)) : 0;
-            const int nlx = hx - 1 - sx * C::TX, nly = hy - 1 - sy * C::TY, nlz = hz - C::ZH - sz * C::TZ;
-            const int cv = (nlz * C::TY + nly) * C::TX + nlx;
-            const u32 ngt = q * Gd.ntiles + (u32)(((ttz + sz) * Gd.nty + (tty + sy)) * Gd.ntx + (ttx + sx));
-            atomicOr(A.dirty + (size_t)ngt * C::NPW + (cv >> 5), 1u << (cv & 31));
-            const double hv = use_h ? heuristic_lo(ox + hx - 1 - gx, oy + hy - 1 - gy, oz + hz - C::ZH - gz, A.he, A.hm) : 0.0;
-            atomicMin(&S.nbrmin[(sz + 1) * 9 + (sy + 1) * 3 + (sx + 1)], W::key(S.g[i], hv));
+            const double hv = use_h ? heuristic_lo(x - gx, y - gy, z - gz, A.he, A.hm) : 0.0;
+            atomicMin(&S.nbrmin[(sz + 1) * 9 + (sy + 1) * 3 + (sx + 1)], W::key(v, hv));
         }
     }
-    if (tid < C::NPW && S.pend[tid]) atomicOr(dq + tid, S.pend[tid]);
+    for (int o = 16; o; o >>= 1) my_edges += __shfl_down_sync(0xFFFFFFFFu, my_edges, o);
+    if (lane == 0 && my_edges) atomicAdd(&S.n_edge, my_edges);
     __syncthreads();
-    if (tid == 0) __threadfence(); // dirty bits visible before the tiles are armed
+    if (tid == 0) fence_gpu(); // cumulative: every word above is visible before a tile is armed
     __syncthreads();
-    // C: arm the tiles that received work
+    // arm the tiles that received work
     if (tid < 27) {
         const u64 k = S.nbrmin[tid];
         if (k != KEY_INF) {
@@ -343,14 +370,13 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     }
     if (tid == 32) {
         if (km_final != KEY_INF) atomicMin(&A.minkey[gt], km_final);
-        atomicAdd(&A.stats[1], 1ull);
-        atomicAdd(&A.stats[2], (u64)S.n_exp);
-        atomicAdd(&A.stats[3], (u64)S.n_edge);
         const long long t_end = clock64();
-        atomicAdd(&A.stats[5], (u64)(t_loaded - t_begin));
-        atomicAdd(&A.stats[6], (u64)(t_looped - t_loaded));
-        atomicAdd(&A.stats[7], (u64)(t_end - t_looped));
-        atomicAdd(&A.stats[12], (u64)S.n_iter);
+        S.stat[1] += 1; S.stat[2] += n_exp;   // per-CTA counters, flushed once at kernel end
+        S.stat[3] += S.n_edge; S.n_edge = 0;
+        S.stat[5] += (u64)(t_loaded - t_begin);
+        S.stat[6] += (u64)(t_looped - t_loaded);
+        S.stat[7] += (u64)(t_end - t_looped);
+        S.stat[12] += n_iter;
     }
     __syncthreads();
 }
@@ -368,6 +394,10 @@ __global__ void __launch_bounds__(NT, 4) k_sssp(const __grid_constant__ SsspArgs
     const u32 ntiles = A.G.ntiles;
     const u32 total = A.nq * ntiles;
     const u32 gstride = gridDim.x * NT;
+    if (tid < 16) S.stat[tid] = 0;
+    if (tid == 0) S.n_edge = 0;
+    if (tid < PMP_MAXM) S.m_need[tid] = 0xFFFFFFFFu; // bit 31 is never free: slot unused
+    __syncthreads();
     if (tid < A.M.k) {
         const int dx = A.M.dx[tid], dy = A.M.dy[tid], dz = A.M.dz[tid];
         S.m_w[tid] = W::wbits(A.M, tid);
@@ -434,7 +464,7 @@ __global__ void __launch_bounds__(NT, 4) k_sssp(const __grid_constant__ SsspArgs
                 } else if (!A.full_field) {
                     const u32 gc = A.goalcell[q];
                     if (gc != 0xFFFFFFFFu) {
-                        const G gg = ld_cg((const G *)A.g + (size_t)q * A.G.pcells + gc);
+                        const G gg = W::dec(ld_cg((const G *)A.g + (size_t)q * A.G.pcells + gc));
                         // every pending key is >= k, keys never decrease along an edge: g[goal] is final
                         if (gg != W::inf() && W::key(gg, 0.0) <= k) st = PMP_ST_REACHED;
                     }
@@ -465,6 +495,8 @@ __global__ void __launch_bounds__(NT, 4) k_sssp(const __grid_constant__ SsspArgs
         grid.sync();
         if (timer) t_wait += globaltimer_ns() - tc;
     }
+    __syncthreads();
+    if (tid < 16 && tid != 0 && tid != 4 && (tid < 8 || tid == 12) && S.stat[tid]) atomicAdd(&A.stats[tid], S.stat[tid]);
     if (timer) {
         A.stats[8] = globaltimer_ns() - t0;
         A.stats[9] = t_scan; A.stats[10] = t_proc; A.stats[11] = t_wait;
@@ -497,13 +529,10 @@ __global__ void k_sssp_init(SsspArgs A) {
         if (!ok) { A.done[q] = PMP_ST_BAD_QUERY; continue; }
         A.done[q] = 0;
         G *gq = (G *)A.g + (size_t)q * Gd.pcells;
-        gq[((size_t)sz * Gd.PY + sy) * Gd.PX + sx] = 0;
+        gq[((size_t)sz * Gd.PY + sy) * Gd.PX + sx] = W::enc((G)0, true);
         const int tx = sx / C::TX, ty = sy / C::TY, tz = sz / C::TZ;
-        const int lx = sx - tx * C::TX, ly = sy - ty * C::TY, lz = sz - tz * C::TZ;
         const u32 t = (u32)((tz * Gd.nty + ty) * Gd.ntx + tx);
         const u32 gt = q * Gd.ntiles + t;
-        const int c = (lz * C::TY + ly) * C::TX + lx;
-        A.dirty[(size_t)gt * C::NPW + (c >> 5)] = 1u << (c & 31);
         const double h = A.use_h ? heuristic_lo(sx - gx, sy - gy, sz - gz, A.he, A.hm) : 0.0;
         const u64 k0 = W::key((G)0, h);
         A.minkey[gt] = k0;
@@ -519,7 +548,7 @@ __global__ void k_sssp_finish(SsspArgs A, double *gcost, int32_t *status) {
         double c = __longlong_as_double(0x7ff0000000000000LL);
         const u32 gc = A.goalcell[q];
         if (st != PMP_ST_BAD_QUERY && gc != 0xFFFFFFFFu) {
-            const G gg = ((const G *)A.g)[(size_t)q * A.G.pcells + gc];
+            const G gg = W::dec(((const G *)A.g)[(size_t)q * A.G.pcells + gc]);
             if (gg != W::inf()) {
                 c = W::to_double(gg);
                 if (st == PMP_ST_EXHAUSTED) st = PMP_ST_REACHED;
@@ -533,8 +562,16 @@ __global__ void k_sssp_finish(SsspArgs A, double *gcost, int32_t *status) {
 }
 
 __global__ void k_field_finalize(u64 *g, size_t n) {
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-        if (g[i] == ~0ull) g[i] = 0x7ff0000000000000ull;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const u64 s = g[i];
+        g[i] = s == WF64::ginf() ? 0x7ff0000000000000ull : WF64::dec(s);
+    }
+}
+__global__ void k_field_finalize_u32(u32 *g, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const u32 s = g[i];
+        g[i] = s == WU32::ginf() ? 0xFFFFFFFFu : WU32::dec(s);
+    }
 }
 
 template <class W>
@@ -553,7 +590,7 @@ __global__ void k_count_settled(GridDev Gd, u32 nq, const typename W::G *g, cons
     }
     u64 local = 0;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < Gd.pcells; i += (size_t)gridDim.x * blockDim.x) {
-        const G v = gq[i];
+        const G v = W::dec(gq[i]);
         if (v == W::inf()) continue;
         if (use_bound) {
             const int x = (int)(i % Gd.PX), y = (int)((i / Gd.PX) % Gd.PY), z = (int)(i / ((size_t)Gd.PX * Gd.PY));
@@ -577,7 +614,7 @@ typedef TileCfg<16, 8, 8, WU32> C3U;
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
-    size_t minkey, dirty, wl0, wl1, qmin0, qmin1, T0, T1, done, goalcell, ctr, stats, total;
+    size_t minkey, wl0, wl1, qmin0, qmin1, T0, T1, done, goalcell, ctr, stats, total;
 };
 
 static WsLayout ws_layout(const pmp_grid *g, int64_t nq) {
@@ -585,7 +622,6 @@ static WsLayout ws_layout(const pmp_grid *g, int64_t nq) {
     const size_t nt = (size_t)nq * g->d.ntiles;
     size_t o = 0;
     L.minkey = o; o = align_up(o + nt * 8, 256);
-    L.dirty = o; o = align_up(o + nt * 32 * 4, 256);
     L.wl0 = o; o = align_up(o + nt * 4, 256);
     L.wl1 = o; o = align_up(o + nt * 4, 256);
     L.qmin0 = o; o = align_up(o + (size_t)nq * 8, 256);
@@ -666,7 +702,6 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
     A.goals = goals_dev;
     A.g = g_dev;
     A.minkey = (u64 *)(ws + L.minkey);
-    A.dirty = (u32 *)(ws + L.dirty);
     A.wl[0] = (u32 *)(ws + L.wl0); A.wl[1] = (u32 *)(ws + L.wl1);
     A.qmin[0] = (u64 *)(ws + L.qmin0); A.qmin[1] = (u64 *)(ws + L.qmin1);
     A.T[0] = (u64 *)(ws + L.T0); A.T[1] = (u64 *)(ws + L.T1);
@@ -688,6 +723,7 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
         A.hm = floor(g->hm_scale);
         A.sub = floor(g->wmin) < 1.0 ? 1.0 : floor(g->wmin);
     }
+    if (P->reserved > 1) A.sub *= (double)P->reserved; // wider in-tile sub-buckets (tuning knob)
     double window = P->window;
     if (!(window > 0.0)) window = (g->d.ndim == 2 ? 24.0 : 10.0) * g->wmin;
     if (P->weight == PMP_W_U32 && window < 1.0) window = 1.0;
@@ -729,7 +765,6 @@ extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
     PMP_CHECK_CUDA(cudaMemsetAsync(g_dev, 0xFF, gsz, s));
     const size_t nt = (size_t)nq * g->d.ntiles;
     PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, nt * 8, s));
-    PMP_CHECK_CUDA(cudaMemsetAsync(A.dirty, 0, nt * 32 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 16 * 8, s));
 
@@ -740,12 +775,13 @@ extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
     return 0;
 }
 
-extern "C" int pmp_field_finalize(void *g_dev, int64_t n_cells, void *stream) {
-    if (!g_dev || n_cells < 0) { pmp_set_error("pmp_field_finalize: bad arguments"); return -1; }
+extern "C" int pmp_field_finalize(void *g_dev, int weight, int64_t n_cells, void *stream) {
+    if (!g_dev || n_cells < 0 || (weight != PMP_W_F64 && weight != PMP_W_U32)) { pmp_set_error("pmp_field_finalize: bad arguments"); return -1; }
     if (n_cells == 0) return 0;
     size_t b = ((size_t)n_cells + 255) / 256;
     if (b > 148 * 32) b = 148 * 32;
-    k_field_finalize<<<(unsigned)b, 256, 0, (cudaStream_t)stream>>>((u64 *)g_dev, (size_t)n_cells);
+    if (weight == PMP_W_F64) k_field_finalize<<<(unsigned)b, 256, 0, (cudaStream_t)stream>>>((u64 *)g_dev, (size_t)n_cells);
+    else k_field_finalize_u32<<<(unsigned)b, 256, 0, (cudaStream_t)stream>>>((u32 *)g_dev, (size_t)n_cells);
     PMP_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -800,17 +836,17 @@ __global__ void k_slab_merge(SsspArgs A, int z, const typename C::G *plane, int 
     u64 local_min = KEY_INF;
     u32 improved = 0;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        const G v = plane[i];
-        if (v == W::inf() || v >= gz[i]) continue;
+        const G sw = plane[i];
+        if (sw == W::ginf()) continue;
+        const G v = W::dec(sw);
+        if (v >= W::dec(gz[i])) continue;
         const int x = (int)(i % Gd.PX), y = (int)(i / Gd.PX);
         if (cell_blocked(Gd, x, y, z)) continue;
-        gz[i] = v;
+        gz[i] = W::enc(v, mark != 0);
         ++improved;
         if (!mark) continue;
         const int tx = x / C::TX, ty = y / C::TY, tz = z / C::TZ;
-        const int c = ((z - tz * C::TZ) * C::TY + (y - ty * C::TY)) * C::TX + (x - tx * C::TX);
         const u32 t = (u32)((tz * Gd.nty + ty) * Gd.ntx + tx);
-        atomicOr(A.dirty + (size_t)t * C::NPW + (c >> 5), 1u << (c & 31));
         const u64 k = W::key(v, 0.0);
         atomicMin(&A.minkey[t], k);
         local_min = k < local_min ? k : local_min;
@@ -845,7 +881,6 @@ extern "C" int pmp_slab_begin(pmp_grid *g, const pmp_sssp_params *P, const int32
     fill_args(g, &Q, 1, start_dev, nullptr, g_dev, ws_dev, L, A);
     PMP_CHECK_CUDA(cudaMemsetAsync(g_dev, 0xFF, (size_t)g->d.pcells * (Q.weight == PMP_W_F64 ? 8 : 4), s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, (size_t)g->d.ntiles * 8, s));
-    PMP_CHECK_CUDA(cudaMemsetAsync(A.dirty, 0, (size_t)g->d.ntiles * 32 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 16 * 8, s));
     if (start_dev) return dispatch_sssp(g, Q.weight, A, nullptr, nullptr, s, 1);

@@ -82,7 +82,8 @@ def sssp(ws, algo, heuristic=0, full_field=False, window=0.0, max_rounds=0, have
     """Launch the search for the queries already uploaded into ws.starts / ws.goals."""
     dg = ws.dg
     P = SsspParams(algo=algo, heuristic=heuristic, weight=ws.weight, full_field=1 if full_field else 0,
-                   window=window or default_window(dg.ndim), max_rounds=max_rounds, reserved=0)
+                   window=window or default_window(dg.ndim), max_rounds=max_rounds,
+                   reserved=int(os.environ.get("PMP_B200_SUB", "0") or 0))
     goals_ptr = ws.goals.data_ptr() if have_goals else None
     _lib.check(dg.L.pmp_sssp(dg.handle, ctypes.byref(P), ws.nq, ws.starts.data_ptr(), goals_ptr,
                              ws.g.data_ptr(), ws.ws.data_ptr(), ws.ws_bytes, ws.gcost.data_ptr(),
@@ -130,10 +131,11 @@ def field_to_numpy(ws, q=0):
     dg = ws.dg
     t = dg.torch
     PX, PY, PZ = dg.padded
-    raw = ws.g[q]
+    raw = ws.g[q].clone()
+    _lib.check(dg.L.pmp_field_finalize(raw.data_ptr(), ws.weight, raw.numel(), dg.stream()),
+               "pmp_field_finalize")
     if ws.weight == W_F64:
-        bits = raw.view(t.int64)
-        f = t.where(bits == -1, t.full_like(raw, float("inf")), raw)
+        f = raw
     else:
         f = raw.to(t.float64)
         f = t.where(raw == -1, t.full_like(f, float("inf")), f)

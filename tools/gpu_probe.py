@@ -64,6 +64,14 @@ for cls in (pmp.AStar3D, pmp.Dijkstra3D):
         (c, path, ex), ms = t_ms(p.plan, 2)
         print(f"3D {m}^3 {cls.__name__} window={w}: cost {c!r} len {len(path)} {ms:.1f} ms {fmt(p.stats)}", flush=True)
 os.environ["PMP_B200_WINDOW"] = ""
+for sub in (2, 4):
+    os.environ["PMP_B200_SUB"] = str(sub)
+    res, ms = t_ms(lambda: pmp.plan_batch(e2, starts, goals, algo="dijkstra", want_paths=False), 2)
+    print(f"2D batch64 sub={sub}: {ms:.1f} ms  {fmt(res.stats)}", flush=True)
+    p = pmp.Dijkstra3D((1, 1, 1), (m - 2, m - 2, m - 2), e3)
+    (c, path, ex), ms = t_ms(p.plan, 2)
+    print(f"3D Dijkstra3D sub={sub}: {ms:.1f} ms {fmt(p.stats)}", flush=True)
+os.environ["PMP_B200_SUB"] = ""
 for wt in ("f64", "u32"):
     e3.motions = [mm for mm in e3.motions if mm.g == 1] if wt == "u32" else e3.motions
     (wsst), ms = t_ms(lambda: pmp.cost_field(e3, (1, 1, 1), weight=wt, to_host=False), 2)

@@ -15,7 +15,7 @@ if case == "field3d":
     torch.cuda.synchronize()
     print("stats", st.cpu().numpy()[:13].tolist())
 else:
-    occ, starts, goals = workloads.random2d(n, nq=32)
+    occ, starts, goals = workloads.random2d(n, nq=int(sys.argv[3]) if len(sys.argv) > 3 else 32)
     env = pmp.Grid(n, n); env.update(occ)
     for _ in range(2):
         res = pmp.plan_batch(env, starts, goals, want_paths=False)
