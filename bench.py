@@ -1,0 +1,404 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of python_motion_planning_b200 ("Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c3|c5|c2] [--impl reference]
+
+One "step" is one pass of the hot path over one batch of synthetic input:
+  c4 (default)  single-query A* on an n^3 26-connected voxel grid with random boxes
+                (BASELINE.json configs[3]; n = 512), start (1,1,1) -> goal (n-2,n-2,n-2)
+  c3            batched Dijkstra, 1024^2 8-connected, 30 % obstacles (configs[2]; --queries)
+  c5            full cost-to-go field, 6-connected unit weights, u32 (configs[4], single GPU size --n)
+  c2            examples/3d_example.py-sized grid (26x20x16), A*, one query per step
+Metric: edge relaxations / s = |motions| * N_settled / t, in GTEPS.
+With N > 1 ranks (torchrun) every rank runs the same workload on its own GPU with its own
+queries -- independent queries shard with no communication ("weak" scaling); the slab-decomposed
+single field has its own driver (python_motion_planning_b200/slab.py, tools/run_slab.py).
+
+`--impl reference` times the CPU restatement of the reference (oracle/, pthreads over queries,
+all host threads) on a bounded sample of the same workload; rank 0 only.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ALG_BYTES = {"f64": 16.125, "u32": 8.125}   # read g + write g + 1 occupancy bit
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# workloads
+# ------------------------------------------------------------------------------------------------
+def build_workload(args, rank, torch, pmp, workloads):
+    """returns dict(env, run(step) -> (edges, settled, algorithmic bytes), e2e(step), meta)"""
+    from python_motion_planning_b200 import engine, _lib
+    from python_motion_planning_b200.environment import motion_table
+    wl = args.workload
+    if wl in ("c4", "c2"):
+        if wl == "c4":
+            n = args.n or 512
+            occ = workloads.boxes3d(n, seed=0)
+            dims = (n, n, n)
+            start = (1, 1, 1)
+            # rank r plans towards its own goal corner region (independent queries per GPU)
+            goals = [(n - 2, n - 2, n - 2), (n - 2, n - 2, 1), (n - 2, 1, n - 2), (1, n - 2, n - 2),
+                     (n - 2, 1, 1), (1, n - 2, 1), (1, 1, n - 2), (n // 2, n - 2, n - 2)]
+            goal = goals[rank % len(goals)]
+            occ[goal[0] - 1:goal[0] + 2, goal[1] - 1:goal[1] + 2, goal[2] - 1:goal[2] + 2] = False
+            workloads.seal(occ)
+            name = f"c4: single-query A* (euclidean), {n}^3 26-connected voxel grid, random boxes"
+        else:
+            occ, dims = workloads.door3d()
+            start, goal = (1, 1, 1), (24, 18, 14)
+            name = "c2: examples/3d_example.py defaults, Grid3D(26,20,16) 'door', A*"
+        env = pmp.Grid3D(*dims, walls=False)
+        host_occ = torch.from_numpy(occ.view(np.uint8)).pin_memory()
+        env.update(host_occ)
+        dg = env.device_grid()
+        dg.set_motions(*motion_table(env, 3))
+        ws = engine.get_workspace(dg, 1, _lib.W_F64)
+        K = 26
+        path_cap = int(min(dg.pcells, 6 * sum(dims) + 4096))
+
+        def run(step):
+            engine.upload_queries(ws, [start], [goal], 3)
+            engine.sssp(ws, _lib.ASTAR, 0)
+            engine.extract_paths(ws, path_cap)
+            return 4   # my kernel launches: init, k_sssp, finish, extract
+
+        def account():
+            settled = int(engine.count_settled(ws, bounded=True).sum().item())
+            return settled * K, settled, settled * ALG_BYTES["f64"], float(ws.cost[0].item())
+
+        def e2e(step):
+            env.update(host_occ)                      # H2D of the occupancy from pinned memory
+            cost, path, expand = pmp.AStar3D(start, goal, env).plan()   # H2D query, D2H cost + path
+            return cost, host_occ.numel() + 24, 32 + 4 * len(path)
+
+        return dict(run=run, account=account, e2e=e2e, name=name, dtype="f64", queries=1,
+                    cfg={"grid": list(dims), "connectivity": 26, "heuristic": "euclidean",
+                         "free_cells": int((~occ).sum())}, occ=occ, start=start, goal=goal)
+    if wl == "c3":
+        n = args.n or 1024
+        nq = args.queries or 4096
+        occ, starts, goals = workloads.random2d(n, nq=nq, seed=rank * 2)
+        env = pmp.Grid(n, n)
+        env.update(occ)
+        dg = env.device_grid()
+        dg.set_motions(*motion_table(env, 2))
+        ws = engine.get_workspace(dg, nq, _lib.W_F64)
+        path_cap = int(min(dg.pcells, 8 * n + 4096))
+
+        def run(step):
+            engine.upload_queries(ws, starts, goals, 2)
+            engine.sssp(ws, _lib.DIJKSTRA, 0)
+            engine.extract_paths(ws, path_cap)
+            return 4
+
+        def account():
+            settled = int(engine.count_settled(ws, bounded=True, use_h=False).sum().item())
+            return settled * 8, settled, settled * ALG_BYTES["f64"], float(np.nanmean(ws.cost.cpu().numpy()[np.isfinite(ws.cost.cpu().numpy())]))
+
+        def e2e(step):
+            res = pmp.plan_batch(env, starts, goals, algo="dijkstra", want_paths=True)
+            return float(np.isfinite(res.costs).sum()), res.h2d_bytes, res.d2h_bytes
+
+        return dict(run=run, account=account, e2e=e2e, dtype="f64", queries=nq,
+                    name=f"c3: batched Dijkstra, {nq} queries, {n}^2 8-connected, 30% random obstacles",
+                    cfg={"grid": [n, n], "connectivity": 8, "queries": nq}, occ=occ, starts=starts, goals=goals)
+    if wl == "c5":
+        n = args.n or 768
+        blk, _ = workloads.replicated_boxes3d(base=128, reps=max(1, n // 128))
+        occ = workloads.replicated_slab(blk, (n, n, n), 0, n)
+        env = pmp.Grid3D(n, n, n, walls=False)
+        env.motions = [m for m in env.motions if m.g == 1]
+        env.update(occ)
+        dg = env.device_grid()
+        dg.set_motions(*motion_table(env, 3))
+        ws = engine.get_workspace(dg, 1, _lib.W_U32)
+        src = (1, 1, 1)
+
+        def run(step):
+            engine.upload_queries(ws, [src], None, 3)
+            engine.sssp(ws, _lib.DIJKSTRA, 0, full_field=True, have_goals=False)
+            return 3
+
+        def account():
+            settled = int(engine.count_settled(ws, bounded=False).sum().item())
+            return settled * 6, settled, settled * ALG_BYTES["u32"], float(settled)
+
+        def e2e(step):
+            wsx, st = pmp.cost_field(env, src, weight="u32", to_host=False)
+            far = int(wsx.g[0][-1].item())    # D2H of one field word
+            return float(far), 12, 4
+
+        return dict(run=run, account=account, e2e=e2e, dtype="u32", queries=1,
+                    name=f"c5: full cost-to-go field, {n}^3 6-connected unit weights (u32), single GPU",
+                    cfg={"grid": [n, n, n], "connectivity": 6}, occ=occ, start=src)
+    raise SystemExit(f"unknown workload {wl}")
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (C restatement of the reference) on the host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_sample(args, workloads, budget_s=12.0):
+    """bounded sample of the workload on all host threads; returns dict for the JSON line"""
+    from oracle import oracle
+    threads = oracle.max_threads()
+    wl = args.workload
+    t0 = time.perf_counter()
+    if wl in ("c4", "c2"):
+        if wl == "c4":
+            n = min(args.n or 512, args.cpu_n or 192)
+            occ = workloads.boxes3d(n, seed=0)
+            sample = f"{threads} A* queries (one per host thread) on a {n}^3 copy of the workload, start (1,1,1), goals on the far faces"
+            rng = np.random.default_rng(5)
+            free_far = np.argwhere(~occ[n // 2:, n // 2:, n // 2:]) + n // 2
+            goals = free_far[rng.integers(0, len(free_far), size=threads)]
+            starts = np.tile(np.array([[1, 1, 1]]), (threads, 1))
+        else:
+            occ, _ = workloads.door3d()
+            sample = f"{threads * 8} repeats of the c2 query, one per host thread"
+            starts = np.tile(np.array([[1, 1, 1]]), (threads * 8, 1))
+            goals = np.tile(np.array([[24, 18, 14]]), (threads * 8, 1))
+        K, algo = 26, oracle.ASTAR
+    elif wl == "c3":
+        n = args.n or 1024
+        occ, starts, goals = workloads.random2d(n, nq=max(threads, 16), seed=0)
+        sample = f"{len(starts)} of the Dijkstra queries on the {n}^2 grid, one per host thread"
+        K, algo = 8, oracle.DIJKSTRA
+    else:
+        n = min(args.n or 768, 128)
+        blk, _ = workloads.replicated_boxes3d(base=128, reps=1)
+        occ = workloads.replicated_slab(blk, (n, n, n), 0, n)
+        starts = np.tile(np.array([[1, 1, 1]]), (threads, 1))
+        goals = np.zeros((threads, 3), dtype=np.int32)      # an obstacle: runs to exhaustion
+        sample = f"{threads} full fields (Dijkstra3D to exhaustion, 6 motions) on the 128^3 block, one per host thread"
+        K, algo = 6, oracle.DIJKSTRA
+    motions = oracle.MOTIONS_3D if occ.ndim == 3 else oracle.MOTIONS_2D
+    mg = oracle.motion_costs(motions)
+    if K == 6:
+        keep = mg == 1.0
+        motions, mg = motions[keep], mg[keep]
+    t_build = time.perf_counter() - t0
+    reps, edges, t_total = 0, 0, 0.0
+    while True:
+        t1 = time.perf_counter()
+        cost, nexp, plen, flags = oracle.plan_batch(occ, starts, goals, algo=algo, motions=motions,
+                                                    motion_g=mg, n_threads=threads)
+        t_total += time.perf_counter() - t1
+        edges += int(nexp.sum()) * K
+        reps += 1
+        if t_total > budget_s or reps >= 64:
+            break
+    return {"value": edges / t_total / 1e9, "unit": "GTEPS", "cores": threads, "kind": "port",
+            "sample": sample + f"; {reps} repetition(s), {t_total:.1f} s",
+            "queries_per_s": reps * len(starts) / t_total, "seconds": t_total, "reps": reps,
+            "edges_per_rep": edges // reps, "queries_per_rep": len(starts)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c4", choices=["c4", "c3", "c5", "c2"])
+    ap.add_argument("--n", type=int, default=0, help="grid edge (default: the BASELINE.json size)")
+    ap.add_argument("--queries", type=int, default=0)
+    ap.add_argument("--cpu-n", type=int, default=0, help="grid edge of the CPU sample (c4)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    from python_motion_planning_b200 import workloads
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        ts = []
+        out = None
+        for i in range(args.warmup + args.steps):
+            out = cpu_sample(args, workloads, budget_s=0.0)     # one repetition per step
+            if i >= args.warmup:
+                ts.append(out)
+        secs = sum(o["seconds"] for o in ts)
+        edges = sum(o["edges_per_rep"] for o in ts)
+        val = edges / secs / 1e9
+        line = {"impl": "reference", "metric": "edge relaxations/s", "value": val, "unit": "GTEPS",
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": secs / max(len(ts), 1) * 1e3, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64" if args.workload != "c5" else "u32",
+                "data": "synthetic", "config": {"workload": args.workload, "sample": out["sample"]},
+                "cpu_baseline": {"value": val, "unit": "GTEPS", "cores": out["cores"], "kind": "port",
+                                 "sample": out["sample"]},
+                "queries_per_s": sum(o["queries_per_rep"] for o in ts) / secs,
+                "e2e": {"value": val, "unit": "GTEPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return
+
+    import torch
+    import python_motion_planning_b200 as pmp
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    W = build_workload(args, rank, torch, pmp, workloads)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident leg: `value` ----
+    for i in range(args.warmup):
+        W["run"](i)
+    torch.cuda.synchronize()
+    edges, settled, abytes, check = W["account"]()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    evs, launches = [], 0
+    t_wall0 = time.perf_counter()
+    for i in range(args.steps):
+        flush.fill_(i & 0xFF)                      # L2 flush between timed iterations
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        launches += W["run"](i)
+        e1.record()
+        evs.append((e0, e1))
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop()
+    ms = [a.elapsed_time(b) for a, b in evs]
+    t_dev = sum(ms) / 1e3
+    # ---- end-to-end leg through the public API with host buffers ----
+    for i in range(2):
+        W["e2e"](i)
+    barrier()
+    t0 = time.perf_counter()
+    h2d = d2h = 0
+    for i in range(args.steps):
+        _, a, b = W["e2e"](i)
+        h2d, d2h = a, b
+    barrier()
+    t_e2e = time.perf_counter() - t0
+
+    tt = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device="cuda")
+    ee = torch.tensor([float(edges), float(settled), float(abytes)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)      # max over ranks
+        dist.all_reduce(ee, op=dist.ReduceOp.SUM)      # whole-job work
+    t_dev_max, t_e2e_max = float(tt[0]), float(tt[1])
+    edges_all, settled_all, abytes_all = float(ee[0]), float(ee[1]), float(ee[2])
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak()
+    value = edges_all * args.steps / t_dev_max / 1e9
+    achieved = abytes / (t_dev / args.steps) / 1e9          # this rank's dominant kernel (k_sssp)
+    line = {
+        "metric": "edge relaxations/s", "value": value, "unit": "GTEPS", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_dev_max / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": W["dtype"],
+        "data": "synthetic",
+        "config": dict(W["cfg"], workload=W["name"], l2="flushed between timed steps (256 MiB write); field > L2",
+                       parallelism=f"independent queries x{world}", settled_cells_per_step=settled,
+                       check_value=check),
+        "queries_per_s": W["queries"] * world * args.steps / t_dev_max,
+        "clocks": clocks,
+        "e2e": {"value": edges_all * args.steps / t_e2e_max / 1e9, "unit": "GTEPS",
+                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": t_e2e_max / args.steps * 1e3,
+                "queries_per_s": W["queries"] * world * args.steps / t_e2e_max},
+        "gpu_launches": launches,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "kernel": "k_sssp (+init/finish/extract, ~1% of the step)",
+                     "algorithmic_bytes_per_step": abytes},
+    }
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof):
+        try:
+            line["roofline"]["traffic"] = json.load(open(prof)).get(args.workload)
+        except Exception:
+            pass
+    if not args.no_cpu and world == 1:
+        line["cpu_baseline"] = cpu_sample(args, workloads)
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -77,3 +77,21 @@ def replicated_slab(blk, shape, z0, z1):
     plane[:, :, zs == 0] = True
     plane[:, :, zs == shape[2] - 1] = True
     return plane
+
+
+def door3d(dims=(26, 20, 16), door_size=2, start=(1, 1, 1), goal=None, bubble=1):
+    """config 2: the default scene of examples/3d_example.py -- two rooms split by a wall at
+    x = X//2 with a door_size^2 door at the centre (examples/scenarios.py:28-47), shell walls,
+    radius-1 bubbles carved at start and goal (3d_example.py:84-86).  Returns (occ, dims)."""
+    X, Y, Z = dims
+    goal = goal or (X - 2, Y - 2, Z - 2)
+    occ = seal(np.zeros(dims, dtype=bool))
+    x0 = X // 2
+    occ[x0, 1:Y - 1, 1:Z - 1] = True
+    ym, zm = Y // 2, Z // 2
+    lo, hi = -(door_size // 2), door_size - (door_size // 2)
+    occ[x0, ym + lo:ym + hi, zm + lo:zm + hi] = False
+    for c in (start, goal):
+        sl = tuple(slice(max(1, c[i] - bubble), min(dims[i] - 1, c[i] + bubble + 1)) for i in range(3))
+        occ[sl] = False
+    return occ, dims
