@@ -135,7 +135,7 @@ def build_workload(args, rank, torch, pmp, workloads):
             cost, path, expand = pmp.AStar3D(start, goal, env).plan()   # H2D query, D2H cost + path
             return cost, host_occ.numel() + 24, 32 + 4 * len(path)
 
-        return dict(run=run, account=account, e2e=e2e, name=name, dtype="f64", queries=1,
+        return dict(run=run, account=account, e2e=e2e, name=name, dtype="f64", queries=1, stats=lambda: ws.stats.cpu().numpy(),
                     cfg={"grid": list(dims), "connectivity": 26, "heuristic": "euclidean",
                          "free_cells": int((~occ).sum())}, occ=occ, start=start, goal=goal)
     if wl == "c3":
@@ -163,7 +163,7 @@ def build_workload(args, rank, torch, pmp, workloads):
             res = pmp.plan_batch(env, starts, goals, algo="dijkstra", want_paths=True)
             return float(np.isfinite(res.costs).sum()), res.h2d_bytes, res.d2h_bytes
 
-        return dict(run=run, account=account, e2e=e2e, dtype="f64", queries=nq,
+        return dict(run=run, account=account, e2e=e2e, dtype="f64", queries=nq, stats=lambda: ws.stats.cpu().numpy(),
                     name=f"c3: batched Dijkstra, {nq} queries, {n}^2 8-connected, 30% random obstacles",
                     cfg={"grid": [n, n], "connectivity": 8, "queries": nq}, occ=occ, starts=starts, goals=goals)
     if wl == "c5":
@@ -192,7 +192,7 @@ def build_workload(args, rank, torch, pmp, workloads):
             far = int(wsx.g[0][-1].item())    # D2H of one field word
             return float(far), 12, 4
 
-        return dict(run=run, account=account, e2e=e2e, dtype="u32", queries=1,
+        return dict(run=run, account=account, e2e=e2e, dtype="u32", queries=1, stats=lambda: ws.stats.cpu().numpy(),
                     name=f"c5: full cost-to-go field, {n}^3 6-connected unit weights (u32), single GPU",
                     cfg={"grid": [n, n, n], "connectivity": 6}, occ=occ, start=src)
     raise SystemExit(f"unknown workload {wl}")
@@ -364,6 +364,7 @@ def main():
             dist.destroy_process_group()
         return
 
+    st = [int(v) for v in W["stats"]().tolist()] if "stats" in W else None
     peak, peak_src = measured_peak()
     value = edges_all * args.steps / t_dev_max / 1e9
     achieved = abytes / (t_dev / args.steps) / 1e9          # this rank's dominant kernel (k_sssp)
@@ -387,6 +388,14 @@ def main():
                      "kernel": "k_sssp (+init/finish/extract, ~1% of the step)",
                      "algorithmic_bytes_per_step": abytes},
     }
+    if st:
+        mhz = (clocks.get("sm_mhz") or 1965.0)
+        nt = max(st[1], 1)
+        line["kernel_stats"] = {
+            "rounds": st[0], "tile_activations": st[1], "cells_expanded": st[2], "edges_relaxed": st[3],
+            "worklist_max": st[4], "sub_iterations": st[12],
+            "us_per_activation": {"load": st[5] / nt / mhz, "settle": st[6] / nt / mhz, "publish": st[7] / nt / mhz},
+            "kernel_ms": st[8] / 1e6, "cta0_ms": {"scan": st[9] / 1e6, "process": st[10] / 1e6, "barrier_wait": st[11] / 1e6}}
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):
         try:

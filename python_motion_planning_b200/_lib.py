@@ -8,7 +8,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpmp_b200.so")
+# PMP_B200_LIB selects an alternative build of the same library (tuning experiments)
+LIB_PATH = os.environ.get("PMP_B200_LIB") or os.path.join(_HERE, "libpmp_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 ASTAR, DIJKSTRA, GBFS = 0, 1, 2

@@ -22,12 +22,18 @@
 //   * A-star = the same with key g + h (h an admissible round-down heuristic), pruning by the best
 //     g[goal] seen, and termination once no pending key is below g[goal].
 #include <cooperative_groups.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
 
 #include "pmp_common.cuh"
 
 namespace cg = cooperative_groups;
 
 #define NT 256
+#ifndef PMP_MINB
+#define PMP_MINB 2 // resident CTAs per SM the register budget is sized for (128 registers: no spills)
+#endif
 
 template <int TX_, int TY_, int TZ_, typename W_>
 struct TileCfg {
@@ -37,38 +43,64 @@ struct TileCfg {
     static constexpr int ZH = TZ_ > 1 ? 1 : 0; // halo width in z (0 for 2D)
     static constexpr int HX = TX_ + 2, HY = TY_ + 2, HZ = TZ_ + 2 * ZH;
     static constexpr int NCELL = TX_ * TY_ * TZ_;
-    static constexpr int NPW = NCELL / 32; // words of the pending mask
+    static constexpr int CPT = NCELL / NT;     // cells owned by one thread
     static constexpr int HC = HX * HY * HZ;
     static constexpr int NCW = (HC + 31) / 32; // words of the changed mask
     static constexpr int NROWS = HY * HZ;
-    static_assert(NCELL == 1024, "tiles hold 1024 cells (dirty mask = 32 words)");
+    static_assert(NCELL == 1024 && CPT == 4, "tiles hold 1024 cells, 4 per thread");
+    static_assert((TZ_ == 1 && TX_ == 32 && TY_ == 32) || (TX_ == 16 && TY_ == 8 && TZ_ == 8), "ownership map");
+    // Cells owned by thread `tid` (j = 0..3).  The map is skewed so that the cells of any
+    // axis-aligned line / plane of the tile are spread evenly over the 8 warps: every warp
+    // expands the frontier cells its own lanes own, so a wavefront sweeping the tile keeps all
+    // warps equally busy.
+    __device__ static inline void owned(int tid, int j, int &lx, int &ly, int &lz) {
+        if (TZ_ == 1) {
+            const int tlx = tid & 31, w = tid >> 5;
+            lx = (tlx + 8 * j) & 31;
+            ly = ((w + (tlx >> 2)) & 7) + 8 * j;
+            lz = 0;
+        } else {
+            const int tlx = tid & 15, tly = (tid >> 4) & 7, tlz = tid >> 7;
+            lx = (tlx + 4 * j) & 15;
+            ly = (tly + 2 * j) & 7;
+            lz = 2 * j + (tlz ^ (tly & 1));
+        }
+    }
+    // lanes of a warp that work on one cell (one lane per canonical direction) and cells
+    // expanded per warp step
+    static constexpr int DPL = TZ_ == 1 ? 16 : 32;
+    static constexpr int NG = 32 / DPL;
+    __device__ static inline int own_hi(int tid, int j) {
+        int lx, ly, lz;
+        owned(tid, j, lx, ly, lz);
+        return ((lz + ZH) * HY + (ly + 1)) * HX + (lx + 1);
+    }
+    __device__ static inline int halo_index(int lx, int ly, int lz) {
+        return ((lz + ZH) * HY + (ly + 1)) * HX + (lx + 1);
+    }
 };
 
 template <class C>
 struct TileSmem {
-    typename C::G g[C::HC]; // cost of tile + halo
+    typename C::G g[C::HC]; // cost words of tile + halo in the global (value << 1 | clean) format
     u64 rows[C::NROWS];     // occupancy bits of the TX+2 cells of each (y,z) row
     u64 nbrmin[27];         // smallest key pushed into each neighbour tile
-    u64 kmin_rest[3];       // min key of pending cells outside the current sub-bucket
-    u64 T, U;
-    u64 m_w[PMP_MAXM];      // motion table staged once per CTA: cost (f64 bits or integer),
-    u32 m_need[PMP_MAXM];   //   neighbourhood cells that must be free,
-    int m_off[PMP_MAXM];    //   (dx+1) | (dy+1)<<2 | (dz+1)<<4 | halo'd smem index delta << 8
-    u32 count[3];
-    u32 pend[C::NPW];
-    u32 ldd[C::NPW];        // cells that were pending when the tile was loaded
-    u32 chgi[C::NPW];       // interior cells whose value changed (by cell index)
-    u32 chg[C::NCW];        // halo cells whose value changed (by halo'd index)
-    u32 fmask[C::NCELL];    // free cells of the 3x3x3 neighbourhood of each compacted frontier cell
+    u64 kmin[2];            // min key of the pending cells (computed on empty sub-iterations)
+    u64 T, U, k0;
+    u32 chg[C::NCW];        // cells (tile + halo, by halo'd index) lowered during this activation
     u64 stat[16];           // per-CTA counters (flushed at kernel end)
-    u32 item, n_edge;
+    u64 tm[6];              // CTA 0's phase timers: t0, scan, proc, wait, ta/tb scratch
+    u32 item, n_edge, n_exp;
     u32 s_live, s_wl_base;
-    uint16_t list[C::NCELL];
 };
 
 struct SsspArgs {
     GridDev G;
-    Motions M;
+    // env.motions by canonical direction d = (dz+1)*9 + (dy+1)*3 + (dx+1): edge cost (f64 bits or
+    // integer) and the cells of the source's 3x3x3 neighbourhood that must be free (isCollision);
+    // directions not in the motion table have need = all-ones (never satisfied).
+    u64 wdir[27];
+    u32 need[27];
     u32 nq;
     const int32_t *starts, *goals;
     void *g;
@@ -85,15 +117,8 @@ struct SsspArgs {
     int use_h, full_field, max_rounds;
 };
 
-__device__ static inline bool smem_min(u64 *p, u64 v) {
-    u64 old = *(volatile u64 *)p;
-    while (v < old) {
-        const u64 assumed = old;
-        old = atomicCAS(p, assumed, v);
-        if (old == assumed) return true;
-    }
-    return false;
-}
+// shared-memory atomic min that reports whether it lowered the word
+__device__ static inline bool smem_min(u64 *p, u64 v) { return atomicMin((unsigned long long *)p, (unsigned long long)v) > v; }
 __device__ static inline bool smem_min(u32 *p, u32 v) { return atomicMin(p, v) > v; }
 
 __device__ static inline u64 globaltimer_ns() {
@@ -113,16 +138,25 @@ __device__ static inline u64 warp_min_u64(u64 v) {
 
 // ---------------------------------------------------------------------------------------------
 // one tile activation
+//
+// Owner-computes push.  Every thread owns 4 cells of the tile and keeps their search state in
+// registers: the halo'd index, the free-mask of the 3x3(x3) neighbourhood, the heuristic and
+// `gprop`, the value it last propagated (a cell is pending iff its value is below gprop).  One
+// sub-iteration: read the own cells, expand those that are pending with key < B (loop over the
+// motions: read the target, compare, shared-memory atomic min for the few that improve), one
+// barrier-with-vote.  B advances by the smallest edge cost per sub-iteration, or jumps to the
+// smallest pending key when a sub-iteration expanded nothing.  A cell lowered by another thread
+// after its owner read it is simply seen in the next sub-iteration: no update can be lost, and
+// the fixed point does not depend on the order.
 // ---------------------------------------------------------------------------------------------
 template <class C>
 __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, TileSmem<C> &S) {
     typedef typename C::W W;
     typedef typename C::G G;
-    constexpr int NW = NT / 32;             // warps per CTA
-    constexpr int WPW = C::NPW / NW;        // pending words per warp
+    constexpr int CPT = C::CPT;
     constexpr int NLD = (C::HC + NT - 1) / NT;
     const GridDev &Gd = A.G;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
     const u32 q = gt / Gd.ntiles, t = gt - q * Gd.ntiles;
     const int ttx = t % Gd.ntx, tty = (t / Gd.ntx) % Gd.nty, ttz = t / (Gd.ntx * Gd.nty);
     const int ox = ttx * C::TX, oy = tty * C::TY, oz = ttz * C::TZ;
@@ -133,11 +167,14 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         gx = A.goals[3 * q]; gy = A.goals[3 * q + 1]; gz = Gd.ndim == 3 ? A.goals[3 * q + 2] : 0;
     }
 
-    const long long t_begin = clock64();
+    const u32 t_begin = (u32)clock64();
+    // ---- prologue: the dependent global round trips are spread over different warps ----
     if (tid == 0) {
-        atomicExch(&A.minkey[gt], KEY_INF); // claim: later pushes re-arm the tile
+        S.k0 = atomicExch(&A.minkey[gt], KEY_INF); // claim: later pushes re-arm the tile
         fence_gpu();
+    } else if (tid == 32) {
         S.T = ld_cg(&A.T[cur][q]);
+    } else if (tid == 64) {
         u64 U = KEY_INF;
         const u32 gc = A.full_field ? 0xFFFFFFFFu : A.goalcell[q];
         if (gc != 0xFFFFFFFFu) {
@@ -145,15 +182,19 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
             if (gg != W::inf()) U = W::key(gg, 0.0);
         }
         S.U = U;
-        S.count[0] = S.count[1] = S.count[2] = 0;
-        S.kmin_rest[0] = S.kmin_rest[1] = S.kmin_rest[2] = KEY_INF;
+    } else if (tid == 96) {
+        S.kmin[0] = S.kmin[1] = KEY_INF;
     }
-    if (tid < 27) S.nbrmin[tid] = KEY_INF;
+    if (tid >= 128 && tid < 128 + 27) S.nbrmin[tid - 128] = KEY_INF;
+    if (tid >= NT - C::NROWS) { // occupancy never changes during a search: no ordering needed
+        const int r = tid - (NT - C::NROWS);
+        const int hy = r % C::HY, hz = r / C::HY;
+        S.rows[r] = row_bits(Gd, ox - 1, oy + hy - 1, oz + hz - C::ZH, C::HX);
+    }
     for (int i = tid; i < C::NCW; i += NT) S.chg[i] = 0;
-    if (tid < C::NPW) { S.chgi[tid] = 0; S.pend[tid] = 0; }
-    __syncthreads();
+    __syncthreads(); // the claim is ordered before every load of g below
 
-    // ---- stage g (tile + halo): all loads first, then decode (keeps NLD loads in flight) ----
+    // ---- stage the raw cost words (tile + halo) ----
     {
         G raw[NLD];
 #pragma unroll
@@ -165,178 +206,156 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
             if (i < C::HC && (unsigned)x < (unsigned)Gd.PX && (unsigned)y < (unsigned)Gd.PY && (unsigned)z < (unsigned)Gd.PZ)
                 raw[k] = ld_cg(gq + ((size_t)z * Gd.PY + y) * Gd.PX + x);
         }
-        if (tid < C::NROWS) {
-            const int hy = tid % C::HY, hz = tid / C::HY;
-            S.rows[tid] = row_bits(Gd, ox - 1, oy + hy - 1, oz + hz - C::ZH, C::HX);
-        }
 #pragma unroll
         for (int k = 0; k < NLD; ++k) {
             const int i = tid + k * NT;
-            if (i < C::HC) {
-                const G sw = raw[k];
-                S.g[i] = W::dec(sw);
-                if (!(sw & 1)) { // pending flag: an interior cell that still has to propagate
-                    const int lx = i % C::HX - 1, ly = (i / C::HX) % C::HY - 1, lz = i / (C::HX * C::HY) - C::ZH;
-                    if ((unsigned)lx < (unsigned)C::TX && (unsigned)ly < (unsigned)C::TY && (unsigned)lz < (unsigned)C::TZ) {
-                        const int c = (lz * C::TY + ly) * C::TX + lx;
-                        atomicOr(&S.pend[c >> 5], 1u << (c & 31));
-                    }
-                }
-            }
+            if (i < C::HC) S.g[i] = raw[k];
         }
     }
     __syncthreads();
 
-    const long long t_loaded = clock64();
+    // ---- per-thread state of the owned cells ----
+    u32 F[CPT];
+    G gprop[CPT];
+    double hh[CPT];
+    u32 ldp = 0; // owned cells that were flagged pending in global memory
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+        int lx, ly, lz;
+        C::owned(tid, j, lx, ly, lz);
+        const int hij = C::halo_index(lx, ly, lz);
+        u32 occ27 = 0; // occupancy of the 3x3(x3) neighbourhood from the staged rows
+#pragma unroll
+        for (int dzz = -C::ZH; dzz <= C::ZH; ++dzz)
+#pragma unroll
+            for (int dyy = -1; dyy <= 1; ++dyy) {
+                const u64 r = S.rows[(lz + C::ZH + dzz) * C::HY + (ly + 1 + dyy)];
+                occ27 |= (u32)((r >> lx) & 7ull) << ((dzz + 1) * 9 + (dyy + 1) * 3);
+            }
+        F[j] = ~occ27 & 0x7FFFFFFu;
+        const G sw = S.g[hij];
+        const bool pend = !(sw & 1) ;
+        gprop[j] = pend ? W::inf() : W::dec(sw);
+        if (pend) ldp |= 1u << j;
+        hh[j] = use_h ? heuristic_lo(ox + lx - gx, oy + ly - gy, oz + lz - gz, A.he, A.hm) : 0.0;
+    }
+
+    // direction handled by this lane in the warp-cooperative expansion
+    const int grp = lane / C::DPL, didx = lane % C::DPL;
+    const int dcan = C::TZ == 1 ? (didx < 9 ? 9 + didx : 13) : (didx < 27 ? didx : 13);
+    const u32 my_need = A.need[dcan]; // all-ones for the centre / unused directions
+    const u64 my_w = A.wdir[dcan];
+    const int my_off = ((dcan / 9 - 1) * C::HY + ((dcan / 3) % 3 - 1)) * C::HX + (dcan % 3 - 1);
+
+    const u32 t_loaded = (u32)clock64();
     const u64 T = S.T, U = S.U;
-    const int K = A.M.k;
-    u64 B = 0; // exclusive upper key of the current sub-bucket; first scan only finds the min
+    // exclusive upper key of the current sub-bucket.  The claimed minkey is a lower bound of the
+    // smallest pending key, so the first bucket is usually non-empty.
+    u64 B = 0;
+    if (S.k0 != KEY_INF) {
+        const u64 nb = W::key_add(S.k0, A.sub);
+        B = nb < T ? nb : T;
+    }
     u64 km_final = KEY_INF;
-    u32 n_exp = 0, n_iter = 0, my_edges = 0;
-    for (int it = 0;; ++it) {
-        const int p = it % 3;
-        // ---- scan the pending mask: compact cells with key < B, track the min of the rest ----
-        if (it == 0 && lane < WPW) S.ldd[warp * WPW + lane] = S.pend[warp * WPW + lane];
-        u32 bits[WPW];
-        u32 any = 0;
+    u32 n_exp = 0, n_iter = 0, my_edges = 0, n_empty = 0;
+    for (;;) {
+        G gv[CPT];
 #pragma unroll
-        for (int j = 0; j < WPW; ++j) { bits[j] = S.pend[warp * WPW + j]; any |= bits[j]; }
-        if (any) { // warps without pending cells (most of them) fall through to the barrier
-            u64 lmin = KEY_INF;
-            u32 actm[WPW], F[WPW];
-            bool act[WPW];
+        for (int j = 0; j < CPT; ++j) gv[j] = W::dec(S.g[C::own_hi(tid, j)]);
+        u64 lmin = KEY_INF;
+        int anyact = 0;
 #pragma unroll
-            for (int j = 0; j < WPW; ++j) {
-                act[j] = false;
-                F[j] = 0;
-                if ((bits[j] >> lane) & 1u) {
-                    const int c = (warp * WPW + j) * 32 + lane;
-                    const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
-                    const int hi = ((lz + C::ZH) * C::HY + (ly + 1)) * C::HX + (lx + 1);
-                    const G gv = S.g[hi];
-                    const double h = use_h ? heuristic_lo(ox + lx - gx, oy + ly - gy, oz + lz - gz, A.he, A.hm) : 0.0;
-                    const u64 k = W::key(gv, h);
-                    if (k < B) {
-                        act[j] = true;
-                        u32 occ27 = 0; // occupancy of the 3x3(x3) neighbourhood from the staged rows
+        for (int j = 0; j < CPT; ++j) {
+            bool act = false;
+            if (gv[j] < gprop[j]) { // pending
+                const u64 k = use_h ? W::key(gv[j], hh[j]) : (u64)gv[j];
+                if (k < B) { act = true; gprop[j] = gv[j]; ++n_exp; }
+                else lmin = k < lmin ? k : lmin;
+            }
+            // ---- warp-cooperative expansion: the frontier cells owned by this warp's lanes are
+            // expanded NG at a time, one lane per canonical direction: broadcast the cell from its
+            // owner lane, test the edge, read the target, one compare-and-swap if it improves.
+            u32 m = __ballot_sync(0xFFFFFFFFu, act);
+            anyact |= m != 0;
+            while (m) {
+                int src = -1;
 #pragma unroll
-                        for (int dzz = -C::ZH; dzz <= C::ZH; ++dzz)
-#pragma unroll
-                            for (int dyy = -1; dyy <= 1; ++dyy) {
-                                const u64 r = S.rows[(lz + C::ZH + dzz) * C::HY + (ly + 1 + dyy)];
-                                occ27 |= (u32)((r >> lx) & 7ull) << ((dzz + 1) * 9 + (dyy + 1) * 3);
+                for (int gI = 0; gI < C::NG; ++gI) {
+                    if (m) {
+                        if (gI == grp) src = __ffs(m) - 1;
+                        m &= m - 1;
+                    }
+                }
+                const int s = src < 0 ? 0 : src;
+                const int hj = C::own_hi((tid & ~31) + s, j);
+                const u32 fm = __shfl_sync(0xFFFFFFFFu, F[j], s);
+                const G gu = __shfl_sync(0xFFFFFFFFu, gv[j], s);
+                if (src >= 0 && (fm & my_need) == my_need) { // isCollision: target / face cells free
+                    ++my_edges;
+                    const int vhi = hj + my_off;
+                    const G tvr = S.g[vhi];
+                    const G cand = W::addw(gu, my_w);
+                    if (cand < W::dec(tvr)) {
+                        bool keep = true;
+                        if (U != KEY_INF) { // cannot be on a better path to the goal?
+                            double hv = 0.0;
+                            if (use_h) {
+                                const int hx = vhi % C::HX, hy = (vhi / C::HX) % C::HY, hz = vhi / (C::HX * C::HY);
+                                hv = heuristic_lo(ox + hx - 1 - gx, oy + hy - 1 - gy, oz + hz - C::ZH - gz, A.he, A.hm);
                             }
-                        F[j] = ~occ27 & 0x7FFFFFFu;
-                    } else {
-                        lmin = k < lmin ? k : lmin;
+                            keep = W::key(cand, hv) <= U;
+                        }
+                        if (keep) {
+                            const G want = W::enc(cand, true);
+                            const G old = atomicCAS(&S.g[vhi], tvr, want);
+                            bool won = old == tvr;
+                            if (!won && want < old) won = smem_min(&S.g[vhi], want); // raced with a worse value
+                            if (won) atomicOr(&S.chg[vhi >> 5], 1u << (vhi & 31));
+                        }
                     }
                 }
             }
-            u32 tot = 0;
-#pragma unroll
-            for (int j = 0; j < WPW; ++j) {
-                actm[j] = __ballot_sync(0xFFFFFFFFu, act[j]);
-                tot += __popc(actm[j]);
-            }
-            u32 base = 0;
-            if (lane == 0) {
-                if (tot) base = atomicAdd(&S.count[p], tot);
-#pragma unroll
-                for (int j = 0; j < WPW; ++j)
-                    if (bits[j]) {
-                        const int w = warp * WPW + j;
-                        S.chgi[w] |= bits[j];
-                        if (actm[j]) S.pend[w] = bits[j] & ~actm[j];
-                    }
-            }
-            if (tot) {
-                base = __shfl_sync(0xFFFFFFFFu, base, 0);
-#pragma unroll
-                for (int j = 0; j < WPW; ++j) {
-                    if (act[j]) {
-                        const u32 slot = base + __popc(actm[j] & ((1u << lane) - 1u));
-                        S.list[slot] = (uint16_t)((warp * WPW + j) * 32 + lane);
-                        S.fmask[slot] = F[j];
-                    }
-                    base += __popc(actm[j]);
-                }
-            }
-            if (__any_sync(0xFFFFFFFFu, lmin != KEY_INF)) {
-                lmin = warp_min_u64(lmin);
-                if (lane == 0) atomicMin(&S.kmin_rest[p], lmin);
-            }
         }
-        __syncthreads();
-        const u32 n = S.count[p];
-        const u64 km = S.kmin_rest[p];
-        if (tid == 0) { // recycle the buffer last used two iterations ago
-            const int r = (it + 2) % 3;
-            S.count[r] = 0;
-            S.kmin_rest[r] = KEY_INF;
-        }
-        n_exp += n;
         ++n_iter;
-        if (n == 0) {
-            if (km >= T) { km_final = km; break; }
-            const u64 nb = W::key_add(km, A.sub);
+        if (__syncthreads_or(anyact)) {
+            const u64 nb = W::key_add(B, A.sub);
             B = nb < T ? nb : T;
             continue;
         }
-        // ---- relax the out-edges of the compacted frontier (push), one (cell, motion) per thread
-        const u32 n_task = n * (u32)K;
-        const u32 inv = 0xFFFFFFFFu / n + 1u; // tsk / n == umulhi(tsk, inv) for tsk * n < 2^32
-        for (u32 tsk = tid; tsk < n_task; tsk += NT) {
-            const u32 m = n == 1 ? tsk : __umulhi(tsk, inv), i = tsk - m * n;
-            const u32 need = S.m_need[m];
-            if ((S.fmask[i] & need) != need) continue; // isCollision: target / face cells occupied
-            ++my_edges;
-            const int c = S.list[i];
-            const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
-            const int hi = ((lz + C::ZH) * C::HY + (ly + 1)) * C::HX + (lx + 1);
-            const G gu = ((volatile G *)S.g)[hi];
-            const int mo = S.m_off[m];
-            const int vhi = hi + (mo >> 8);
-            const G cand = W::addw(gu, S.m_w[m]);
-            if (cand >= ((volatile G *)S.g)[vhi]) continue;
-            const int vx = lx + (mo & 3) - 1, vy = ly + ((mo >> 2) & 3) - 1, vz = lz + ((mo >> 4) & 3) - 1;
-            if (U != KEY_INF) {
-                const double hv = use_h ? heuristic_lo(ox + vx - gx, oy + vy - gy, oz + vz - gz, A.he, A.hm) : 0.0;
-                if (W::key(cand, hv) > U) continue; // cannot be on a better path to the goal
-            }
-            if (!smem_min(&S.g[vhi], cand)) continue;
-            if ((unsigned)vx < (unsigned)C::TX && (unsigned)vy < (unsigned)C::TY && (unsigned)vz < (unsigned)C::TZ) {
-                const int cv = (vz * C::TY + vy) * C::TX + vx;
-                atomicOr(&S.pend[cv >> 5], 1u << (cv & 31));
-            } else {
-                atomicOr(&S.chg[vhi >> 5], 1u << (vhi & 31));
-            }
-        }
-        {
-            const u64 nb = W::key_add(B, A.sub);
-            B = nb < T ? nb : T;
+        // nothing was expanded anywhere: the values are stable, take the exact min pending key
+        const int e = n_empty & 1;
+        ++n_empty;
+        if (__any_sync(0xFFFFFFFFu, lmin != KEY_INF)) {
+            lmin = warp_min_u64(lmin);
+            if (lane == 0) atomicMin(&S.kmin[e], lmin);
         }
         __syncthreads();
+        const u64 km = S.kmin[e];
+        if (tid == 0) S.kmin[e ^ 1] = KEY_INF;
+        if (km >= T) { km_final = km; break; }
+        const u64 nb = W::key_add(km, A.sub);
+        B = nb < T ? nb : T;
     }
 
-    const long long t_looped = clock64();
+    const u32 t_looped = (u32)clock64();
     // ---- publish.  Values and pending flags travel in one word, so one atomic per cell:
-    //  * own cells that changed: atomicMin(value, flag) -- a neighbour may have lowered a border
-    //    cell meanwhile, then its (lower, pending) word stays;
+    //  * own cells that were lowered: atomicMin(value, flag) -- a neighbour tile may have lowered
+    //    a border cell meanwhile, then its (lower, pending) word stays;
     //  * own cells that were pending at load, have propagated now and kept their value: CAS
     //    pending -> clean (fails harmlessly if somebody lowered the cell in between);
-    //  * improved halo cells: atomicMin(value, pending) into the neighbour tile.
+    //  * lowered halo cells: atomicMin(value, pending) into the neighbour tile.
 #pragma unroll
-    for (int k = 0; k < C::NCELL / NT; ++k) {
-        const int c = tid + k * NT;
-        const int w = c >> 5, b = c & 31;
-        if ((S.chgi[w] >> b) & 1u) {
-            const int lx = c % C::TX, ly = (c / C::TX) % C::TY, lz = c / (C::TX * C::TY);
-            const int hi = ((lz + C::ZH) * C::HY + (ly + 1)) * C::HX + (lx + 1);
+    for (int j = 0; j < CPT; ++j) {
+        const int hj = C::own_hi(tid, j);
+        const G v = W::dec(S.g[hj]);
+        const bool pending = v < gprop[j];
+        const bool changed = (S.chg[hj >> 5] >> (hj & 31)) & 1u;
+        if (changed || ((ldp >> j) & 1u)) {
+            int lx, ly, lz;
+            C::owned(tid, j, lx, ly, lz);
             G *addr = gq + ((size_t)(oz + lz) * Gd.PY + (oy + ly)) * Gd.PX + (ox + lx);
-            const G v = S.g[hi];
-            const bool pending = (S.pend[w] >> b) & 1u;
-            red_min(addr, W::enc(v, pending));
-            if (!pending && ((S.ldd[w] >> b) & 1u)) cas_word(addr, W::enc(v, true), W::enc(v, false));
+            if (changed) red_min(addr, W::enc(v, pending));
+            else if (!pending) cas_word(addr, W::enc(v, true), W::enc(v, false));
         }
     }
 #pragma unroll
@@ -344,18 +363,26 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         const int i = tid + k * NT;
         if (i < C::HC && ((S.chg[i >> 5] >> (i & 31)) & 1u)) {
             const int hx = i % C::HX, hy = (i / C::HX) % C::HY, hz = i / (C::HX * C::HY);
-            const int x = ox + hx - 1, y = oy + hy - 1, z = oz + hz - C::ZH;
-            const G v = S.g[i];
-            red_min(gq + ((size_t)z * Gd.PY + y) * Gd.PX + x, W::enc(v, true));
             const int sx = hx == 0 ? -1 : (hx == C::HX - 1 ? 1 : 0);
             const int sy = hy == 0 ? -1 : (hy == C::HY - 1 ? 1 : 0);
             const int sz = C::ZH ? (hz == 0 ? -1 : (hz == C::HZ - 1 ? 1 : 0)) : 0;
-            const double hv = use_h ? heuristic_lo(x - gx, y - gy, z - gz, A.he, A.hm) : 0.0;
-            atomicMin(&S.nbrmin[(sz + 1) * 9 + (sy + 1) * 3 + (sx + 1)], W::key(v, hv));
+            if (sx | sy | sz) { // a halo cell
+                const int x = ox + hx - 1, y = oy + hy - 1, z = oz + hz - C::ZH;
+                const G v = W::dec(S.g[i]);
+                red_min(gq + ((size_t)z * Gd.PY + y) * Gd.PX + x, W::enc(v, true));
+                const double hv = use_h ? heuristic_lo(x - gx, y - gy, z - gz, A.he, A.hm) : 0.0;
+                atomicMin(&S.nbrmin[(sz + 1) * 9 + (sy + 1) * 3 + (sx + 1)], W::key(v, hv));
+            }
         }
     }
-    for (int o = 16; o; o >>= 1) my_edges += __shfl_down_sync(0xFFFFFFFFu, my_edges, o);
-    if (lane == 0 && my_edges) atomicAdd(&S.n_edge, my_edges);
+    for (int o = 16; o; o >>= 1) {
+        my_edges += __shfl_down_sync(0xFFFFFFFFu, my_edges, o);
+        n_exp += __shfl_down_sync(0xFFFFFFFFu, n_exp, o);
+    }
+    if (lane == 0) {
+        if (my_edges) atomicAdd(&S.n_edge, my_edges);
+        if (n_exp) atomicAdd(&S.n_exp, n_exp);
+    }
     __syncthreads();
     if (tid == 0) fence_gpu(); // cumulative: every word above is visible before a tile is armed
     __syncthreads();
@@ -370,8 +397,8 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     }
     if (tid == 32) {
         if (km_final != KEY_INF) atomicMin(&A.minkey[gt], km_final);
-        const long long t_end = clock64();
-        S.stat[1] += 1; S.stat[2] += n_exp;   // per-CTA counters, flushed once at kernel end
+        const u32 t_end = (u32)clock64();
+        S.stat[1] += 1; S.stat[2] += S.n_exp; S.n_exp = 0;   // per-CTA counters, flushed once at kernel end
         S.stat[3] += S.n_edge; S.n_edge = 0;
         S.stat[5] += (u64)(t_loaded - t_begin);
         S.stat[6] += (u64)(t_looped - t_loaded);
@@ -385,7 +412,7 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
 // persistent round loop
 // ---------------------------------------------------------------------------------------------
 template <class C>
-__global__ void __launch_bounds__(NT, 4) k_sssp(const __grid_constant__ SsspArgs A) {
+__global__ void __launch_bounds__(NT, PMP_MINB) k_sssp(const __grid_constant__ SsspArgs A) {
     typedef typename C::W W;
     typedef typename C::G G;
     cg::grid_group grid = cg::this_grid();
@@ -395,24 +422,13 @@ __global__ void __launch_bounds__(NT, 4) k_sssp(const __grid_constant__ SsspArgs
     const u32 total = A.nq * ntiles;
     const u32 gstride = gridDim.x * NT;
     if (tid < 16) S.stat[tid] = 0;
-    if (tid == 0) S.n_edge = 0;
-    if (tid < PMP_MAXM) S.m_need[tid] = 0xFFFFFFFFu; // bit 31 is never free: slot unused
-    __syncthreads();
-    if (tid < A.M.k) {
-        const int dx = A.M.dx[tid], dy = A.M.dy[tid], dz = A.M.dz[tid];
-        S.m_w[tid] = W::wbits(A.M, tid);
-        S.m_need[tid] = A.M.need[tid];
-        S.m_off[tid] = (dx + 1) | ((dy + 1) << 2) | ((dz + 1) << 4) | (((dz * C::HY + dy) * C::HX + dx) * 256);
-    }
-    __syncthreads();
+    if (tid == 0) { S.n_edge = 0; S.n_exp = 0; }
     const bool timer = blockIdx.x == 0 && tid == 0;
-    u64 t0 = 0, t_scan = 0, t_proc = 0, t_wait = 0;
-    if (timer) t0 = globaltimer_ns();
+    if (timer) { S.tm[0] = globaltimer_ns(); S.tm[1] = S.tm[2] = S.tm[3] = 0; }
 
     for (int r = 0;; ++r) {
         const int cur = r & 1, nxt = cur ^ 1;
-        u64 ta = 0;
-        if (timer) ta = globaltimer_ns();
+        if (timer) S.tm[4] = globaltimer_ns();
         // ---- SCAN: which (query, tile) pairs fall inside their query's key window ----
         if (tid == 0) S.s_live = 0;
         __syncthreads();
@@ -449,8 +465,7 @@ __global__ void __launch_bounds__(NT, 4) k_sssp(const __grid_constant__ SsspArgs
 
         const u32 live = ld_cg(&A.ctr[4 + cur]);
         const u32 nwl = ld_cg(&A.ctr[cur]);
-        u64 tb = 0;
-        if (timer) { tb = globaltimer_ns(); t_scan += tb - ta; }
+        if (timer) { const u64 tb = globaltimer_ns(); S.tm[1] += tb - S.tm[4]; S.tm[4] = tb; }
         if (live == 0) break;
         if (A.max_rounds > 0 && r >= A.max_rounds) break;
 
@@ -490,16 +505,15 @@ __global__ void __launch_bounds__(NT, 4) k_sssp(const __grid_constant__ SsspArgs
             if (it >= nwl) break;
             process_tile<C>(A, ld_cg(&A.wl[cur][it]), cur, S);
         }
-        u64 tc = 0;
-        if (timer) { tc = globaltimer_ns(); t_proc += tc - tb; }
+        if (timer) { const u64 tc = globaltimer_ns(); S.tm[2] += tc - S.tm[4]; S.tm[4] = tc; }
         grid.sync();
-        if (timer) t_wait += globaltimer_ns() - tc;
+        if (timer) S.tm[3] += globaltimer_ns() - S.tm[4];
     }
     __syncthreads();
     if (tid < 16 && tid != 0 && tid != 4 && (tid < 8 || tid == 12) && S.stat[tid]) atomicAdd(&A.stats[tid], S.stat[tid]);
     if (timer) {
-        A.stats[8] = globaltimer_ns() - t0;
-        A.stats[9] = t_scan; A.stats[10] = t_proc; A.stats[11] = t_wait;
+        A.stats[8] = globaltimer_ns() - S.tm[0];
+        A.stats[9] = S.tm[1]; A.stats[10] = S.tm[2]; A.stats[11] = S.tm[3];
     }
 }
 
@@ -661,6 +675,8 @@ static int launch_sssp(pmp_grid *g, SsspArgs &A, double *gcost_dev, int32_t *sta
         PMP_CHECK_CUDA(cudaGetDevice(&dev));
         PMP_CHECK_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
         if (blocks_per_sm < 1) { pmp_set_error("k_sssp does not fit on an SM"); return -2; }
+        const char *e = getenv("PMP_B200_CTAS_PER_SM"); // tuning: fewer resident CTAs than fit
+        if (e && atoi(e) >= 1 && atoi(e) < blocks_per_sm) blocks_per_sm = atoi(e);
     }
     const unsigned ib = (unsigned)((A.nq + 255) / 256);
     if (mode & 1) {
@@ -696,7 +712,15 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
     A.key_cap = KEY_INF;
 
     A.G = g->d;
-    A.M = g->mot;
+    for (int d = 0; d < 27; ++d) { A.wdir[d] = ~0ull; A.need[d] = 0xFFFFFFFFu; }
+    for (int m = 0; m < g->mot.k; ++m) {
+        const int d = (g->mot.dz[m] + 1) * 9 + (g->mot.dy[m] + 1) * 3 + (g->mot.dx[m] + 1);
+        u64 w;
+        if (P->weight == PMP_W_F64) memcpy(&w, &g->mot.w[m], 8);
+        else w = g->mot.wi[m];
+        if (A.need[d] == 0xFFFFFFFFu || w < A.wdir[d]) A.wdir[d] = w; // duplicate offsets: cheapest
+        A.need[d] = g->mot.need[m];
+    }
     A.nq = (u32)nq;
     A.starts = starts_dev;
     A.goals = goals_dev;
