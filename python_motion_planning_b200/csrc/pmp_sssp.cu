@@ -101,16 +101,16 @@ struct SsspArgs {
     // directions not in the motion table have need = all-ones (never satisfied).
     u64 wdir[27];
     u32 need[27];
-    u32 nq;
+    u32 nq, ring_cap;
     const int32_t *starts, *goals;
     void *g;
     u64 *minkey;
-    u32 *wl[2];
+    u32 *wl[2];    // [0] ring of queued (query, tile) ids + 1 (0 = empty slot), [1] per-tile "in queue" flag
     u64 *qmin[2];
     u64 *T[2];
     int *done;
     u32 *goalcell; // padded cell index of each goal (0xFFFFFFFF = none)
-    u32 *ctr;      // [0,1] worklist counts, [2,3] worklist heads, [4,5] live tiles
+    u32 *ctr;      // per round parity p: [p] ring tail, [2+p] ring head, [4+p] live tiles, [6+p] tiles in flight
     u64 *stats;    // 16 counters, see include/pmp_b200.h (pmp_sssp)
     double window, sub, he, hm;
     u64 key_cap; // slab mode: only keys below this bound are processed (KEY_INF otherwise)
@@ -170,6 +170,7 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     const u32 t_begin = (u32)clock64();
     // ---- prologue: the dependent global round trips are spread over different warps ----
     if (tid == 0) {
+        atomicExch(&A.wl[1][gt], 0u);              // leave the queue: later pushes append the tile again
         S.k0 = atomicExch(&A.minkey[gt], KEY_INF); // claim: later pushes re-arm the tile
         fence_gpu();
     } else if (tid == 32) {
@@ -393,6 +394,11 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
             const int sx = tid % 3 - 1, sy = (tid / 3) % 3 - 1, sz = tid / 9 - 1;
             const u32 ngt = q * Gd.ntiles + (u32)(((ttz + sz) * Gd.nty + (tty + sy)) * Gd.ntx + (ttx + sx));
             atomicMin(&A.minkey[ngt], k);
+            if (k < T && atomicExch(&A.wl[1][ngt], 1u) == 0) { // inside the window and not queued yet
+                atomicAdd(&A.ctr[6 + cur], 1u);
+                const u32 pos = atomicAdd(&A.ctr[cur], 1u);
+                *(volatile u32 *)&A.wl[0][pos % A.ring_cap] = ngt + 1u;
+            }
         }
     }
     if (tid == 32) {
@@ -450,12 +456,16 @@ __global__ void __launch_bounds__(NT, PMP_MINB) k_sssp(const __grid_constant__ S
                 }
             }
             my_live += live;
+            if (take) take = atomicExch(&A.wl[1][gt], 1u) == 0; // the "in queue" flag
             const u32 m = __ballot_sync(0xFFFFFFFFu, take);
             if (m) {
                 u32 pos = 0;
-                if (lane == 0) pos = atomicAdd(&A.ctr[cur], (u32)__popc(m));
+                if (lane == 0) {
+                    atomicAdd(&A.ctr[6 + cur], (u32)__popc(m)); // tiles in flight
+                    pos = atomicAdd(&A.ctr[cur], (u32)__popc(m));
+                }
                 pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
-                if (take) A.wl[cur][pos + __popc(m & ((1u << lane) - 1u))] = gt;
+                if (take) A.wl[0][(pos + __popc(m & ((1u << lane) - 1u))) % A.ring_cap] = gt + 1u;
             }
         }
         if (my_live) atomicAdd(&S.s_live, my_live);
@@ -464,7 +474,6 @@ __global__ void __launch_bounds__(NT, PMP_MINB) k_sssp(const __grid_constant__ S
         grid.sync();
 
         const u32 live = ld_cg(&A.ctr[4 + cur]);
-        const u32 nwl = ld_cg(&A.ctr[cur]);
         if (timer) { const u64 tb = globaltimer_ns(); S.tm[1] += tb - S.tm[4]; S.tm[4] = tb; }
         if (live == 0) break;
         if (A.max_rounds > 0 && r >= A.max_rounds) break;
@@ -491,23 +500,45 @@ __global__ void __launch_bounds__(NT, PMP_MINB) k_sssp(const __grid_constant__ S
             A.qmin[nxt][q] = KEY_INF;
         }
         if (blockIdx.x == 0 && tid == 0) {
-            A.ctr[nxt] = 0; A.ctr[2 + nxt] = 0; A.ctr[4 + nxt] = 0;
+            A.ctr[nxt] = 0; A.ctr[2 + nxt] = 0; A.ctr[4 + nxt] = 0; A.ctr[6 + nxt] = 0;
             A.stats[0] = (u64)(r + 1);
-            if ((u64)nwl > A.stats[4]) A.stats[4] = nwl;
         }
 
-        // ---- PROCESS the worklist ----
+        // ---- PROCESS: asynchronous cascade.  The ring holds the tiles whose smallest pending key
+        // lies inside the window; a tile that pushes such a key into a neighbour appends the
+        // neighbour itself (process_tile), so the wave crosses many tiles per round without a
+        // grid barrier.  The round ends when no tile is queued or being processed.
         for (;;) {
-            if (tid == 0) S.item = atomicAdd(&A.ctr[2 + cur], 1u);
+            if (tid == 0) {
+                const u32 ticket = atomicAdd(&A.ctr[2 + cur], 1u);
+                u32 *slot = &A.wl[0][ticket % A.ring_cap];
+                u32 v;
+                unsigned ns = 20, spins = 0;
+                for (;;) {
+                    v = ld_cg(slot);
+                    if (v) break;
+                    if (ld_cg(&A.ctr[6 + cur]) == 0) break; // nothing in flight: nobody can append
+                    __nanosleep(ns);
+                    if (ns < 160) ns *= 2;
+                    if (++spins > (1u << 22)) { A.stats[15] = 0xDEADu; break; } // safety net (seconds)
+                }
+                if (v) { *(volatile u32 *)slot = 0; fence_gpu(); }
+                S.item = v;
+            }
             __syncthreads();
             const u32 it = S.item;
             __syncthreads();
-            if (it >= nwl) break;
-            process_tile<C>(A, ld_cg(&A.wl[cur][it]), cur, S);
+            if (it == 0) break;
+            process_tile<C>(A, it - 1u, cur, S);
+            if (tid == 0) atomicSub(&A.ctr[6 + cur], 1u); // after this tile's own appends
         }
         if (timer) { const u64 tc = globaltimer_ns(); S.tm[2] += tc - S.tm[4]; S.tm[4] = tc; }
         grid.sync();
-        if (timer) S.tm[3] += globaltimer_ns() - S.tm[4];
+        if (timer) {
+            S.tm[3] += globaltimer_ns() - S.tm[4];
+            const u64 nwl = ld_cg(&A.ctr[cur]);
+            if (nwl > A.stats[4]) A.stats[4] = nwl;
+        }
     }
     __syncthreads();
     if (tid < 16 && tid != 0 && tid != 4 && (tid < 8 || tid == 12) && S.stat[tid]) atomicAdd(&A.stats[tid], S.stat[tid]);
@@ -627,6 +658,9 @@ typedef TileCfg<16, 8, 8, WU32> C3U;
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// The ring has more slots than tiles + resident CTAs, so a waiting consumer ticket can never alias
+// the slot of a queued tile (at most one ticket per CTA is outstanding beyond the tail).
+#define RING_SLACK 1024
 struct WsLayout {
     size_t minkey, wl0, wl1, qmin0, qmin1, T0, T1, done, goalcell, ctr, stats, total;
 };
@@ -636,7 +670,7 @@ static WsLayout ws_layout(const pmp_grid *g, int64_t nq) {
     const size_t nt = (size_t)nq * g->d.ntiles;
     size_t o = 0;
     L.minkey = o; o = align_up(o + nt * 8, 256);
-    L.wl0 = o; o = align_up(o + nt * 4, 256);
+    L.wl0 = o; o = align_up(o + (nt + RING_SLACK) * 4, 256);
     L.wl1 = o; o = align_up(o + nt * 4, 256);
     L.qmin0 = o; o = align_up(o + (size_t)nq * 8, 256);
     L.qmin1 = o; o = align_up(o + (size_t)nq * 8, 256);
@@ -722,6 +756,7 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
         A.need[d] = g->mot.need[m];
     }
     A.nq = (u32)nq;
+    A.ring_cap = (u32)((size_t)nq * g->d.ntiles + RING_SLACK);
     A.starts = starts_dev;
     A.goals = goals_dev;
     A.g = g_dev;
@@ -749,7 +784,11 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
     }
     if (P->reserved > 1) A.sub *= (double)P->reserved; // wider in-tile sub-buckets (tuning knob)
     double window = P->window;
-    if (!(window > 0.0)) window = (g->d.ndim == 2 ? 24.0 : 10.0) * g->wmin;
+    // Default key window per round.  Inside a round tiles cascade asynchronously, so the window
+    // only bounds how far ahead of the smallest pending key work may run: wide for full sweeps
+    // (few rounds), narrow for A-star, whose keys g + h span a small range and where everything
+    // above the final cost is wasted.
+    if (!(window > 0.0)) window = (A.use_h ? 6.0 : (g->d.ndim == 2 ? 48.0 : 24.0)) * g->wmin;
     if (P->weight == PMP_W_U32 && window < 1.0) window = 1.0;
     A.window = window;
 
@@ -789,6 +828,8 @@ extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
     PMP_CHECK_CUDA(cudaMemsetAsync(g_dev, 0xFF, gsz, s));
     const size_t nt = (size_t)nq * g->d.ntiles;
     PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, nt * 8, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[0], 0, (nt + RING_SLACK) * 4, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[1], 0, nt * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 16 * 8, s));
 
@@ -905,6 +946,8 @@ extern "C" int pmp_slab_begin(pmp_grid *g, const pmp_sssp_params *P, const int32
     fill_args(g, &Q, 1, start_dev, nullptr, g_dev, ws_dev, L, A);
     PMP_CHECK_CUDA(cudaMemsetAsync(g_dev, 0xFF, (size_t)g->d.pcells * (Q.weight == PMP_W_F64 ? 8 : 4), s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, (size_t)g->d.ntiles * 8, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[0], 0, ((size_t)g->d.ntiles + RING_SLACK) * 4, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[1], 0, (size_t)g->d.ntiles * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 16 * 8, s));
     if (start_dev) return dispatch_sssp(g, Q.weight, A, nullptr, nullptr, s, 1);
