@@ -148,6 +148,15 @@ int pmp_extract_paths(const pmp_grid *g, int weight, int64_t nq,
                       uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
                       double *cost_dev, void *stream);
 
+/* ---- shortest-path certificate (no reference counterpart; tests + slab driver) ----
+ * Checks, for the planes z in [z_lo, z_hi) of ONE cost field in the internal word format, that
+ * g(source) = 0 and every other free cell satisfies g(v) = min over legal in-edges u->v of
+ * fl(g(u) + w) (+inf when no in-neighbour is reached), which characterises the shortest-path
+ * field.  out_dev: 3 x uint64 = {violating cells, reached cells, cells still flagged pending}.
+ * source_dev: 3 x int32 local coordinates, or NULL when the source lies outside this grid. */
+int pmp_verify_field(const pmp_grid *g, int weight, const void *g_dev, const int32_t *source_dev,
+                     int z_lo, int z_hi, uint64_t *out_dev, void *stream);
+
 /* ---- greedy best-first: replaces GBFS.plan / GBFS3D.plan (gbfs.py:36-86, gbfs3d.py:34-82) ----
  * One warp per query runs the reference's sequential loop (binary heap keyed by h, FIFO
  * counter as in gbfs3d.py:46).  family: 2 = 2D record/tie rule, 3 = 3D.

@@ -23,7 +23,7 @@ SYMBOLS = (
     "pmp_grid_create", "pmp_grid_destroy", "pmp_grid_layout", "pmp_grid_set_cells",
     "pmp_grid_set_dense", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
     "pmp_grid_set_motions", "pmp_sssp_sizes", "pmp_sssp", "pmp_field_finalize",
-    "pmp_count_settled", "pmp_extract_paths", "pmp_gbfs",
+    "pmp_count_settled", "pmp_extract_paths", "pmp_verify_field", "pmp_gbfs",
     "pmp_slab_begin", "pmp_slab_run", "pmp_slab_merge",
 )
 
@@ -86,6 +86,7 @@ def lib():
         "pmp_field_finalize": [vp, i32, i64, vp],
         "pmp_count_settled": [vp, i32, i64, vp, vp, vp, i32, vp, vp],
         "pmp_extract_paths": [vp, i32, i64, vp, vp, vp, vp, i64, vp, vp, vp],
+        "pmp_verify_field": [vp, i32, vp, vp, i32, i32, vp, vp],
         "pmp_gbfs": [vp, i32, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp, vp],
         "pmp_slab_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, i64, vp],
         "pmp_slab_run": [vp, ctypes.POINTER(SsspParams), vp, vp, i64, dbl, vp, vp],

@@ -114,3 +114,56 @@ def cost_field(env, source, weight="f64", window=0.0, to_host=True):
     if not to_host:
         return ws, ws.stats
     return engine.field_to_numpy(ws, 0)
+
+
+def shard_range(nq, rank, world):
+    """contiguous slice [q0, q1) of the queries planned by `rank` (sizes differ by at most one)"""
+    base, rem = divmod(nq, world)
+    q0 = rank * base + min(rank, rem)
+    return q0, q0 + base + (1 if rank < rem else 0)
+
+
+def plan_batch_sharded(env, starts, goals, dist=None, gather=True, _plan=None, **kw):
+    """plan_batch over several GPUs: the occupancy bitmask is
+    replicated, the queries are split 1/P per rank, no communication on the data path.  With
+    gather=True the per-query scalars (costs, gcosts, status, path_len) are all-gathered so
+    every rank returns the complete arrays; paths stay on the rank that planned them
+    (`res.paths[q]` is None elsewhere).  `dist`: torch.distributed (initialised), or None."""
+    plan = _plan or plan_batch
+    ndim = env._ndim
+    starts = np.asarray(starts, dtype=np.int32).reshape(-1, ndim)
+    goals = np.asarray(goals, dtype=np.int32).reshape(-1, ndim)
+    nq = len(starts)
+    world = dist.get_world_size() if dist is not None else 1
+    rank = dist.get_rank() if dist is not None else 0
+    q0, q1 = shard_range(nq, rank, world)
+    local = plan(env, starts[q0:q1], goals[q0:q1], **kw) if q1 > q0 else None
+    res = BatchResult()
+    res.costs = np.full(nq, np.inf)
+    res.gcosts = np.full(nq, np.inf)
+    res.status = np.zeros(nq, dtype=np.int32)
+    res.path_len = np.zeros(nq, dtype=np.int32)
+    res.shard = (q0, q1)
+    if local is not None:
+        res.costs[q0:q1], res.gcosts[q0:q1] = local.costs, local.gcosts
+        res.status[q0:q1], res.path_len[q0:q1] = local.status, local.path_len
+        res.stats = local.stats
+        res.h2d_bytes, res.d2h_bytes = local.h2d_bytes, local.d2h_bytes
+        if local.paths is not None:
+            res.paths = [None] * nq
+            res.paths[q0:q1] = local.paths
+        if local.settled is not None:
+            res.settled = np.zeros(nq, dtype=np.int64)
+            res.settled[q0:q1] = local.settled
+    if gather and world > 1:
+        import torch
+        dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+        # +inf / zeros outside the own shard: min / max reductions assemble the full arrays
+        c = torch.from_numpy(np.stack([res.costs, res.gcosts])).to(dev)
+        dist.all_reduce(c, op=dist.ReduceOp.MIN)
+        s = torch.from_numpy(np.stack([res.status, res.path_len]).astype(np.int64)).to(dev)
+        dist.all_reduce(s, op=dist.ReduceOp.MAX)
+        c, s = c.cpu().numpy(), s.cpu().numpy()
+        res.costs, res.gcosts = c[0], c[1]
+        res.status, res.path_len = s[0].astype(np.int32), s[1].astype(np.int32)
+    return res

@@ -96,6 +96,72 @@ extern "C" int pmp_extract_paths(const pmp_grid *g, int weight, int64_t nq,
 }
 
 // ---------------------------------------------------------------------------------------------
+// shortest-path certificate (no reference counterpart; used by tests and the slab driver).
+// A field g is THE single-source shortest-path field iff g(source) = 0 and every other free
+// cell v satisfies g(v) = min over legal in-edges u->v of fl(g(u) + w) (+inf if no in-neighbour
+// is reached).  Counts the cells that violate this, the reached cells and the cells that still
+// carry a pending flag, for the planes z in [z_lo, z_hi).
+// ---------------------------------------------------------------------------------------------
+template <class W>
+__global__ void k_verify_field(const GridDev G, const __grid_constant__ Motions M,
+                               const typename W::G *g, const int32_t *source, int z_lo, int z_hi,
+                               u64 *out) {
+    typedef typename W::G GT;
+    const size_t plane = (size_t)G.PX * G.PY;
+    const size_t lo = (size_t)z_lo * plane, hi = (size_t)z_hi * plane;
+    int sx = -1, sy = -1, sz = -1;
+    if (source) { sx = source[0]; sy = source[1]; sz = G.ndim == 3 ? source[2] : 0; }
+    u64 bad = 0, reached = 0, pend = 0;
+    for (size_t i = lo + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < hi; i += (size_t)gridDim.x * blockDim.x) {
+        const int x = (int)(i % G.PX), y = (int)((i / G.PX) % G.PY), z = (int)(i / plane);
+        const GT sw = g[i];
+        const GT v = W::dec(sw);
+        if (cell_blocked(G, x, y, z)) { if (sw != W::ginf()) ++bad; continue; }
+        if (v != W::inf()) { ++reached; if (!(sw & 1)) ++pend; }
+        GT best = W::inf();
+        for (int m = 0; m < M.k; ++m) {
+            const int ux = x - M.dx[m], uy = y - M.dy[m], uz = z - M.dz[m];
+            if (!edge_legal(G, M, m, ux, uy, uz)) continue;
+            const GT gu = W::dec(g[((size_t)uz * G.PY + uy) * G.PX + ux]);
+            if (gu == W::inf()) continue;
+            const GT c = W::add(gu, M, m);
+            best = c < best ? c : best;
+        }
+        if (x == sx && y == sy && z == sz) { if (v != 0) ++bad; }
+        else if (v != best) ++bad;
+    }
+    for (int o = 16; o; o >>= 1) {
+        bad += __shfl_down_sync(0xFFFFFFFFu, bad, o);
+        reached += __shfl_down_sync(0xFFFFFFFFu, reached, o);
+        pend += __shfl_down_sync(0xFFFFFFFFu, pend, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (bad) atomicAdd(&out[0], bad);
+        if (reached) atomicAdd(&out[1], reached);
+        if (pend) atomicAdd(&out[2], pend);
+    }
+}
+
+extern "C" int pmp_verify_field(const pmp_grid *g, int weight, const void *g_dev,
+                                const int32_t *source_dev, int z_lo, int z_hi, uint64_t *out_dev,
+                                void *stream) {
+    if (!g || !g_dev || !out_dev || z_lo < 0 || z_hi > g->d.PZ || z_lo > z_hi) {
+        pmp_set_error("pmp_verify_field: bad arguments");
+        return -1;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    PMP_CHECK_CUDA(cudaMemsetAsync(out_dev, 0, 3 * 8, s));
+    if (z_lo == z_hi) return 0;
+    if (weight == PMP_W_F64)
+        k_verify_field<WF64><<<148 * 8, 256, 0, s>>>(g->d, g->mot, (const u64 *)g_dev, source_dev, z_lo, z_hi, (u64 *)out_dev);
+    else if (weight == PMP_W_U32)
+        k_verify_field<WU32><<<148 * 8, 256, 0, s>>>(g->d, g->mot, (const u32 *)g_dev, source_dev, z_lo, z_hi, (u64 *)out_dev);
+    else { pmp_set_error("pmp_verify_field: bad weight type"); return -1; }
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 // greedy best-first search
 // ---------------------------------------------------------------------------------------------
 struct __align__(16) HeapRec {

@@ -316,3 +316,48 @@ def test_default_grid3d_walls_quirk_on_device():
             ref[p] = True
     assert np.array_equal(occ, ref)
     assert not ref[1:-1, 1:-1, 1:-1].any() and ref[0, :, :-1].all()
+
+
+def test_slab_decomposition_single_gpu_emulation():
+    """config 5 in miniature: the z-slab protocol through the C ABI (pmp_slab_begin / run / merge),
+    three slabs held by one process and run in turn; bit-exact against the oracle and against
+    the one-piece field, plus the shortest-path certificate (pmp_verify_field)."""
+    from python_motion_planning_b200 import slab
+    occ = random_boxes((40, 33, 37), 90, 7, 21)
+    occ[1:-1, 16, 1:-1] = True            # a wall with two holes: paths cross slab boundaries
+    occ[3, 16, 30] = False
+    occ[30, 16, 4] = False
+    src = (1, 1, 1)
+    occ[1:3, 1:3, 1:3] = False
+    Z = occ.shape[2]
+    for mset, weight in ((6, "u32"), (6, "f64"), (26, "f64")):
+        motions, mg = gio.motions_for(3, mset)
+        ref = oracle.plan(occ, src, None, algo=oracle.DIJKSTRA, motions=motions, motion_g=mg,
+                          want_field=True, want_expand=False).g_field
+        engines = []
+        for p in range(3):
+            h0, h1 = slab.ghost_range(Z, p, 3)
+            engines.append(slab.CudaSlabEngine(slab.build_local_env(occ[:, :, h0:h1], str(mset)), weight))
+        its, drv = slab.solve_in_process(engines, Z, src, outer_window=6.0)
+        field = np.full(occ.shape, np.inf)
+        bad = reached = pend = 0
+        for d in drv:
+            field[:, :, d.z0:d.z1] = d.e.field(d.local_z(d.z0), d.local_z(d.z1))
+            b, r, pn = d.e.verify((src[0], src[1], d.local_z(src[2])) if d.owns(src[2]) else None,
+                                  d.local_z(d.z0), d.local_z(d.z1))
+            bad, reached, pend = bad + b, reached + r, pend + pn
+        assert np.array_equal(field, ref), (mset, weight)
+        assert (bad, pend) == (0, 0) and reached == int(np.isfinite(ref).sum()), (mset, weight, bad, pend)
+        assert its > 2
+        # one piece, same certificate
+        one = slab.CudaSlabEngine(slab.build_local_env(occ, str(mset)), weight)
+        slab.solve_in_process([one], Z, src)
+        assert np.array_equal(one.field(0, Z), ref)
+        assert one.verify(src, 0, Z)[0] == 0
+        # the certificate notices a wrong value
+        import torch
+        words = one.ws.g.view(torch.int64 if weight == "f64" else torch.int32)
+        free = np.argwhere(np.isfinite(ref))
+        cx, cy, cz = (int(v) for v in free[len(free) // 2])
+        words[0, (cz * one.dg.padded[1] + cy) * one.dg.padded[0] + cx] += 8
+        assert one.verify(src, 0, Z)[0] > 0
