@@ -884,8 +884,8 @@ __global__ void k_slab_arm(SsspArgs A, u64 cap) {
 }
 
 __global__ void k_slab_export(SsspArgs A, u64 *out) {
-    const u64 a = A.qmin[0][0], b = A.qmin[1][0];
-    out[0] = a < b ? a : b; // smallest pending key left in this slab (KEY_INF: none)
+    // the scan of the last round (parity = rounds completed & 1) saw every key still pending
+    out[0] = A.qmin[A.stats[0] & 1][0]; // smallest pending key left in this slab (KEY_INF: none)
     out[1] = A.stats[0];
     out[2] = A.stats[1];
     out[3] = A.stats[2];
