@@ -395,6 +395,7 @@ def main():
             "rounds": st[0], "tile_activations": st[1], "cells_expanded": st[2], "edges_relaxed": st[3],
             "worklist_max": st[4], "sub_iterations": st[12],
             "us_per_activation": {"load": st[5] / nt / mhz, "settle": st[6] / nt / mhz, "publish": st[7] / nt / mhz},
+            "prof_warp_cycles_per_subiter": {"scan": st[13] / max(st[12], 1) / 8, "expand": st[14] / max(st[12], 1) / 8, "barrier": st[15] / max(st[12], 1) / 8},
             "kernel_ms": st[8] / 1e6, "cta0_ms": {"scan": st[9] / 1e6, "process": st[10] / 1e6, "barrier_wait": st[11] / 1e6}}
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):

@@ -26,6 +26,16 @@ __device__ static inline bool edge_legal(const GridDev &G, const Motions &M, int
     return true;
 }
 
+// 64-bit / 32-bit warp minimum with the hardware reductions (REDUX works on 32-bit words)
+__device__ static inline u64 warp_min(u64 v) {
+    const u32 hi = (u32)(v >> 32);
+    const u32 mh = __reduce_min_sync(0xFFFFFFFFu, hi);
+    const u32 lo = hi == mh ? (u32)v : 0xFFFFFFFFu;
+    const u32 ml = __reduce_min_sync(0xFFFFFFFFu, lo);
+    return ((u64)mh << 32) | ml;
+}
+__device__ static inline u32 warp_min(u32 v) { return __reduce_min_sync(0xFFFFFFFFu, v); }
+
 template <class W>
 __global__ void k_extract_paths(const GridDev G, const __grid_constant__ Motions M, u32 nq,
                                 const int32_t *starts, const int32_t *goals,
@@ -45,6 +55,13 @@ __global__ void k_extract_paths(const GridDev G, const __grid_constant__ Motions
         if (lane == 0) { plen[q] = 0; cost[q] = INF_D; }
         return;
     }
+    // this lane's motion: offset, cost, and the face cells of the SOURCE u = v - offset that
+    // the directed rule needs free (graph_search.py:78-86, graph_search_3d.py:97-105); u itself
+    // is free iff it has a finite value, v is on the path
+    const bool has = lane < M.k;
+    const int dx = has ? M.dx[lane] : 0, dy = has ? M.dy[lane] : 0, dz = has ? M.dz[lane] : 0;
+    const int nax = (dx != 0) + (dy != 0) + (dz != 0);
+    const double mylen = has ? M.len[lane] : 0.0;
     int64_t n = 0;
     double c = 0.0;
     int32_t result = 0;
@@ -53,24 +70,24 @@ __global__ void k_extract_paths(const GridDev G, const __grid_constant__ Motions
         ++n;
         if (vx == sx && vy == sy && vz == sz) { result = n <= cap ? (int32_t)n : -1; break; }
         GT cand = W::inf();
-        if (lane < M.k) {
-            const int ux = vx - M.dx[lane], uy = vy - M.dy[lane], uz = vz - M.dz[lane];
-            if (edge_legal(G, M, lane, ux, uy, uz)) {
-                const GT gu = W::dec(gq[((size_t)uz * G.PY + uy) * G.PX + ux]);
-                if (gu != W::inf()) cand = W::add(gu, M, lane);
+        const int ux = vx - dx, uy = vy - dy, uz = vz - dz;
+        if (has && (unsigned)ux < (unsigned)G.PX && (unsigned)uy < (unsigned)G.PY && (unsigned)uz < (unsigned)G.PZ) {
+            // independent loads: the value of u and the (0, 2 or 3) face cells
+            const GT gu = W::dec(gq[((size_t)uz * G.PY + uy) * G.PX + ux]);
+            int blocked = 0;
+            if (nax >= 2) {
+                if (dx) blocked |= cell_blocked(G, ux + dx, uy, uz);
+                if (dy) blocked |= cell_blocked(G, ux, uy + dy, uz);
+                if (dz) blocked |= cell_blocked(G, ux, uy, uz + dz);
             }
+            if (!blocked && gu != W::inf()) cand = W::add(gu, M, lane);
         }
-        GT best = cand;
-#pragma unroll
-        for (int o = 16; o; o >>= 1) {
-            const GT other = __shfl_xor_sync(0xFFFFFFFFu, best, o);
-            best = other < best ? other : best;
-        }
+        const GT best = warp_min(cand);
         if (best == W::inf()) { result = 0; c = INF_D; break; } // cannot happen on a converged field
         const u32 who = __ballot_sync(0xFFFFFFFFu, cand == best);
         const int m = __ffs(who) - 1;
-        c += M.len[m]; // Planner.dist (planner.py:22-23): hypot of the step, summed goal -> start
-        vx -= M.dx[m]; vy -= M.dy[m]; vz -= M.dz[m];
+        c += __shfl_sync(0xFFFFFFFFu, mylen, m); // Planner.dist (planner.py:22-23): hypot of the step, summed goal -> start
+        vx -= __shfl_sync(0xFFFFFFFFu, dx, m); vy -= __shfl_sync(0xFFFFFFFFu, dy, m); vz -= __shfl_sync(0xFFFFFFFFu, dz, m);
         if (n > (int64_t)G.pcells) { result = 0; c = INF_D; break; }
     }
     if (lane == 0) { plen[q] = result; cost[q] = c; }

@@ -88,6 +88,7 @@ struct TileSmem {
     u64 kmin[2];            // min key of the pending cells (computed on empty sub-iterations)
     u64 T, U, k0;
     u32 chg[C::NCW];        // cells (tile + halo, by halo'd index) lowered during this activation
+    ulonglong2 fq[NT / 32][C::NCELL / (NT / 32)]; // per-warp frontier records: .x = value, .y = free mask | halo'd index << 32
     u64 stat[16];           // per-CTA counters (flushed at kernel end)
     u64 tm[6];              // CTA 0's phase timers: t0, scan, proc, wait, ta/tb scratch
     u32 item, n_edge, n_exp;
@@ -101,6 +102,8 @@ struct SsspArgs {
     // directions not in the motion table have need = all-ones (never satisfied).
     u64 wdir[27];
     u32 need[27];
+    int ndir, dpl_log2;       // number of motions; lanes per cell in the expansion = 1 << dpl_log2 (>= ndir)
+    unsigned char dirs[32];   // canonical direction handled by lane index i of a lane group (13 = none)
     u32 nq, ring_cap;
     const int32_t *starts, *goals;
     void *g;
@@ -241,12 +244,15 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         hh[j] = use_h ? heuristic_lo(ox + lx - gx, oy + ly - gy, oz + lz - gz, A.he, A.hm) : 0.0;
     }
 
-    // direction handled by this lane in the warp-cooperative expansion
-    const int grp = lane / C::DPL, didx = lane % C::DPL;
-    const int dcan = C::TZ == 1 ? (didx < 9 ? 9 + didx : 13) : (didx < 27 ? didx : 13);
-    const u32 my_need = A.need[dcan]; // all-ones for the centre / unused directions
+    // direction handled by this lane in the warp-cooperative expansion: a group of 2^dpl_log2 lanes
+    // (8 for up to 8 motions, 16, or 32) works on one frontier cell, one lane per motion
+    const int dpl_log2 = A.dpl_log2;
+    const int grp = lane >> dpl_log2, ngrp = 32 >> dpl_log2;
+    const int dcan = A.dirs[lane & ((1 << dpl_log2) - 1)];
+    const u32 my_need = A.need[dcan]; // all-ones for unused lanes
     const u64 my_w = A.wdir[dcan];
     const int my_off = ((dcan / 9 - 1) * C::HY + ((dcan / 3) % 3 - 1)) * C::HX + (dcan % 3 - 1);
+    ulonglong2 *wq = S.fq[tid >> 5];
 
     const u32 t_loaded = (u32)clock64();
     const u64 T = S.T, U = S.U;
@@ -259,66 +265,81 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     }
     u64 km_final = KEY_INF;
     u32 n_exp = 0, n_iter = 0, my_edges = 0, n_empty = 0;
+#ifdef PMP_PROF
+    u32 pc[3] = {0, 0, 0};
+#endif
     for (;;) {
         G gv[CPT];
 #pragma unroll
         for (int j = 0; j < CPT; ++j) gv[j] = W::dec(S.g[C::own_hi(tid, j)]);
         u64 lmin = KEY_INF;
-        int anyact = 0;
+        bool act[CPT];
+        u32 am[CPT], tot = 0;
+#ifdef PMP_PROF
+        const u32 pk0 = (u32)clock64();
+#endif
 #pragma unroll
         for (int j = 0; j < CPT; ++j) {
-            bool act = false;
+            act[j] = false;
             if (gv[j] < gprop[j]) { // pending
                 const u64 k = use_h ? W::key(gv[j], hh[j]) : (u64)gv[j];
-                if (k < B) { act = true; gprop[j] = gv[j]; ++n_exp; }
+                if (k < B) { act[j] = true; gprop[j] = gv[j]; ++n_exp; }
                 else lmin = k < lmin ? k : lmin;
             }
+            am[j] = __ballot_sync(0xFFFFFFFFu, act[j]);
+            tot += __popc(am[j]);
+        }
+        const int anyact = tot != 0;
+#ifdef PMP_PROF
+        const u32 pk1 = (u32)clock64();
+#endif
+        if (tot) {
             // ---- warp-cooperative expansion: the frontier cells owned by this warp's lanes are
-            // expanded NG at a time, one lane per canonical direction: broadcast the cell from its
-            // owner lane, test the edge, read the target, one compare-and-swap if it improves.
-            u32 m = __ballot_sync(0xFFFFFFFFu, act);
-            anyact |= m != 0;
-            while (m) {
-                int src = -1;
+            // written as records into the warp's queue, then expanded ngrp at a time, one lane per
+            // motion: test the edge, read the target, one compare-and-swap if it improves.
+            u32 base = 0;
 #pragma unroll
-                for (int gI = 0; gI < C::NG; ++gI) {
-                    if (m) {
-                        if (gI == grp) src = __ffs(m) - 1;
-                        m &= m - 1;
+            for (int j = 0; j < CPT; ++j) {
+                if (act[j])
+                    wq[base + __popc(am[j] & ((1u << lane) - 1u))] =
+                        make_ulonglong2((u64)gv[j], (u64)F[j] | ((u64)(u32)C::own_hi(tid, j) << 32));
+                base += __popc(am[j]);
+            }
+            __syncwarp();
+            for (u32 r = grp; r < tot; r += ngrp) {
+                const ulonglong2 rec = wq[r];
+                const u32 fm = (u32)rec.y;
+                if ((fm & my_need) != my_need) continue; // isCollision: target / face cells occupied
+                ++my_edges;
+                const int vhi = (int)(rec.y >> 32) + my_off;
+                const G tvr = S.g[vhi];
+                const G cand = W::addw((G)rec.x, my_w);
+                if (cand >= W::dec(tvr)) continue;
+                if (U != KEY_INF) { // cannot be on a better path to the goal?
+                    double hv = 0.0;
+                    if (use_h) {
+                        const int hx = vhi % C::HX, hy = (vhi / C::HX) % C::HY, hz = vhi / (C::HX * C::HY);
+                        hv = heuristic_lo(ox + hx - 1 - gx, oy + hy - 1 - gy, oz + hz - C::ZH - gz, A.he, A.hm);
                     }
+                    if (W::key(cand, hv) > U) continue;
                 }
-                const int s = src < 0 ? 0 : src;
-                const int hj = C::own_hi((tid & ~31) + s, j);
-                const u32 fm = __shfl_sync(0xFFFFFFFFu, F[j], s);
-                const G gu = __shfl_sync(0xFFFFFFFFu, gv[j], s);
-                if (src >= 0 && (fm & my_need) == my_need) { // isCollision: target / face cells free
-                    ++my_edges;
-                    const int vhi = hj + my_off;
-                    const G tvr = S.g[vhi];
-                    const G cand = W::addw(gu, my_w);
-                    if (cand < W::dec(tvr)) {
-                        bool keep = true;
-                        if (U != KEY_INF) { // cannot be on a better path to the goal?
-                            double hv = 0.0;
-                            if (use_h) {
-                                const int hx = vhi % C::HX, hy = (vhi / C::HX) % C::HY, hz = vhi / (C::HX * C::HY);
-                                hv = heuristic_lo(ox + hx - 1 - gx, oy + hy - 1 - gy, oz + hz - C::ZH - gz, A.he, A.hm);
-                            }
-                            keep = W::key(cand, hv) <= U;
-                        }
-                        if (keep) {
-                            const G want = W::enc(cand, true);
-                            const G old = atomicCAS(&S.g[vhi], tvr, want);
-                            bool won = old == tvr;
-                            if (!won && want < old) won = smem_min(&S.g[vhi], want); // raced with a worse value
-                            if (won) atomicOr(&S.chg[vhi >> 5], 1u << (vhi & 31));
-                        }
-                    }
-                }
+                const G want = W::enc(cand, true);
+                const G old = atomicCAS(&S.g[vhi], tvr, want);
+                bool won = old == tvr;
+                if (!won && want < old) won = smem_min(&S.g[vhi], want); // raced with a worse value
+                if (won) atomicOr(&S.chg[vhi >> 5], 1u << (vhi & 31));
             }
         }
         ++n_iter;
+#ifdef PMP_PROF
+        const u32 pk2 = (u32)clock64();
+        const int vote = __syncthreads_or(anyact);
+        const u32 pk3 = (u32)clock64();
+        pc[0] += pk1 - pk0; pc[1] += pk2 - pk1; pc[2] += pk3 - pk2;
+        if (vote) {
+#else
         if (__syncthreads_or(anyact)) {
+#endif
             const u64 nb = W::key_add(B, A.sub);
             B = nb < T ? nb : T;
             continue;
@@ -380,6 +401,13 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         my_edges += __shfl_down_sync(0xFFFFFFFFu, my_edges, o);
         n_exp += __shfl_down_sync(0xFFFFFFFFu, n_exp, o);
     }
+#ifdef PMP_PROF
+    if (lane == 0) {
+        atomicAdd((unsigned long long *)&S.stat[13], (unsigned long long)pc[0]);
+        atomicAdd((unsigned long long *)&S.stat[14], (unsigned long long)pc[1]);
+        atomicAdd((unsigned long long *)&S.stat[15], (unsigned long long)pc[2]);
+    }
+#endif
     if (lane == 0) {
         if (my_edges) atomicAdd(&S.n_edge, my_edges);
         if (n_exp) atomicAdd(&S.n_exp, n_exp);
@@ -541,7 +569,7 @@ __global__ void __launch_bounds__(NT, PMP_MINB) k_sssp(const __grid_constant__ S
         }
     }
     __syncthreads();
-    if (tid < 16 && tid != 0 && tid != 4 && (tid < 8 || tid == 12) && S.stat[tid]) atomicAdd(&A.stats[tid], S.stat[tid]);
+    if (tid < 16 && tid != 0 && tid != 4 && (tid < 8 || tid >= 12) && S.stat[tid]) atomicAdd(&A.stats[tid], S.stat[tid]);
     if (timer) {
         A.stats[8] = globaltimer_ns() - S.tm[0];
         A.stats[9] = S.tm[1]; A.stats[10] = S.tm[2]; A.stats[11] = S.tm[3];
@@ -755,6 +783,11 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
         if (A.need[d] == 0xFFFFFFFFu || w < A.wdir[d]) A.wdir[d] = w; // duplicate offsets: cheapest
         A.need[d] = g->mot.need[m];
     }
+    A.ndir = 0;
+    for (int i = 0; i < 32; ++i) A.dirs[i] = 13; // centre: need = all-ones
+    for (int d = 0; d < 27; ++d)
+        if (A.need[d] != 0xFFFFFFFFu) A.dirs[A.ndir++] = (unsigned char)d;
+    A.dpl_log2 = A.ndir <= 8 ? 3 : (A.ndir <= 16 ? 4 : 5);
     A.nq = (u32)nq;
     A.ring_cap = (u32)((size_t)nq * g->d.ntiles + RING_SLACK);
     A.starts = starts_dev;
@@ -787,8 +820,9 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
     // Default key window per round.  Inside a round tiles cascade asynchronously, so the window
     // only bounds how far ahead of the smallest pending key work may run: wide for full sweeps
     // (few rounds), narrow for A-star, whose keys g + h span a small range and where everything
-    // above the final cost is wasted.
-    if (!(window > 0.0)) window = (A.use_h ? 6.0 : (g->d.ndim == 2 ? 48.0 : 24.0)) * g->wmin;
+    // above the final cost is wasted.  Integer (unit) weights re-relax least when run far ahead.
+    if (!(window > 0.0))
+        window = (A.use_h ? 6.0 : (P->weight == PMP_W_U32 ? 256.0 : 48.0)) * g->wmin;
     if (P->weight == PMP_W_U32 && window < 1.0) window = 1.0;
     A.window = window;
 
