@@ -135,7 +135,20 @@ def build_workload(args, rank, torch, pmp, workloads):
             cost, path, expand = pmp.AStar3D(start, goal, env).plan()   # H2D query, D2H cost + path
             return cost, host_occ.numel() + 24, 32 + 4 * len(path)
 
-        return dict(run=run, account=account, e2e=e2e, name=name, dtype="f64", queries=1, stats=lambda: ws.stats.cpu().numpy(),
+        def phases():
+            """device time of the pieces of one step, each timed alone with CUDA events"""
+            out = {}
+            for nm, fn in (("search_ms", lambda: engine.sssp(ws, _lib.ASTAR, 0)),
+                           ("extract_ms", lambda: engine.extract_paths(ws, path_cap))):
+                ts = []
+                for _ in range(3):
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+                    ts.append(e0.elapsed_time(e1))
+                out[nm] = min(ts)
+            return out
+
+        return dict(run=run, account=account, e2e=e2e, name=name, dtype="f64", queries=1, stats=lambda: ws.stats.cpu().numpy(), phases=phases,
                     cfg={"grid": list(dims), "connectivity": 26, "heuristic": "euclidean",
                          "free_cells": int((~occ).sum())}, occ=occ, start=start, goal=goal)
     if wl == "c3":
@@ -388,6 +401,8 @@ def main():
                      "kernel": "k_sssp (+init/finish/extract, ~1% of the step)",
                      "algorithmic_bytes_per_step": abytes},
     }
+    if "phases" in W:
+        line["phases"] = W["phases"]()
     if st:
         mhz = (clocks.get("sm_mhz") or 1965.0)
         nt = max(st[1], 1)

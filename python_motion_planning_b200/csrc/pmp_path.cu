@@ -89,6 +89,19 @@ __global__ void k_extract_paths(const GridDev G, const __grid_constant__ Motions
         c += __shfl_sync(0xFFFFFFFFu, mylen, m); // Planner.dist (planner.py:22-23): hypot of the step, summed goal -> start
         vx -= __shfl_sync(0xFFFFFFFFu, dx, m); vy -= __shfl_sync(0xFFFFFFFFu, dy, m); vz -= __shfl_sync(0xFFFFFFFFu, dz, m);
         if (n > (int64_t)G.pcells) { result = 0; c = INF_D; break; }
+        // The walk is one dependent L2 round trip per step unless the lines are already in L1:
+        // prefetch the rows within distance 3 of the new cell (needed two steps from now).
+        const int zr = G.ndim == 3 ? 3 : 0, nrow = 7 * (2 * zr + 1);
+        for (int r = lane; r < nrow; r += 32) {
+            const int py = vy + r % 7 - 3, pz = vz + r / 7 - zr;
+            if ((unsigned)py < (unsigned)G.PY && (unsigned)pz < (unsigned)G.PZ) {
+                const size_t row = (size_t)pz * G.PY + py;
+                const int x0 = vx - 4 < 0 ? 0 : vx - 4, x1 = vx + 4 >= G.PX ? G.PX - 1 : vx + 4;
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(gq + row * G.PX + x0));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(gq + row * G.PX + x1));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(G.bits + row * G.wpr + (vx >> 5)));
+            }
+        }
     }
     if (lane == 0) { plen[q] = result; cost[q] = c; }
 }

@@ -306,28 +306,61 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
                 base += __popc(am[j]);
             }
             __syncwarp();
-            for (u32 r = grp; r < tot; r += ngrp) {
-                const ulonglong2 rec = wq[r];
-                const u32 fm = (u32)rec.y;
-                if ((fm & my_need) != my_need) continue; // isCollision: target / face cells occupied
-                ++my_edges;
-                const int vhi = (int)(rec.y >> 32) + my_off;
-                const G tvr = S.g[vhi];
-                const G cand = W::addw((G)rec.x, my_w);
-                if (cand >= W::dec(tvr)) continue;
-                if (U != KEY_INF) { // cannot be on a better path to the goal?
-                    double hv = 0.0;
-                    if (use_h) {
-                        const int hx = vhi % C::HX, hy = (vhi / C::HX) % C::HY, hz = vhi / (C::HX * C::HY);
-                        hv = heuristic_lo(ox + hx - 1 - gx, oy + hy - 1 - gy, oz + hz - C::ZH - gz, A.he, A.hm);
+            // records are taken NB at a time so that the shared-memory round trips (record, target,
+            // compare-and-swap, flag) of different cells overlap instead of forming one chain
+#ifndef PMP_NB
+#define PMP_NB 1
+#endif
+            constexpr int NB = PMP_NB;
+            for (u32 r0 = grp; r0 < tot; r0 += ngrp * NB) {
+                int vhi[NB];
+                G tvr[NB], cand[NB];
+                bool go[NB];
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    const u32 r = r0 + b * ngrp;
+                    go[b] = false;
+                    vhi[b] = 0;
+                    tvr[b] = 0;
+                    cand[b] = 0;
+                    if (r < tot) {
+                        const ulonglong2 rec = wq[r];
+                        const u32 fm = (u32)rec.y;
+                        if ((fm & my_need) == my_need) { // isCollision: target / face cells free
+                            ++my_edges;
+                            vhi[b] = (int)(rec.y >> 32) + my_off;
+                            tvr[b] = S.g[vhi[b]];
+                            cand[b] = W::addw((G)rec.x, my_w);
+                            go[b] = true;
+                        }
                     }
-                    if (W::key(cand, hv) > U) continue;
                 }
-                const G want = W::enc(cand, true);
-                const G old = atomicCAS(&S.g[vhi], tvr, want);
-                bool won = old == tvr;
-                if (!won && want < old) won = smem_min(&S.g[vhi], want); // raced with a worse value
-                if (won) atomicOr(&S.chg[vhi >> 5], 1u << (vhi & 31));
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    go[b] = go[b] && cand[b] < W::dec(tvr[b]);
+                    if (go[b] && U != KEY_INF) { // cannot be on a better path to the goal?
+                        double hv = 0.0;
+                        if (use_h) {
+                            const int hx = vhi[b] % C::HX, hy = (vhi[b] / C::HX) % C::HY, hz = vhi[b] / (C::HX * C::HY);
+                            hv = heuristic_lo(ox + hx - 1 - gx, oy + hy - 1 - gy, oz + hz - C::ZH - gz, A.he, A.hm);
+                        }
+                        go[b] = W::key(cand[b], hv) <= U;
+                    }
+                }
+                G old[NB];
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    old[b] = 0;
+                    if (go[b]) old[b] = atomicCAS(&S.g[vhi[b]], tvr[b], W::enc(cand[b], true));
+                }
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    if (!go[b]) continue;
+                    const G want = W::enc(cand[b], true);
+                    bool won = old[b] == tvr[b];
+                    if (!won && want < old[b]) won = smem_min(&S.g[vhi[b]], want); // raced with a worse value
+                    if (won) atomicOr(&S.chg[vhi[b] >> 5], 1u << (vhi[b] & 31));
+                }
             }
         }
         ++n_iter;
