@@ -92,6 +92,7 @@ struct TileSmem {
     u64 stat[16];           // per-CTA counters (flushed at kernel end)
     u64 tm[6];              // CTA 0's phase timers: t0, scan, proc, wait, ta/tb scratch
     u32 item, n_edge, n_exp;
+    u32 fqn[2];             // records in the CTA-wide queue (double-buffered by sub-iteration parity)
     u32 s_live, s_wl_base;
 };
 
@@ -137,6 +138,36 @@ __device__ static inline u64 warp_min_u64(u64 v) {
         v = other < v ? other : v;
     }
     return v;
+}
+
+// One frontier record against this lane's motion.
+template <class C>
+__device__ __forceinline__ void relax_record(TileSmem<C> &S, const SsspArgs &A, const ulonglong2 rec,
+                                             const u32 my_need, const u64 my_w, const int my_off,
+                                             const u64 U, const int use_h, const int rx, const int ry,
+                                             const int rz, u32 &my_edges) {
+    typedef typename C::W W;
+    typedef typename C::G G;
+    const u32 fm = (u32)rec.y;
+    if ((fm & my_need) != my_need) return; // isCollision: target / face cells occupied
+    ++my_edges;
+    const int vhi = (int)(rec.y >> 32) + my_off;
+    const G tvr = S.g[vhi];
+    const G cand = W::addw((G)rec.x, my_w);
+    if (cand >= W::dec(tvr)) return;
+    if (U != KEY_INF) { // cannot be on a better path to the goal?
+        double hv = 0.0;
+        if (use_h) {
+            const int hx = vhi % C::HX, hy = (vhi / C::HX) % C::HY, hz = vhi / (C::HX * C::HY);
+            hv = heuristic_lo(rx + hx - 1, ry + hy - 1, rz + hz - C::ZH, A.he, A.hm);
+        }
+        if (W::key(cand, hv) > U) return;
+    }
+    const G want = W::enc(cand, true);
+    const G old = atomicCAS(&S.g[vhi], tvr, want);
+    bool won = old == tvr;
+    if (!won && want < old) won = smem_min(&S.g[vhi], want); // raced with a worse value
+    if (won) atomicOr(&S.chg[vhi >> 5], 1u << (vhi & 31));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -188,6 +219,7 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         S.U = U;
     } else if (tid == 96) {
         S.kmin[0] = S.kmin[1] = KEY_INF;
+        S.fqn[0] = S.fqn[1] = 0;
     }
     if (tid >= 128 && tid < 128 + 27) S.nbrmin[tid - 128] = KEY_INF;
     if (tid >= NT - C::NROWS) { // occupancy never changes during a search: no ordering needed
@@ -293,86 +325,53 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
 #ifdef PMP_PROF
         const u32 pk1 = (u32)clock64();
 #endif
-        if (tot) {
-            // ---- warp-cooperative expansion: the frontier cells owned by this warp's lanes are
-            // written as records into the warp's queue, then expanded ngrp at a time, one lane per
-            // motion: test the edge, read the target, one compare-and-swap if it improves.
-            u32 base = 0;
+        // ---- warp-cooperative expansion: frontier cells become records in shared memory and are
+        // expanded one lane per motion: test the edge, read the target, one compare-and-swap if it
+        // improves.  With more than 16 motions a cell takes a whole warp, so the records of all
+        // warps go into one CTA-wide queue and are dealt round-robin to the 8 warps (one extra
+        // barrier, but a skewed frontier no longer serialises on one warp); with fewer motions
+        // each warp expands the cells its own lanes own, 2-4 at a time.
+        int vote;
+        if (dpl_log2 == 5) {
+            const int pb = n_iter & 1;
+            ulonglong2 *cq = &S.fq[0][0];
+            if (tot) {
+                u32 base = 0;
+                if (lane == 0) base = atomicAdd(&S.fqn[pb], tot);
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
 #pragma unroll
-            for (int j = 0; j < CPT; ++j) {
-                if (act[j])
-                    wq[base + __popc(am[j] & ((1u << lane) - 1u))] =
-                        make_ulonglong2((u64)gv[j], (u64)F[j] | ((u64)(u32)C::own_hi(tid, j) << 32));
-                base += __popc(am[j]);
-            }
-            __syncwarp();
-            // records are taken NB at a time so that the shared-memory round trips (record, target,
-            // compare-and-swap, flag) of different cells overlap instead of forming one chain
-#ifndef PMP_NB
-#define PMP_NB 1
-#endif
-            constexpr int NB = PMP_NB;
-            for (u32 r0 = grp; r0 < tot; r0 += ngrp * NB) {
-                int vhi[NB];
-                G tvr[NB], cand[NB];
-                bool go[NB];
-#pragma unroll
-                for (int b = 0; b < NB; ++b) {
-                    const u32 r = r0 + b * ngrp;
-                    go[b] = false;
-                    vhi[b] = 0;
-                    tvr[b] = 0;
-                    cand[b] = 0;
-                    if (r < tot) {
-                        const ulonglong2 rec = wq[r];
-                        const u32 fm = (u32)rec.y;
-                        if ((fm & my_need) == my_need) { // isCollision: target / face cells free
-                            ++my_edges;
-                            vhi[b] = (int)(rec.y >> 32) + my_off;
-                            tvr[b] = S.g[vhi[b]];
-                            cand[b] = W::addw((G)rec.x, my_w);
-                            go[b] = true;
-                        }
-                    }
-                }
-#pragma unroll
-                for (int b = 0; b < NB; ++b) {
-                    go[b] = go[b] && cand[b] < W::dec(tvr[b]);
-                    if (go[b] && U != KEY_INF) { // cannot be on a better path to the goal?
-                        double hv = 0.0;
-                        if (use_h) {
-                            const int hx = vhi[b] % C::HX, hy = (vhi[b] / C::HX) % C::HY, hz = vhi[b] / (C::HX * C::HY);
-                            hv = heuristic_lo(ox + hx - 1 - gx, oy + hy - 1 - gy, oz + hz - C::ZH - gz, A.he, A.hm);
-                        }
-                        go[b] = W::key(cand[b], hv) <= U;
-                    }
-                }
-                G old[NB];
-#pragma unroll
-                for (int b = 0; b < NB; ++b) {
-                    old[b] = 0;
-                    if (go[b]) old[b] = atomicCAS(&S.g[vhi[b]], tvr[b], W::enc(cand[b], true));
-                }
-#pragma unroll
-                for (int b = 0; b < NB; ++b) {
-                    if (!go[b]) continue;
-                    const G want = W::enc(cand[b], true);
-                    bool won = old[b] == tvr[b];
-                    if (!won && want < old[b]) won = smem_min(&S.g[vhi[b]], want); // raced with a worse value
-                    if (won) atomicOr(&S.chg[vhi[b] >> 5], 1u << (vhi[b] & 31));
+                for (int j = 0; j < CPT; ++j) {
+                    if (act[j])
+                        cq[base + __popc(am[j] & ((1u << lane) - 1u))] =
+                            make_ulonglong2((u64)gv[j], (u64)F[j] | ((u64)(u32)C::own_hi(tid, j) << 32));
+                    base += __popc(am[j]);
                 }
             }
+            __syncthreads();
+            const u32 n = S.fqn[pb];
+            if (tid == 0) S.fqn[pb ^ 1] = 0;
+            for (u32 r = tid >> 5; r < n; r += NT / 32)
+                relax_record<C>(S, A, cq[r], my_need, my_w, my_off, U, use_h, ox - gx, oy - gy, oz - gz, my_edges);
+            vote = n != 0;
+            if (vote) __syncthreads(); // every relaxation lands before the next scan
+        } else {
+            if (tot) {
+                u32 base = 0;
+#pragma unroll
+                for (int j = 0; j < CPT; ++j) {
+                    if (act[j])
+                        wq[base + __popc(am[j] & ((1u << lane) - 1u))] =
+                            make_ulonglong2((u64)gv[j], (u64)F[j] | ((u64)(u32)C::own_hi(tid, j) << 32));
+                    base += __popc(am[j]);
+                }
+                __syncwarp();
+                for (u32 r = grp; r < tot; r += ngrp)
+                    relax_record<C>(S, A, wq[r], my_need, my_w, my_off, U, use_h, ox - gx, oy - gy, oz - gz, my_edges);
+            }
+            vote = __syncthreads_or(anyact);
         }
         ++n_iter;
-#ifdef PMP_PROF
-        const u32 pk2 = (u32)clock64();
-        const int vote = __syncthreads_or(anyact);
-        const u32 pk3 = (u32)clock64();
-        pc[0] += pk1 - pk0; pc[1] += pk2 - pk1; pc[2] += pk3 - pk2;
         if (vote) {
-#else
-        if (__syncthreads_or(anyact)) {
-#endif
             const u64 nb = W::key_add(B, A.sub);
             B = nb < T ? nb : T;
             continue;
