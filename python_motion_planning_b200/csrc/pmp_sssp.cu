@@ -109,7 +109,7 @@ struct SsspArgs {
     const int32_t *starts, *goals;
     void *g;
     u64 *minkey;
-    u32 *wl[2];    // [0] ring of queued (query, tile) ids + 1 (0 = empty slot), [1] per-tile "in queue" flag
+    u32 *wl[2];    // [0] ring of queued (query, tile) ids + 1 (0 = empty slot), [1] unused
     u64 *qmin[2];
     u64 *T[2];
     int *done;
@@ -198,20 +198,21 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     const int use_h = A.use_h;
     int gx = 0, gy = 0, gz = 0;
     if (use_h) {
-        gx = A.goals[3 * q]; gy = A.goals[3 * q + 1]; gz = Gd.ndim == 3 ? A.goals[3 * q + 2] : 0;
+        gx = __ldg(A.goals + 3 * q); gy = __ldg(A.goals + 3 * q + 1); gz = Gd.ndim == 3 ? __ldg(A.goals + 3 * q + 2) : 0;
     }
 
     const u32 t_begin = (u32)clock64();
     // ---- prologue: the dependent global round trips are spread over different warps ----
     if (tid == 0) {
-        atomicExch(&A.wl[1][gt], 0u);              // leave the queue: later pushes append the tile again
-        S.k0 = atomicExch(&A.minkey[gt], KEY_INF); // claim: later pushes re-arm the tile
+        // claim.  Invariant: a tile is in the ring iff its minkey is below the window bound T, so
+        // resetting minkey also "leaves the queue": a later push below T appends the tile again.
+        S.k0 = atomicExch(&A.minkey[gt], KEY_INF);
         fence_gpu();
     } else if (tid == 32) {
         S.T = ld_cg(&A.T[cur][q]);
     } else if (tid == 64) {
         u64 U = KEY_INF;
-        const u32 gc = A.full_field ? 0xFFFFFFFFu : A.goalcell[q];
+        const u32 gc = A.full_field ? 0xFFFFFFFFu : __ldg(A.goalcell + q);
         if (gc != 0xFFFFFFFFu) {
             const G gg = W::dec(ld_cg(gq + gc));
             if (gg != W::inf()) U = W::key(gg, 0.0);
@@ -230,7 +231,12 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     for (int i = tid; i < C::NCW; i += NT) S.chg[i] = 0;
     __syncthreads(); // the claim is ordered before every load of g below
 
-    // ---- stage the raw cost words (tile + halo) ----
+    // ---- stage the raw cost words (tile + halo); while the loads are in flight, set up the
+    // per-thread state of the owned cells that depends only on the occupancy and the position ----
+    u32 F[CPT];
+    G gprop[CPT];
+    double hh[CPT];
+    u32 ldp = 0; // owned cells that were flagged pending in global memory
     {
         G raw[NLD];
 #pragma unroll
@@ -243,37 +249,33 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
                 raw[k] = ld_cg(gq + ((size_t)z * Gd.PY + y) * Gd.PX + x);
         }
 #pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            int lx, ly, lz;
+            C::owned(tid, j, lx, ly, lz);
+            u32 occ27 = 0; // occupancy of the 3x3(x3) neighbourhood from the staged rows
+#pragma unroll
+            for (int dzz = -C::ZH; dzz <= C::ZH; ++dzz)
+#pragma unroll
+                for (int dyy = -1; dyy <= 1; ++dyy) {
+                    const u64 r = S.rows[(lz + C::ZH + dzz) * C::HY + (ly + 1 + dyy)];
+                    occ27 |= (u32)((r >> lx) & 7ull) << ((dzz + 1) * 9 + (dyy + 1) * 3);
+                }
+            F[j] = ~occ27 & 0x7FFFFFFu;
+            hh[j] = use_h ? heuristic_lo(ox + lx - gx, oy + ly - gy, oz + lz - gz, A.he, A.hm) : 0.0;
+        }
+#pragma unroll
         for (int k = 0; k < NLD; ++k) {
             const int i = tid + k * NT;
             if (i < C::HC) S.g[i] = raw[k];
         }
     }
     __syncthreads();
-
-    // ---- per-thread state of the owned cells ----
-    u32 F[CPT];
-    G gprop[CPT];
-    double hh[CPT];
-    u32 ldp = 0; // owned cells that were flagged pending in global memory
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
-        int lx, ly, lz;
-        C::owned(tid, j, lx, ly, lz);
-        const int hij = C::halo_index(lx, ly, lz);
-        u32 occ27 = 0; // occupancy of the 3x3(x3) neighbourhood from the staged rows
-#pragma unroll
-        for (int dzz = -C::ZH; dzz <= C::ZH; ++dzz)
-#pragma unroll
-            for (int dyy = -1; dyy <= 1; ++dyy) {
-                const u64 r = S.rows[(lz + C::ZH + dzz) * C::HY + (ly + 1 + dyy)];
-                occ27 |= (u32)((r >> lx) & 7ull) << ((dzz + 1) * 9 + (dyy + 1) * 3);
-            }
-        F[j] = ~occ27 & 0x7FFFFFFu;
-        const G sw = S.g[hij];
-        const bool pend = !(sw & 1) ;
+        const G sw = S.g[C::own_hi(tid, j)];
+        const bool pend = !(sw & 1);
         gprop[j] = pend ? W::inf() : W::dec(sw);
         if (pend) ldp |= 1u << j;
-        hh[j] = use_h ? heuristic_lo(ox + lx - gx, oy + ly - gy, oz + lz - gz, A.he, A.hm) : 0.0;
     }
 
     // direction handled by this lane in the warp-cooperative expansion: a group of 2^dpl_log2 lanes
@@ -453,8 +455,8 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         if (k != KEY_INF) {
             const int sx = tid % 3 - 1, sy = (tid / 3) % 3 - 1, sz = tid / 9 - 1;
             const u32 ngt = q * Gd.ntiles + (u32)(((ttz + sz) * Gd.nty + (tty + sy)) * Gd.ntx + (ttx + sx));
-            atomicMin(&A.minkey[ngt], k);
-            if (k < T && atomicExch(&A.wl[1][ngt], 1u) == 0) { // inside the window and not queued yet
+            const u64 was = atomicMin(&A.minkey[ngt], k);
+            if (k < T && was >= T) { // enters the window now: not queued yet (see the claim)
                 atomicAdd(&A.ctr[6 + cur], 1u);
                 const u32 pos = atomicAdd(&A.ctr[cur], 1u);
                 *(volatile u32 *)&A.wl[0][pos % A.ring_cap] = ngt + 1u;
@@ -516,7 +518,6 @@ __global__ void __launch_bounds__(NT, PMP_MINB) k_sssp(const __grid_constant__ S
                 }
             }
             my_live += live;
-            if (take) take = atomicExch(&A.wl[1][gt], 1u) == 0; // the "in queue" flag
             const u32 m = __ballot_sync(0xFFFFFFFFu, take);
             if (m) {
                 u32 pos = 0;
@@ -582,7 +583,7 @@ __global__ void __launch_bounds__(NT, PMP_MINB) k_sssp(const __grid_constant__ S
                     if (ns < 160) ns *= 2;
                     if (++spins > (1u << 22)) { A.stats[15] = 0xDEADu; break; } // safety net (seconds)
                 }
-                if (v) { *(volatile u32 *)slot = 0; fence_gpu(); }
+                if (v) { fence_gpu(); *(volatile u32 *)slot = 0; } // acquire, then recycle the slot
                 S.item = v;
             }
             __syncthreads();
@@ -895,7 +896,6 @@ extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
     const size_t nt = (size_t)nq * g->d.ntiles;
     PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, nt * 8, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[0], 0, (nt + RING_SLACK) * 4, s));
-    PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[1], 0, nt * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 16 * 8, s));
 
@@ -1013,7 +1013,6 @@ extern "C" int pmp_slab_begin(pmp_grid *g, const pmp_sssp_params *P, const int32
     PMP_CHECK_CUDA(cudaMemsetAsync(g_dev, 0xFF, (size_t)g->d.pcells * (Q.weight == PMP_W_F64 ? 8 : 4), s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, (size_t)g->d.ntiles * 8, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[0], 0, ((size_t)g->d.ntiles + RING_SLACK) * 4, s));
-    PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[1], 0, (size_t)g->d.ntiles * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 16 * 8, s));
     if (start_dev) return dispatch_sssp(g, Q.weight, A, nullptr, nullptr, s, 1);
