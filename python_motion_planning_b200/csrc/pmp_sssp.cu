@@ -299,9 +299,6 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     }
     u64 km_final = KEY_INF;
     u32 n_exp = 0, n_iter = 0, my_edges = 0, n_empty = 0;
-#ifdef PMP_PROF
-    u32 pc[3] = {0, 0, 0};
-#endif
     for (;;) {
         G gv[CPT];
 #pragma unroll
@@ -309,9 +306,6 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         u64 lmin = KEY_INF;
         bool act[CPT];
         u32 am[CPT], tot = 0;
-#ifdef PMP_PROF
-        const u32 pk0 = (u32)clock64();
-#endif
 #pragma unroll
         for (int j = 0; j < CPT; ++j) {
             act[j] = false;
@@ -324,9 +318,6 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
             tot += __popc(am[j]);
         }
         const int anyact = tot != 0;
-#ifdef PMP_PROF
-        const u32 pk1 = (u32)clock64();
-#endif
         // ---- warp-cooperative expansion: frontier cells become records in shared memory and are
         // expanded one lane per motion: test the edge, read the target, one compare-and-swap if it
         // improves.  With more than 16 motions a cell takes a whole warp, so the records of all
@@ -435,13 +426,6 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         my_edges += __shfl_down_sync(0xFFFFFFFFu, my_edges, o);
         n_exp += __shfl_down_sync(0xFFFFFFFFu, n_exp, o);
     }
-#ifdef PMP_PROF
-    if (lane == 0) {
-        atomicAdd((unsigned long long *)&S.stat[13], (unsigned long long)pc[0]);
-        atomicAdd((unsigned long long *)&S.stat[14], (unsigned long long)pc[1]);
-        atomicAdd((unsigned long long *)&S.stat[15], (unsigned long long)pc[2]);
-    }
-#endif
     if (lane == 0) {
         if (my_edges) atomicAdd(&S.n_edge, my_edges);
         if (n_exp) atomicAdd(&S.n_exp, n_exp);
@@ -602,7 +586,7 @@ __global__ void __launch_bounds__(NT, PMP_MINB) k_sssp(const __grid_constant__ S
         }
     }
     __syncthreads();
-    if (tid < 16 && tid != 0 && tid != 4 && (tid < 8 || tid >= 12) && S.stat[tid]) atomicAdd(&A.stats[tid], S.stat[tid]);
+    if (tid < 16 && tid != 0 && tid != 4 && (tid < 8 || tid == 12) && S.stat[tid]) atomicAdd(&A.stats[tid], S.stat[tid]);
     if (timer) {
         A.stats[8] = globaltimer_ns() - S.tm[0];
         A.stats[9] = S.tm[1]; A.stats[10] = S.tm[2]; A.stats[11] = S.tm[3];

@@ -11,7 +11,7 @@ def fmt(st):
     mhz = 1900.0
     return (f"rounds {st[0]} tiles {st[1]} cells {st[2]} edges {st[3]} wlmax {st[4]} | per-tile us load {st[5]/max(st[1],1)/mhz:.1f} "
             f"settle {st[6]/max(st[1],1)/mhz:.1f} publish {st[7]/max(st[1],1)/mhz:.1f} iters/tile {st[12]/max(st[1],1):.1f} | kernel {st[8]/1e6:.2f} ms: "
-            f"scan {st[9]/1e6:.2f} proc {st[10]/1e6:.2f} wait {st[11]/1e6:.2f} | per expansion: pass1 {st[13]/max(st[2],1):.0f} cyc pass2 {st[14]/max(st[2],1):.0f} cyc improved {st[15]/max(st[2],1):.1f}; exp/iter/tile {st[2]/max(st[12],1):.1f}")
+            f"scan {st[9]/1e6:.2f} proc {st[10]/1e6:.2f} wait {st[11]/1e6:.2f}")
 
 def t_ms(fn, n=3):
     torch.cuda.synchronize(); out = None; ts = []
