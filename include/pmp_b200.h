@@ -73,6 +73,10 @@ int pmp_grid_layout(const pmp_grid *g, int64_t *out8);
 int pmp_grid_set_cells(pmp_grid *g, const int32_t *coords_dev, int64_t n, void *stream);
 /* Same from a dense device array occ_dev[(z*Y + y)*X + x] != 0 (unpadded box). */
 int pmp_grid_set_dense(pmp_grid *g, const uint8_t *occ_dev, void *stream);
+/* Same from a dense device array in the caller's own index order occ_dev[(x*Y + y)*Z + z] != 0 --
+ * the memory layout of a C-ordered array indexed [x, y(, z)] like the reference's coordinate
+ * tuples; transposed on the fly, no host-side or extra device pass. */
+int pmp_grid_set_dense_xyz(pmp_grid *g, const uint8_t *occ_dev, void *stream);
 /* Toggle single cells without rebuilding (obstacle edits between plans). value: 1 block, 0 free */
 int pmp_grid_edit_cells(pmp_grid *g, const int32_t *coords_dev, int64_t n, int value, void *stream);
 /* Copy the device bitmask to host: words_per_row * PY * PZ uint32 (bit x%32 of word x/32). Synchronous. */

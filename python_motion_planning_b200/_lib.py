@@ -21,7 +21,7 @@ ST_RUNNING, ST_EXHAUSTED, ST_REACHED, ST_BAD_QUERY = 0, 1, 2, 3
 SYMBOLS = (
     "pmp_last_error", "pmp_abi_version", "pmp_device_count",
     "pmp_grid_create", "pmp_grid_destroy", "pmp_grid_layout", "pmp_grid_set_cells",
-    "pmp_grid_set_dense", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
+    "pmp_grid_set_dense", "pmp_grid_set_dense_xyz", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
     "pmp_grid_set_motions", "pmp_sssp_sizes", "pmp_sssp", "pmp_field_finalize",
     "pmp_count_settled", "pmp_extract_paths", "pmp_verify_field", "pmp_gbfs",
     "pmp_slab_begin", "pmp_slab_run", "pmp_slab_merge",
@@ -77,6 +77,7 @@ def lib():
         "pmp_grid_layout": [vp, vp],
         "pmp_grid_set_cells": [vp, vp, i64, vp],
         "pmp_grid_set_dense": [vp, vp, vp],
+        "pmp_grid_set_dense_xyz": [vp, vp, vp],
         "pmp_grid_edit_cells": [vp, vp, i64, i32, vp],
         "pmp_grid_read_bits": [vp, vp, i64],
         "pmp_grid_count_free": [vp, vp],

@@ -86,6 +86,25 @@ __global__ void k_bits_pack_dense(GridDev G, u32 *bits, const uint8_t *occ) {
     }
 }
 
+// dense u8 box in the caller's own index order [(x*Y + y)*Z + z] (arrays indexed [x, y(, z)] as
+// the reference's coordinate tuples are) -> bits.  A block transposes a 32(x) x 32(z) patch
+// through shared memory: reads coalesced along z, ballots along x.
+__global__ void k_bits_pack_xyz(GridDev G, u32 *bits, const uint8_t *occ) {
+    __shared__ uint8_t tile[32][33];
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int z0 = blockIdx.x * 32, y = blockIdx.y, wx = blockIdx.z;
+    {
+        const int x = wx * 32 + ty, z = z0 + tx;
+        uint8_t v = 1; // outside the box: blocked
+        if (x < G.X && z < G.Z) v = occ[((size_t)x * G.Y + y) * G.Z + z] != 0;
+        tile[ty][tx] = v;
+    }
+    __syncthreads();
+    const u32 w = __ballot_sync(0xFFFFFFFFu, tile[tx][ty] != 0); // lane = x, warp = z
+    const int z = z0 + ty;
+    if (tx == 0 && z < G.Z) bits[((size_t)z * G.PY + y) * G.wpr + wx] = w;
+}
+
 __global__ void k_count_free(GridDev G, const u32 *bits, u64 *out) {
     const size_t n_words = (size_t)G.wpr * G.PY * G.PZ;
     u64 local = 0;
@@ -267,6 +286,18 @@ extern "C" int pmp_grid_set_dense(pmp_grid *g, const uint8_t *occ_dev, void *str
     if (!g || !occ_dev) { pmp_set_error("pmp_grid_set_dense: bad arguments"); return -1; }
     const size_t n_words = (size_t)g->d.wpr * g->d.PY * g->d.PZ;
     k_bits_pack_dense<<<blocks_for(n_words, 8), 256, 0, (cudaStream_t)stream>>>(g->d, g->bits, occ_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pmp_grid_set_dense_xyz(pmp_grid *g, const uint8_t *occ_dev, void *stream) {
+    if (!g || !occ_dev) { pmp_set_error("pmp_grid_set_dense_xyz: bad arguments"); return -1; }
+    if (g->d.Y > 65535 || g->d.wpr > 65535) { pmp_set_error("pmp_grid_set_dense_xyz: grid too wide"); return -1; }
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t n_words = (size_t)g->d.wpr * g->d.PY * g->d.PZ;
+    k_bits_reset<<<blocks_for(n_words, 256), 256, 0, s>>>(g->d, g->bits); // padding rows / planes: blocked
+    dim3 grid((unsigned)((g->d.Z + 31) / 32), (unsigned)g->d.Y, (unsigned)g->d.wpr), block(32, 32);
+    k_bits_pack_xyz<<<grid, block, 0, s>>>(g->d, g->bits, occ_dev);
     PMP_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

@@ -178,25 +178,30 @@ class DeviceGrid:
         self._keep = dev
 
     def set_dense(self, occ):
-        """occ: array / tensor indexed [x, y(, z)], non-zero = obstacle."""
+        """occ: array / tensor indexed [x, y(, z)], non-zero = obstacle.  One-byte element types
+        are uploaded as they are (pinned host memory -> device) and packed by a transposing
+        kernel; nothing is converted or transposed on the host."""
         t = self.torch
         if isinstance(occ, t.Tensor):
-            o = occ.to(self.device)
-            if tuple(o.shape) != self.dims:
-                raise ValueError(f"occupancy shape {tuple(o.shape)} != grid {self.dims}")
-            perm = tuple(range(self.ndim - 1, -1, -1))
-            dev = (o != 0).permute(perm).contiguous().to(t.uint8)
-            self.h2d_bytes = 0 if occ.is_cuda else occ.numel() * occ.element_size()
+            if tuple(occ.shape) != self.dims:
+                raise ValueError(f"occupancy shape {tuple(occ.shape)} != grid {self.dims}")
+            o = occ if occ.element_size() == 1 else (occ != 0)
+            o = o.contiguous()
+            self.h2d_bytes = 0 if o.is_cuda else o.numel() * o.element_size()
+            dev = o.to(self.device, non_blocking=True)
+            dev = dev.view(t.uint8)
         else:
             a = np.asarray(occ)
             if a.shape != self.dims:
                 raise ValueError(f"occupancy shape {a.shape} != grid {self.dims}")
-            zmaj = np.ascontiguousarray((a != 0).T).view(np.uint8)
-            host = t.from_numpy(zmaj)
+            if a.dtype.itemsize != 1:
+                a = a != 0
+            a = np.ascontiguousarray(a).view(np.uint8)
+            host = t.from_numpy(a)
             dev = host.pin_memory().to(self.device, non_blocking=True)
-            self.h2d_bytes = zmaj.nbytes
-        _lib.check(self.L.pmp_grid_set_dense(self.handle, dev.data_ptr(), self.stream()),
-                   "pmp_grid_set_dense")
+            self.h2d_bytes = a.nbytes
+        _lib.check(self.L.pmp_grid_set_dense_xyz(self.handle, dev.data_ptr(), self.stream()),
+                   "pmp_grid_set_dense_xyz")
         self._keep = dev
 
     def set_motions(self, offsets, costs):
