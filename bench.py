@@ -30,7 +30,13 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-ALG_BYTES = {"f64": 16.125, "u32": 8.125}   # read g + write g + 1 occupancy bit
+ALG_BYTES = {"f64": 16.125, "u32": 8.125}
+WORKLOAD_NAMES = {
+    "c4": "c4: single-query A* (euclidean), 512^3 26-connected voxel grid, random boxes",
+    "c2": "c2: examples/3d_example.py defaults, Grid3D(26,20,16) 'door', A*",
+    "c3": "c3: batched Dijkstra, 4096 queries, 1024^2 8-connected, 30% random obstacles",
+    "c5": "c5: full cost-to-go field, 768^3 6-connected unit weights (u32), single GPU",
+}   # read g + write g + 1 occupancy bit
 
 
 def measured_peak():
@@ -333,7 +339,8 @@ def main():
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": secs / max(len(ts), 1) * 1e3, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64" if args.workload != "c5" else "u32",
-                "data": "synthetic", "config": {"workload": args.workload, "sample": out["sample"]},
+                "data": "synthetic", "config": {"workload": WORKLOAD_NAMES.get(args.workload, args.workload) if not args.n else args.workload,
+                                                  "sample": out["sample"]},
                 "cpu_baseline": {"value": val, "unit": "GTEPS", "cores": out["cores"], "kind": "port",
                                  "sample": out["sample"]},
                 "queries_per_s": sum(o["queries_per_rep"] for o in ts) / secs,
