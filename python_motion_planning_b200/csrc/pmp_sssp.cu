@@ -463,8 +463,11 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
 // ---------------------------------------------------------------------------------------------
 // persistent round loop
 // ---------------------------------------------------------------------------------------------
-template <class C>
-__global__ void __launch_bounds__(NT, PMP_MINB) k_sssp(const __grid_constant__ SsspArgs A) {
+// MINB = resident CTAs per SM the register budget is sized for: 2 (128 registers, no spills,
+// fastest single activation -- latency-bound single queries) or 3 (80 registers, more tiles in
+// flight -- batches and full fields, which are throughput-bound).
+template <class C, int MINB>
+__global__ void __launch_bounds__(NT, MINB) k_sssp(const __grid_constant__ SsspArgs A) {
     typedef typename C::W W;
     typedef typename C::G G;
     cg::grid_group grid = cg::this_grid();
@@ -744,12 +747,11 @@ extern "C" int pmp_sssp_sizes(const pmp_grid *g, int64_t nq, int weight, int64_t
     return 0;
 }
 
-template <class C>
-static int launch_sssp(pmp_grid *g, SsspArgs &A, double *gcost_dev, int32_t *status_dev, cudaStream_t s, int mode) {
-    typedef typename C::W W;
+template <class C, int MINB>
+static int launch_coop(SsspArgs &A, cudaStream_t s) {
     static int blocks_per_sm = 0, n_sm = 0;
     if (!blocks_per_sm) {
-        PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_sssp<C>, NT, 0));
+        PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_sssp<C, MINB>, NT, 0));
         int dev = 0;
         PMP_CHECK_CUDA(cudaGetDevice(&dev));
         PMP_CHECK_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
@@ -757,16 +759,26 @@ static int launch_sssp(pmp_grid *g, SsspArgs &A, double *gcost_dev, int32_t *sta
         const char *e = getenv("PMP_B200_CTAS_PER_SM"); // tuning: fewer resident CTAs than fit
         if (e && atoi(e) >= 1 && atoi(e) < blocks_per_sm) blocks_per_sm = atoi(e);
     }
+    // persistent grid: every CTA resident (cooperative launch), a multiple of the SM count
+    dim3 grid((unsigned)(blocks_per_sm * n_sm)), block(NT);
+    void *args[] = {(void *)&A};
+    PMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void *)k_sssp<C, MINB>, grid, block, args, 0, s));
+    return 0;
+}
+
+template <class C>
+static int launch_sssp(pmp_grid *g, SsspArgs &A, double *gcost_dev, int32_t *status_dev, cudaStream_t s, int mode) {
+    typedef typename C::W W;
     const unsigned ib = (unsigned)((A.nq + 255) / 256);
     if (mode & 1) {
         k_sssp_init<C><<<ib > 1024 ? 1024 : ib, 256, 0, s>>>(A);
         PMP_CHECK_CUDA(cudaGetLastError());
     }
     if (mode & 2) {
-        // persistent grid: every CTA resident (cooperative launch), a multiple of the SM count
-        dim3 grid((unsigned)(blocks_per_sm * n_sm)), block(NT);
-        void *args[] = {(void *)&A};
-        PMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void *)k_sssp<C>, grid, block, args, 0, s));
+        const char *e = getenv("PMP_B200_MINB");
+        const bool throughput = e ? atoi(e) >= 3 : (A.full_field || A.nq >= 8);
+        const int rc = throughput ? launch_coop<C, 3>(A, s) : launch_coop<C, 2>(A, s);
+        if (rc) return rc;
     }
     if (mode & 4) {
         k_sssp_finish<W><<<ib > 1024 ? 1024 : ib, 256, 0, s>>>(A, gcost_dev, status_dev);

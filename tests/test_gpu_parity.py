@@ -361,3 +361,91 @@ def test_slab_decomposition_single_gpu_emulation():
         cx, cy, cz = (int(v) for v in free[len(free) // 2])
         words[0, (cz * one.dg.padded[1] + cy) * one.dg.padded[0] + cx] += 8
         assert one.verify(src, 0, Z)[0] > 0
+
+
+def test_custom_motion_costs_2d():
+    """env.motions is user data (graph_search.py:26): non-default costs and a reordered /
+    partial table must give the oracle's field (2D planners accumulate motion.g, node.py:41)."""
+    rng = np.random.default_rng(5)
+    occ = rng.random((70, 61)) < 0.2
+    occ[0, :] = occ[-1, :] = True
+    occ[:, 0] = occ[:, -1] = True
+    free = np.argwhere(~occ)
+    src = tuple(int(v) for v in free[7])
+    motions = np.array([(1, 0, 0), (0, 1, 0), (-1, 0, 0), (0, -1, 0), (1, 1, 0), (-1, -1, 0)], dtype=np.int32)
+    costs = np.array([1.0, 2.5, 1.25, 0.75, 1.5, 3.0])
+    ref = oracle.plan(occ, src, None, algo=oracle.DIJKSTRA, motions=motions, motion_g=costs,
+                      want_field=True, want_expand=False).g_field
+    env = make_env(occ)
+    env.motions = [pmp.Node((int(m[0]), int(m[1])), None, float(c), None) for m, c in zip(motions, costs)]
+    f = pmp.cost_field(env, src)
+    assert np.array_equal(f, ref)
+    goal = tuple(int(v) for v in free[-9])
+    cost, path, _ = pmp.Dijkstra(src, goal, env).plan()
+    r = oracle.plan(occ, src, goal, algo=oracle.DIJKSTRA, motions=motions, motion_g=costs, want_expand=False)
+    if r.reached:
+        assert f[goal] == ref[goal] and len(path) >= 2
+        # the reported cost is the sum of Euclidean step lengths along the path (a_star.py:109-116)
+        assert cost == resum(path)
+    else:
+        assert (cost, path) == ([], [])
+
+
+def test_mid_size_3d_certificate_and_astar():
+    """sizes the oracle cannot sweep quickly: 26-connected fp64 and 6-connected u32 fields on a
+    160^3 grid are checked by the shortest-path certificate (pmp_verify_field); A* cost equals
+    the field value at the goal and the Dijkstra cost."""
+    from python_motion_planning_b200 import slab, workloads
+    n = 160
+    occ = workloads.boxes3d(n, seed=3)
+    for mset, weight in (("26", "f64"), ("6", "u32")):
+        eng = slab.CudaSlabEngine(slab.build_local_env(occ, mset), weight)
+        slab.solve_in_process([eng], n, (1, 1, 1))
+        bad, reached, pend = eng.verify((1, 1, 1), 0, n)
+        assert bad == 0 and pend == 0 and reached > 0.5 * (~occ).sum(), (mset, bad, pend, reached)
+    env = pmp.Grid3D(n, n, n, walls=False)
+    env.update(occ)
+    goal = (n - 2, n - 2, n - 2)
+    ca, pa, _ = pmp.AStar3D((1, 1, 1), goal, env).plan()
+    cd, pd, _ = pmp.Dijkstra3D((1, 1, 1), goal, env).plan()
+    assert ca == pytest.approx(cd, rel=REL)
+    check_path(occ, pa, (1, 1, 1), goal, "start_first", oracle.MOTIONS_3D)
+    assert ca == resum(pa[::-1])
+    ws, _ = pmp.cost_field(env, (1, 1, 1), to_host=False)
+    from python_motion_planning_b200 import engine
+    f = engine.field_to_numpy(ws, 0)
+    assert f[goal] == pytest.approx(ca, rel=REL)
+
+
+def test_abi_rejects_bad_arguments():
+    """errors are return codes + pmp_last_error(), never exceptions or crashes"""
+    import ctypes
+    from python_motion_planning_b200 import _lib
+    L = _lib.lib()
+    h = ctypes.c_void_p()
+    dims = (ctypes.c_int32 * 3)(0, 5, 1)
+    assert L.pmp_grid_create(2, dims, ctypes.byref(h)) < 0 and b"dims" in L.pmp_last_error()
+    dims = (ctypes.c_int32 * 3)(8, 8, 1)
+    assert L.pmp_grid_create(4, dims, ctypes.byref(h)) < 0
+    assert L.pmp_grid_create(2, dims, ctypes.byref(h)) == 0
+    off = (ctypes.c_int32 * 3)(2, 0, 0)
+    w = (ctypes.c_double * 1)(1.0)
+    assert L.pmp_grid_set_motions(h, 1, off, w) < 0 and b"offsets" in L.pmp_last_error()
+    off = (ctypes.c_int32 * 3)(1, 0, 0)
+    w = (ctypes.c_double * 1)(-1.0)
+    assert L.pmp_grid_set_motions(h, 1, off, w) < 0
+    P = _lib.SsspParams(algo=2, heuristic=0, weight=0)
+    assert L.pmp_sssp(h, ctypes.byref(P), 1, None, None, None, None, 0, None, None, None, None) < 0
+    P = _lib.SsspParams(algo=0, heuristic=0, weight=1)       # u32 needs integer costs (sqrt 2 present)
+    gb, wb = ctypes.c_int64(), ctypes.c_int64()
+    assert L.pmp_sssp_sizes(h, 1, 1, ctypes.byref(gb), ctypes.byref(wb)) == 0
+    import torch
+    g = torch.empty(gb.value, dtype=torch.uint8, device="cuda")
+    ws = torch.empty(wb.value, dtype=torch.uint8, device="cuda")
+    q = torch.zeros(6, dtype=torch.int32, device="cuda")
+    assert L.pmp_sssp(h, ctypes.byref(P), 1, q.data_ptr(), q.data_ptr(), g.data_ptr(), ws.data_ptr(), wb.value,
+                      None, None, None, None) < 0 and b"integer" in L.pmp_last_error()
+    P = _lib.SsspParams(algo=0, heuristic=0, weight=0)
+    assert L.pmp_sssp(h, ctypes.byref(P), 1, q.data_ptr(), q.data_ptr(), g.data_ptr(), ws.data_ptr(), 16,
+                      None, None, None, None) < 0 and b"workspace" in L.pmp_last_error()
+    assert L.pmp_grid_destroy(h) == 0
