@@ -87,22 +87,37 @@ __global__ void k_bits_pack_dense(GridDev G, u32 *bits, const uint8_t *occ) {
 }
 
 // dense u8 box in the caller's own index order [(x*Y + y)*Z + z] (arrays indexed [x, y(, z)] as
-// the reference's coordinate tuples are) -> bits.  A block transposes a 32(x) x 32(z) patch
-// through shared memory: reads coalesced along z, ballots along x.
-__global__ void k_bits_pack_xyz(GridDev G, u32 *bits, const uint8_t *occ) {
-    __shared__ uint8_t tile[32][33];
+// the reference's coordinate tuples are) -> bits.  A block of 32 x 8 threads transposes a
+// 32(x) x 128(z) patch through shared memory: 4-byte reads coalesced along z, ballots along x.
+__global__ void k_bits_pack_xyz(GridDev G, u32 *bits, const uint8_t *occ, int vec) {
+    __shared__ u32 tile[32][33]; // [x][z / 4]
     const int tx = threadIdx.x, ty = threadIdx.y;
-    const int z0 = blockIdx.x * 32, y = blockIdx.y, wx = blockIdx.z;
-    {
-        const int x = wx * 32 + ty, z = z0 + tx;
-        uint8_t v = 1; // outside the box: blocked
-        if (x < G.X && z < G.Z) v = occ[((size_t)x * G.Y + y) * G.Z + z] != 0;
-        tile[ty][tx] = v;
+    const int z0 = blockIdx.x * 128, y = blockIdx.y, wx = blockIdx.z;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int xi = ty + 8 * k, x = wx * 32 + xi, z = z0 + 4 * tx;
+        u32 v = 0x01010101u; // outside the box: blocked
+        if (x < G.X && z < G.Z) {
+            const uint8_t *p = occ + ((size_t)x * G.Y + y) * G.Z + z;
+            if (vec && z + 3 < G.Z) {
+                v = *(const u32 *)p;
+            } else {
+                v = 0;
+                for (int b = 0; b < 4; ++b) v |= (u32)((z + b < G.Z) ? (p[b] != 0) : 1) << (8 * b);
+            }
+        }
+        tile[xi][tx] = v;
     }
     __syncthreads();
-    const u32 w = __ballot_sync(0xFFFFFFFFu, tile[tx][ty] != 0); // lane = x, warp = z
-    const int z = z0 + ty;
-    if (tx == 0 && z < G.Z) bits[((size_t)z * G.PY + y) * G.wpr + wx] = w;
+    // warp ty handles z = z0 + ty, ty + 8, ...: lane = x
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int zi = ty + 8 * k; // 0..127
+        const u32 word = tile[tx][zi >> 2];
+        const u32 w = __ballot_sync(0xFFFFFFFFu, ((word >> (8 * (zi & 3))) & 0xFFu) != 0);
+        const int z = z0 + zi;
+        if (tx == 0 && z < G.Z) bits[((size_t)z * G.PY + y) * G.wpr + wx] = w;
+    }
 }
 
 __global__ void k_count_free(GridDev G, const u32 *bits, u64 *out) {
@@ -296,8 +311,9 @@ extern "C" int pmp_grid_set_dense_xyz(pmp_grid *g, const uint8_t *occ_dev, void 
     cudaStream_t s = (cudaStream_t)stream;
     const size_t n_words = (size_t)g->d.wpr * g->d.PY * g->d.PZ;
     k_bits_reset<<<blocks_for(n_words, 256), 256, 0, s>>>(g->d, g->bits); // padding rows / planes: blocked
-    dim3 grid((unsigned)((g->d.Z + 31) / 32), (unsigned)g->d.Y, (unsigned)g->d.wpr), block(32, 32);
-    k_bits_pack_xyz<<<grid, block, 0, s>>>(g->d, g->bits, occ_dev);
+    dim3 grid((unsigned)((g->d.Z + 127) / 128), (unsigned)g->d.Y, (unsigned)g->d.wpr), block(32, 8);
+    const int vec = (g->d.Z % 4 == 0) && (((uintptr_t)occ_dev & 3) == 0); // 4-byte loads stay aligned
+    k_bits_pack_xyz<<<grid, block, 0, s>>>(g->d, g->bits, occ_dev, vec);
     PMP_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

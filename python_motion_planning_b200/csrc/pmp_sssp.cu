@@ -80,6 +80,8 @@ struct TileCfg {
     }
 };
 
+#define BFS_LV 63 // levels one pass of the unit-weight solver sweeps (2 x 64 x 32 words = the record queues' 16 KB)
+
 template <class C>
 struct TileSmem {
     typename C::G g[C::HC]; // cost words of tile + halo in the global (value << 1 | clean) format
@@ -88,7 +90,15 @@ struct TileSmem {
     u64 kmin[2];            // min key of the pending cells (computed on empty sub-iterations)
     u64 T, U, k0;
     u32 chg[C::NCW];        // cells (tile + halo, by halo'd index) lowered during this activation
-    ulonglong2 fq[NT / 32][C::NCELL / (NT / 32)]; // per-warp frontier records: .x = value, .y = free mask | halo'd index << 32
+    union {
+        ulonglong2 fq[NT / 32][C::NCELL / (NT / 32)]; // per-warp frontier records: .x = value, .y = free mask | halo'd index << 32
+        struct {                  // unit-weight fast path (solve_bfs): one bit per cell, by level
+            u32 fin[BFS_LV + 1][32];  // cells whose value at load is Lmin + i
+            u32 seed[BFS_LV][32];     // ... and that are pending
+        } b;
+    };
+    u32 bw[4][32];          // solve_bfs: free cells, cells below Lmin, cells lowered, cells expanded
+    u32 bmin, bmax;         // solve_bfs: smallest / largest pending level
     u64 stat[16];           // per-CTA counters (flushed at kernel end)
     u64 tm[6];              // CTA 0's phase timers: t0, scan, proc, wait, ta/tb scratch
     u32 item, n_edge, n_exp;
@@ -103,6 +113,7 @@ struct SsspArgs {
     // directions not in the motion table have need = all-ones (never satisfied).
     u64 wdir[27];
     u32 need[27];
+    int bfs;                  // unit-cost axis motions + integer field: bit-parallel in-tile solver
     int ndir, dpl_log2;       // number of motions; lanes per cell in the expansion = 1 << dpl_log2 (>= ndir)
     unsigned char dirs[32];   // canonical direction handled by lane index i of a lane group (13 = none)
     u32 nq, ring_cap;
@@ -168,6 +179,171 @@ __device__ __forceinline__ void relax_record(TileSmem<C> &S, const SsspArgs &A, 
     bool won = old == tvr;
     if (!won && want < old) won = smem_min(&S.g[vhi], want); // raced with a worse value
     if (won) atomicOr(&S.chg[vhi >> 5], 1u << (vhi & 31));
+}
+
+// ---------------------------------------------------------------------------------------------
+// Unit-weight in-tile solver (integer fields, axis motions of cost 1: the 4/6-connected grids).
+// With unit weights the cost is a BFS level, so a whole tile is one bit per cell in the 32
+// lanes of ONE warp (3D: word = two x-rows of 16, lane = lz*4 + ly/2; 2D: word = one row) and a
+// level step is a handful of shifts and shuffles instead of a round of shared-memory atomics:
+//     frontier(L)  = cells assigned L by the previous step | pending cells whose value is L
+//     next         = neighbours(frontier) & free & ~(cells whose value is already <= L + 1)
+// Cells are first bucketed by their value at load (fin / seed masks per level, by all 256
+// threads); afterwards every thread pushes its expanded boundary cells into the halo.  The
+// result is the same fixed point as the generic solver's.
+// ---------------------------------------------------------------------------------------------
+template <class C>
+__device__ __forceinline__ void bfs_cellbit(int lx, int ly, int lz, int &w, u32 &bit) {
+    if (C::TZ == 1) { w = ly; bit = 1u << lx; }
+    else { w = lz * 4 + (ly >> 1); bit = 1u << ((ly & 1) * 16 + lx); }
+}
+
+template <class C>
+__device__ void solve_bfs(TileSmem<C> &S, const SsspArgs &A, const u64 T, const u32 (&F)[C::CPT],
+                          typename C::G (&gprop)[C::CPT], u64 &km_final, u32 &n_exp, u32 &n_iter, u32 &my_edges) {
+    typedef typename C::W W;
+    typedef typename C::G G;
+    constexpr int CPT = C::CPT;
+    const int tid = threadIdx.x, lane = tid & 31;
+    // canonical directions of the axis moves: d = (dz+1)*9 + (dy+1)*3 + (dx+1)
+    const bool xp = A.need[14] != 0xFFFFFFFFu, xm = A.need[12] != 0xFFFFFFFFu;
+    const bool yp = A.need[16] != 0xFFFFFFFFu, ym = A.need[10] != 0xFFFFFFFFu;
+    const bool zp = A.need[22] != 0xFFFFFFFFu, zm = A.need[4] != 0xFFFFFFFFu;
+    int cw[CPT];
+    u32 cb[CPT];
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+        int lx, ly, lz;
+        C::owned(tid, j, lx, ly, lz);
+        bfs_cellbit<C>(lx, ly, lz, cw[j], cb[j]);
+    }
+    for (;;) {
+        // ---- smallest pending level; clear the level masks ----
+        u32 lminp = 0xFFFFFFFFu, lmaxp = 0;
+        G gv[CPT];
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            gv[j] = W::dec(S.g[C::own_hi(tid, j)]);
+            if (gv[j] < gprop[j]) {
+                lminp = gv[j] < lminp ? (u32)gv[j] : lminp;
+                lmaxp = gv[j] > lmaxp ? (u32)gv[j] : lmaxp;
+            }
+        }
+        lminp = __reduce_min_sync(0xFFFFFFFFu, lminp);
+        lmaxp = __reduce_max_sync(0xFFFFFFFFu, lmaxp);
+        if (tid == 0) { S.bmin = 0xFFFFFFFFu; S.bmax = 0; }
+        for (int i = tid; i < (2 * BFS_LV + 1) * 32; i += NT) (&S.b.fin[0][0])[i] = 0;
+        if (tid < 128) S.bw[tid >> 5][tid & 31] = 0;
+        __syncthreads();
+        if (lane == 0 && lminp != 0xFFFFFFFFu) { atomicMin(&S.bmin, lminp); atomicMax(&S.bmax, lmaxp); }
+        __syncthreads();
+        const u32 Lmin = S.bmin;
+        if (Lmin == 0xFFFFFFFFu) { km_final = KEY_INF; break; }
+        if ((u64)Lmin >= T) { km_final = (u64)Lmin; break; }
+        const u64 lend64 = (u64)Lmin + BFS_LV;
+        const u32 Lend = (u32)(lend64 < T ? lend64 : T);
+        // ---- bucket the owned cells by their value ----
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            if (!((F[j] >> 13) & 1u)) continue; // the cell itself is blocked
+            atomicOr(&S.bw[0][cw[j]], cb[j]);
+            const G v = gv[j];
+            if (v == W::inf()) continue;
+            if (v < Lmin) { atomicOr(&S.bw[1][cw[j]], cb[j]); continue; }
+            const u32 i = (u32)v - Lmin;
+            if (i > BFS_LV) continue;
+            atomicOr(&S.b.fin[i][cw[j]], cb[j]);
+            if (v < gprop[j] && i < BFS_LV) atomicOr(&S.b.seed[i][cw[j]], cb[j]);
+        }
+        __syncthreads();
+        // ---- the sweep: warp 0, lane = word ----
+        if (tid < 32) {
+            const u32 freew = S.bw[0][lane];
+            u32 vis = S.bw[1][lane], lowered = 0, expd = 0, carry = 0, nx = 0, iters = 0;
+            const u32 Lmaxp = S.bmax;
+            u32 L = Lmin;
+            for (; L < Lend; ++L) {
+                const int i = (int)(L - Lmin);
+                vis |= S.b.fin[i][lane];
+                const u32 Fr = carry | (S.b.seed[i][lane] & ~lowered);
+                carry = 0;
+                if (!__any_sync(0xFFFFFFFFu, Fr != 0)) {
+                    S.b.seed[i][lane] = lowered;
+                    if (L >= Lmaxp) { ++L; break; } // no frontier and no pending cell further up
+                    continue;
+                }
+                ++iters;
+                expd |= Fr;
+                nx += __popc(Fr);
+                const u32 up1 = __shfl_up_sync(0xFFFFFFFFu, Fr, 1), dn1 = __shfl_down_sync(0xFFFFFFFFu, Fr, 1);
+                u32 N = 0;
+                if (C::TZ == 1) {
+                    if (xp) N |= Fr << 1;
+                    if (xm) N |= Fr >> 1;
+                    if (yp && lane >= 1) N |= up1;
+                    if (ym && lane < 31) N |= dn1;
+                } else {
+                    const u32 up4 = __shfl_up_sync(0xFFFFFFFFu, Fr, 4), dn4 = __shfl_down_sync(0xFFFFFFFFu, Fr, 4);
+                    if (xp) N |= (Fr & 0x7FFF7FFFu) << 1;
+                    if (xm) N |= (Fr & 0xFFFEFFFEu) >> 1;
+                    if (yp) { N |= (Fr & 0xFFFFu) << 16; if (lane & 3) N |= up1 >> 16; }
+                    if (ym) { N |= Fr >> 16; if ((lane & 3) != 3) N |= (dn1 & 0xFFFFu) << 16; }
+                    if (zp && lane >= 4) N |= up4;
+                    if (zm && lane < 28) N |= dn4;
+                }
+                N &= freew & ~(vis | S.b.fin[i + 1][lane]);
+                lowered |= N;
+                vis |= N;
+                carry = N;
+                // seed[i] is consumed: reuse the row for the cells lowered up to and including this
+                // step (value Lmin + i + 1 or less); owners binary-search their level afterwards
+                S.b.seed[i][lane] = lowered;
+            }
+            if (lane == 0) S.bmax = L - Lmin; // number of level rows written
+            S.bw[2][lane] = lowered;
+            S.bw[3][lane] = expd;
+            n_exp += nx;
+            if (lane == 0) n_iter += iters;
+        }
+        __syncthreads();
+        // ---- owners: expanded cells are clean now; push them into the halo ----
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            const int hj = C::own_hi(tid, j);
+            G v = W::dec(S.g[hj]);
+            if (S.bw[2][cw[j]] & cb[j]) { // lowered: first level row whose cumulative mask has the bit
+                int lo = 0, hi = (int)S.bmax - 1;
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (S.b.seed[mid][cw[j]] & cb[j]) hi = mid; else lo = mid + 1;
+                }
+                v = (G)(Lmin + (u32)lo + 1u);
+                S.g[hj] = W::enc(v, true);
+                atomicOr(&S.chg[hj >> 5], 1u << (hj & 31));
+            }
+            if (!(S.bw[3][cw[j]] & cb[j])) continue;
+            gprop[j] = v;
+            int lx, ly, lz;
+            C::owned(tid, j, lx, ly, lz);
+            const G want = W::enc(v + 1, true);
+#pragma unroll
+            for (int d = 0; d < 6; ++d) {
+                const int dx = d == 0 ? 1 : (d == 1 ? -1 : 0), dy = d == 2 ? 1 : (d == 3 ? -1 : 0);
+                const int dz = d == 4 ? 1 : (d == 5 ? -1 : 0);
+                if (C::TZ == 1 && dz != 0) continue;
+                const int dcan = (dz + 1) * 9 + (dy + 1) * 3 + (dx + 1);
+                if (A.need[dcan] == 0xFFFFFFFFu || !((F[j] >> dcan) & 1u)) continue;
+                ++my_edges;
+                if ((unsigned)(lx + dx) < (unsigned)C::TX && (unsigned)(ly + dy) < (unsigned)C::TY &&
+                    (unsigned)(lz + dz) < (unsigned)C::TZ)
+                    continue; // interior target: done by the sweep
+                const int vhi = hj + (dz * C::HY + dy) * C::HX + dx;
+                if (v + 1 < W::dec(S.g[vhi]) && W::dec(atomicMin(&S.g[vhi], want)) > v + 1)
+                    atomicOr(&S.chg[vhi >> 5], 1u << (vhi & 31));
+            }
+        }
+        __syncthreads();
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -299,7 +475,9 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     }
     u64 km_final = KEY_INF;
     u32 n_exp = 0, n_iter = 0, my_edges = 0, n_empty = 0;
-    for (;;) {
+    const bool bfs = W::kind == PMP_W_U32 && A.bfs;
+    if (bfs) solve_bfs<C>(S, A, T, F, gprop, km_final, n_exp, n_iter, my_edges);
+    else for (;;) {
         G gv[CPT];
 #pragma unroll
         for (int j = 0; j < CPT; ++j) gv[j] = W::dec(S.g[C::own_hi(tid, j)]);
@@ -817,6 +995,11 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
     for (int d = 0; d < 27; ++d)
         if (A.need[d] != 0xFFFFFFFFu) A.dirs[A.ndir++] = (unsigned char)d;
     A.dpl_log2 = A.ndir <= 8 ? 3 : (A.ndir <= 16 ? 4 : 5);
+    A.bfs = P->weight == PMP_W_U32 && !getenv("PMP_B200_NO_BFS");
+    for (int m = 0; m < g->mot.k; ++m) {
+        const int nax = (g->mot.dx[m] != 0) + (g->mot.dy[m] != 0) + (g->mot.dz[m] != 0);
+        if (nax != 1 || g->mot.wi[m] != 1) A.bfs = 0;
+    }
     A.nq = (u32)nq;
     A.ring_cap = (u32)((size_t)nq * g->d.ntiles + RING_SLACK);
     A.starts = starts_dev;
@@ -837,6 +1020,7 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
     // requested type is scaled by the largest admissible factor (manhattan on 8/26-connected
     // grids over-estimates in the reference, graph_search.py:41-42 -- see DESIGN.md).
     A.use_h = (P->algo == PMP_ASTAR && !A.full_field) ? 1 : 0;
+    if (A.use_h) A.bfs = 0; // the unit-weight solver orders by g alone
     A.he = g->he_scale;
     A.hm = g->hm_scale;
     if (P->weight == PMP_W_U32) { // integer keys: floor the factors so h stays an integer lower bound
