@@ -31,6 +31,9 @@
 namespace cg = cooperative_groups;
 
 #define NT 256
+#ifndef PMP_TP_MINB
+#define PMP_TP_MINB 4 // CTAs per SM of the throughput build of k_sssp (64 registers; measured best for batches and fields)
+#endif
 #ifndef PMP_MINB
 #define PMP_MINB 2 // resident CTAs per SM the register budget is sized for (128 registers: no spills)
 #endif
@@ -642,8 +645,8 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
 // persistent round loop
 // ---------------------------------------------------------------------------------------------
 // MINB = resident CTAs per SM the register budget is sized for: 2 (128 registers, no spills,
-// fastest single activation -- latency-bound single queries) or 3 (80 registers, more tiles in
-// flight -- batches and full fields, which are throughput-bound).
+// fastest single activation -- latency-bound single queries) or 3-4 (80 / 64 registers, more tiles in
+// flight -- batches and full fields, which are throughput-bound; the launcher uses 4 there).
 template <class C, int MINB>
 __global__ void __launch_bounds__(NT, MINB) k_sssp(const __grid_constant__ SsspArgs A) {
     typedef typename C::W W;
@@ -955,7 +958,7 @@ static int launch_sssp(pmp_grid *g, SsspArgs &A, double *gcost_dev, int32_t *sta
     if (mode & 2) {
         const char *e = getenv("PMP_B200_MINB");
         const bool throughput = e ? atoi(e) >= 3 : (A.full_field || A.nq >= 8);
-        const int rc = throughput ? launch_coop<C, 3>(A, s) : launch_coop<C, 2>(A, s);
+        const int rc = throughput ? launch_coop<C, PMP_TP_MINB>(A, s) : launch_coop<C, 2>(A, s);
         if (rc) return rc;
     }
     if (mode & 4) {

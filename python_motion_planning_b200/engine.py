@@ -126,12 +126,13 @@ def cells_to_coords(cells, dg):
     return np.stack([x, y, c // (PX * PY)], axis=1)
 
 
-def field_to_numpy(ws, q=0):
-    """cost field of query q as a float64 array indexed [x, y(, z)] (+inf = unreached)"""
+def field_to_numpy(ws, q=0, raw=None):
+    """cost field of query q as a float64 array indexed [x, y(, z)] (+inf = unreached);
+    `raw`: a private device copy of the field words to decode instead of ws.g[q]"""
     dg = ws.dg
     t = dg.torch
     PX, PY, PZ = dg.padded
-    raw = ws.g[q].clone()
+    raw = ws.g[q].clone() if raw is None else raw
     _lib.check(dg.L.pmp_field_finalize(raw.data_ptr(), ws.weight, raw.numel(), dg.stream()),
                "pmp_field_finalize")
     if ws.weight == W_F64:

@@ -219,7 +219,8 @@ class _SearchMixin:
 
             def _build(self):
                 if not self._built:
-                    c, g, h, p = planner._expand_arrays(ws, bound)
+                    c, g, h, p = planner._expand_arrays(ws, bound, getattr(self, "_snap", None))
+                    self._snap = None
                     self._coords, self._g, self._h, self._parents = c, g, h, p
                     self._built = True
 
@@ -232,13 +233,13 @@ class _SearchMixin:
                 return ExpandView.__getitem__(self, i)
 
         view = _Lazy()
-        if ws.dg.pcells <= (1 << 22):          # small grids: snapshot now (buffers are reused)
-            view._build()
-        return view
+        if ws.dg.pcells <= (1 << 22):          # small grids: keep a device copy of the field (the
+            view._snap = ws.g[0].clone()       # workspace is reused by the next plan()); records
+        return view                            # are still built on first use only
 
-    def _expand_arrays(self, ws, bound):
+    def _expand_arrays(self, ws, bound, snap=None):
         dg = ws.dg
-        f = engine.field_to_numpy(ws, 0)
+        f = engine.field_to_numpy(ws, 0, snap)
         finite = np.isfinite(f)
         coords = np.argwhere(finite)
         g = f[finite]
