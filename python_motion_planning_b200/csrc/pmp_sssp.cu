@@ -743,6 +743,9 @@ __global__ void __launch_bounds__(NT, MINB) k_sssp(const __grid_constant__ SsspA
                 u32 *slot = &A.wl[0][ticket % A.ring_cap];
                 u32 v;
                 unsigned ns = 20, spins = 0;
+#ifdef PMP_POPSTAT
+                const long long pt0 = clock64();
+#endif
                 for (;;) {
                     v = ld_cg(slot);
                     if (v) break;
@@ -751,6 +754,9 @@ __global__ void __launch_bounds__(NT, MINB) k_sssp(const __grid_constant__ SsspA
                     if (ns < 160) ns *= 2;
                     if (++spins > (1u << 22)) { A.stats[15] = 0xDEADu; break; } // safety net (seconds)
                 }
+#ifdef PMP_POPSTAT
+                if (v) { S.stat[13] += (u64)(clock64() - pt0); S.stat[14] += spins == 0; S.stat[15] += 1; }
+#endif
                 if (v) { fence_gpu(); *(volatile u32 *)slot = 0; } // acquire, then recycle the slot
                 S.item = v;
             }
@@ -770,7 +776,7 @@ __global__ void __launch_bounds__(NT, MINB) k_sssp(const __grid_constant__ SsspA
         }
     }
     __syncthreads();
-    if (tid < 16 && tid != 0 && tid != 4 && (tid < 8 || tid == 12) && S.stat[tid]) atomicAdd(&A.stats[tid], S.stat[tid]);
+    if (tid < 16 && tid != 0 && tid != 4 && (tid < 8 || tid >= 12) && S.stat[tid]) atomicAdd(&A.stats[tid], S.stat[tid]);
     if (timer) {
         A.stats[8] = globaltimer_ns() - S.tm[0];
         A.stats[9] = S.tm[1]; A.stats[10] = S.tm[2]; A.stats[11] = S.tm[3];
