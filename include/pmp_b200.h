@@ -47,7 +47,8 @@ enum pmp_status {
     PMP_ST_RUNNING = 0,
     PMP_ST_EXHAUSTED = 1, /* every reachable cell settled; goal (if any) not reached */
     PMP_ST_REACHED = 2,   /* g[goal] is final */
-    PMP_ST_BAD_QUERY = 3  /* start or goal outside the box or on an obstacle */
+    PMP_ST_BAD_QUERY = 3, /* start or goal outside the box or on an obstacle */
+    PMP_ST_REPLAN_OVERFLOW = 4 /* pmp_replan_update: scratch too small for the invalidated region */
 };
 
 const char *pmp_last_error(void);
@@ -192,6 +193,32 @@ int pmp_slab_run(pmp_grid *g, const pmp_sssp_params *params, void *g_dev, void *
  * to out_dev[4]); mark = 0: values only (refreshing a ghost plane). */
 int pmp_slab_merge(pmp_grid *g, int weight, void *g_dev, void *ws_dev, int64_t ws_bytes,
                    int z_local, int mark, const void *plane_dev, uint64_t *out_dev, void *stream);
+
+/* ---- incremental replanning on a resident field.  Replaces the repair loop
+ *      of the reference's incremental planners: LPAStar.OnPress / LPAStar3D.apply_change +
+ *      computeShortestPath + updateVertex (global_planner/graph_search/lpa_star.py:102-177,
+ *      lpa_star3d.py:98-177) and DStar3D.apply_dynamic_obstacles (d_star3d.py:115-151).  One
+ *      query; the field g_dev and the workspace ws_dev stay on the device between calls and
+ *      must not be touched by other searches. ---- */
+
+/* First plan: pmp_sssp for one query, run without the g[goal] pruning so that the field can be
+ * repaired later.  Same outputs as pmp_sssp. */
+int pmp_replan_begin(pmp_grid *g, const pmp_sssp_params *params, const int32_t *start_dev,
+                     const int32_t *goal_dev, void *g_dev, void *ws_dev, int64_t ws_bytes,
+                     double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream);
+/* Applies n_changes occupancy changes (cells_dev: [n][3] int32 box coordinates, one entry per
+ * cell; blocked_dev[i] = 1 obstacle added, 0 obstacle removed) to the handle's bitmask, resets
+ * every value that lost its support, re-arms the cells around the change and resumes the search;
+ * afterwards the field equals the field of a search from scratch on the new map.
+ * scratch_dev: 16 control words + two candidate buffers of (scratch_words - 16) / 2 cells each;
+ * after the call [3] = overflow flag, [4] = cells reset, [5] = invalidation waves.  If the
+ * invalidated region does not fit, nothing is searched, status = PMP_ST_REPLAN_OVERFLOW and the
+ * caller falls back to pmp_replan_begin (the bitmask is already up to date). */
+int pmp_replan_update(pmp_grid *g, const pmp_sssp_params *params, const int32_t *start_dev,
+                      const int32_t *goal_dev, void *g_dev, void *ws_dev, int64_t ws_bytes,
+                      const int32_t *cells_dev, const uint8_t *blocked_dev, int64_t n_changes,
+                      uint32_t *scratch_dev, int64_t scratch_words,
+                      double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream);
 
 #ifdef __cplusplus
 }

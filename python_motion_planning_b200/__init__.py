@@ -11,8 +11,10 @@ from .environment import Env, Env3D, Grid, Grid3D, Node, Node3D
 from .planner import (AStar, AStar3D, Dijkstra, Dijkstra3D, GBFS, GBFS3D, GraphSearcher,
                       GraphSearcher3D, Planner, Planner3D, SearchFactory, ExpandView)
 from .batch import plan_batch, plan_batch_sharded, cost_field, shard_range
+from .replan import LPAStar, LPAStar3D, DynamicField, ReplanSession
 from ._lib import PmpError
 
 __all__ = ["Env", "Env3D", "Grid", "Grid3D", "Node", "Node3D", "AStar", "AStar3D", "Dijkstra",
            "Dijkstra3D", "GBFS", "GBFS3D", "GraphSearcher", "GraphSearcher3D", "Planner",
-           "Planner3D", "SearchFactory", "ExpandView", "plan_batch", "plan_batch_sharded", "shard_range", "cost_field", "PmpError"]
+           "Planner3D", "SearchFactory", "ExpandView", "plan_batch", "plan_batch_sharded", "shard_range", "cost_field", "PmpError",
+           "LPAStar", "LPAStar3D", "DynamicField", "ReplanSession"]

@@ -15,7 +15,7 @@ CSRC = os.path.join(_HERE, "csrc")
 ASTAR, DIJKSTRA, GBFS = 0, 1, 2
 H_EUCLIDEAN, H_MANHATTAN = 0, 1
 W_F64, W_U32 = 0, 1
-ST_RUNNING, ST_EXHAUSTED, ST_REACHED, ST_BAD_QUERY = 0, 1, 2, 3
+ST_RUNNING, ST_EXHAUSTED, ST_REACHED, ST_BAD_QUERY, ST_REPLAN_OVERFLOW = 0, 1, 2, 3, 4
 
 # every symbol include/pmp_b200.h declares (tests/test_abi.py checks the header against this)
 SYMBOLS = (
@@ -24,7 +24,7 @@ SYMBOLS = (
     "pmp_grid_set_dense", "pmp_grid_set_dense_xyz", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
     "pmp_grid_set_motions", "pmp_sssp_sizes", "pmp_sssp", "pmp_field_finalize",
     "pmp_count_settled", "pmp_extract_paths", "pmp_verify_field", "pmp_gbfs",
-    "pmp_slab_begin", "pmp_slab_run", "pmp_slab_merge",
+    "pmp_slab_begin", "pmp_slab_run", "pmp_slab_merge", "pmp_replan_begin", "pmp_replan_update",
 )
 
 
@@ -92,6 +92,9 @@ def lib():
         "pmp_slab_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, i64, vp],
         "pmp_slab_run": [vp, ctypes.POINTER(SsspParams), vp, vp, i64, dbl, vp, vp],
         "pmp_slab_merge": [vp, i32, vp, vp, i64, i32, i32, vp, vp, vp],
+        "pmp_replan_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, vp, i64, vp, vp, vp, vp],
+        "pmp_replan_update": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, vp, i64, vp, vp, i64, vp, i64,
+                              vp, vp, vp, vp],
     }
     for name, argtypes in sig.items():
         fn = getattr(L, name)

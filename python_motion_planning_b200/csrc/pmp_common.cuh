@@ -134,6 +134,19 @@ __device__ static inline int cell_blocked(const GridDev &G, int x, int y, int z)
     return (w >> (x & 31)) & 1u;
 }
 
+// legality of the edge u -> u + m, evaluated at u (global bitmask reads)
+__device__ static inline bool edge_legal(const GridDev &G, const Motions &M, int m, int ux, int uy, int uz) {
+    const int dx = M.dx[m], dy = M.dy[m], dz = M.dz[m];
+    if (cell_blocked(G, ux, uy, uz) || cell_blocked(G, ux + dx, uy + dy, uz + dz)) return false;
+    const int nz = (dx != 0) + (dy != 0) + (dz != 0);
+    if (nz >= 2) {
+        if (dx && cell_blocked(G, ux + dx, uy, uz)) return false;
+        if (dy && cell_blocked(G, ux, uy + dy, uz)) return false;
+        if (dz && cell_blocked(G, ux, uy, uz + dz)) return false;
+    }
+    return true;
+}
+
 // Admissible heuristic used for ordering / pruning only: max(he * euclid_lo, hm * manhattan),
 // euclid_lo a round-down float sqrt (never above the reference's math.hypot / math.sqrt,
 // graph_search.py:41-44, graph_search_3d.py:46-49).

@@ -13,19 +13,6 @@
 // utils/environment/node.py:51-54, which is not a total order).
 #include "pmp_common.cuh"
 
-// legality of the edge u -> u + m, evaluated at u (global bitmask reads)
-__device__ static inline bool edge_legal(const GridDev &G, const Motions &M, int m, int ux, int uy, int uz) {
-    const int dx = M.dx[m], dy = M.dy[m], dz = M.dz[m];
-    if (cell_blocked(G, ux, uy, uz) || cell_blocked(G, ux + dx, uy + dy, uz + dz)) return false;
-    const int nz = (dx != 0) + (dy != 0) + (dz != 0);
-    if (nz >= 2) {
-        if (dx && cell_blocked(G, ux + dx, uy, uz)) return false;
-        if (dy && cell_blocked(G, ux, uy + dy, uz)) return false;
-        if (dz && cell_blocked(G, ux, uy, uz + dz)) return false;
-    }
-    return true;
-}
-
 // 64-bit / 32-bit warp minimum with the hardware reductions (REDUX works on 32-bit words)
 __device__ static inline u64 warp_min(u64 v) {
     const u32 hi = (u32)(v >> 32);

@@ -131,6 +131,7 @@ struct SsspArgs {
     u32 *ctr;      // per round parity p: [p] ring tail, [2+p] ring head, [4+p] live tiles, [6+p] tiles in flight
     u64 *stats;    // 16 counters, see include/pmp_b200.h (pmp_sssp)
     double window, sub, he, hm;
+    int no_prune; // replanning: keep relaxations that cannot beat the current g[goal] (pmp_replan.cuh)
     u64 key_cap; // slab mode: only keys below this bound are processed (KEY_INF otherwise)
     int use_h, full_field, max_rounds;
 };
@@ -391,7 +392,7 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         S.T = ld_cg(&A.T[cur][q]);
     } else if (tid == 64) {
         u64 U = KEY_INF;
-        const u32 gc = A.full_field ? 0xFFFFFFFFu : __ldg(A.goalcell + q);
+        const u32 gc = (A.full_field || A.no_prune) ? 0xFFFFFFFFu : __ldg(A.goalcell + q);
         if (gc != 0xFFFFFFFFu) {
             const G gg = W::dec(ld_cg(gq + gc));
             if (gg != W::inf()) U = W::key(gg, 0.0);
@@ -1050,10 +1051,10 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
 
 }
 
-extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
-                        const int32_t *starts_dev, const int32_t *goals_dev,
-                        void *g_dev, void *ws_dev, int64_t ws_bytes,
-                        double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream) {
+static int sssp_from_scratch(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const int32_t *starts_dev,
+                             const int32_t *goals_dev, void *g_dev, void *ws_dev, int64_t ws_bytes,
+                             double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream,
+                             int no_prune) {
     if (!g || !P || nq < 1 || !starts_dev || !g_dev || !ws_dev) {
         pmp_set_error("pmp_sssp: bad arguments");
         return -1;
@@ -1080,6 +1081,7 @@ extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
     cudaStream_t s = (cudaStream_t)stream;
     SsspArgs A;
     fill_args(g, P, nq, starts_dev, goals_dev, g_dev, ws_dev, L, A);
+    A.no_prune = no_prune;
     const size_t gsz = (size_t)nq * g->d.pcells * (P->weight == PMP_W_F64 ? 8 : 4);
     PMP_CHECK_CUDA(cudaMemsetAsync(g_dev, 0xFF, gsz, s));
     const size_t nt = (size_t)nq * g->d.ntiles;
@@ -1093,6 +1095,14 @@ extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
     if (stats_dev)
         PMP_CHECK_CUDA(cudaMemcpyAsync(stats_dev, A.stats, 16 * 8, cudaMemcpyDeviceToDevice, s));
     return 0;
+}
+
+extern "C" int pmp_sssp(pmp_grid *g, const pmp_sssp_params *P, int64_t nq,
+                        const int32_t *starts_dev, const int32_t *goals_dev,
+                        void *g_dev, void *ws_dev, int64_t ws_bytes,
+                        double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream) {
+    return sssp_from_scratch(g, P, nq, starts_dev, goals_dev, g_dev, ws_dev, ws_bytes, gcost_dev, status_dev,
+                             stats_dev, stream, 0);
 }
 
 extern "C" int pmp_field_finalize(void *g_dev, int weight, int64_t n_cells, void *stream) {
@@ -1258,3 +1268,5 @@ extern "C" int pmp_slab_merge(pmp_grid *g, int weight, void *g_dev, void *ws_dev
     PMP_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
+
+#include "pmp_replan.cuh"

@@ -475,4 +475,7 @@ class SearchFactory(object):
             return Dijkstra(**config)
         elif planner_name == "gbfs":
             return GBFS(**config)
+        elif planner_name == "lpa_star":
+            from .replan import LPAStar
+            return LPAStar(**config)
         raise ValueError("The `planner_name` must be set correctly.")
