@@ -220,6 +220,24 @@ int pmp_replan_update(pmp_grid *g, const pmp_sssp_params *params, const int32_t 
                       uint32_t *scratch_dev, int64_t scratch_words,
                       double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream);
 
+/* ---- line of sight and any-angle shortcutting ---- */
+
+/* ThetaStar.lineOfSight (global_planner/graph_search/theta_star.py:110-171; 2D handles) and
+ * ThetaStar3D.lineOfSight / LazyThetaStar3D.lineOfSight (theta_star3d.py:139-215,
+ * lazy_theta_star3d.py:158-235; 3D handles) for n ordered pairs a[i] -> b[i] ([n][3] int32 box
+ * coordinates): out_dev[i] = 1 iff the reference returns True.  Cells outside the box are blocked. */
+int pmp_line_of_sight(const pmp_grid *g, int64_t n, const int32_t *a_dev, const int32_t *b_dev,
+                      uint8_t *out_dev, void *stream);
+/* Any-angle shortcut of the paths written by pmp_extract_paths (same layout, goal first): from
+ * each kept waypoint the grid path is followed while the next cell is still visible from it
+ * (the "path 2" test of ThetaStar.updateVertex, theta_star.py:96-108, applied to the extracted
+ * path).  out_path_dev: [nq][path_cap] kept waypoints (padded cell indices), out_len_dev their
+ * number (0: no path; -1: input length > path_cap), out_cost_dev the summed Euclidean lengths
+ * (Planner.dist, accumulated goal -> start). */
+int pmp_shortcut_paths(const pmp_grid *g, int64_t nq, const uint32_t *path_dev, int64_t path_cap,
+                       const int32_t *path_len_dev, uint32_t *out_path_dev, int32_t *out_len_dev,
+                       double *out_cost_dev, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -73,6 +73,8 @@ def lib():
         L.pmp_oracle_is_collision.restype = ctypes.c_int
         L.pmp_oracle_is_collision.argtypes = [ctypes.c_int, vp, vp, vp, vp]
         L.pmp_oracle_max_threads.restype = ctypes.c_int
+        L.pmp_oracle_line_of_sight.restype = ctypes.c_int
+        L.pmp_oracle_line_of_sight.argtypes = [ctypes.c_int, vp, vp, ctypes.c_int64, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -182,6 +184,22 @@ def plan_batch(occ, starts, goals, algo=DIJKSTRA, heuristic=EUCLIDEAN, motions=N
 def is_collision(occ, p1, p2):
     ndim, dims, occ_c, _, _ = _prep(occ, None, None)
     return bool(lib().pmp_oracle_is_collision(ndim, _p(dims), _p(occ_c), _p(_c3(p1)), _p(_c3(p2))))
+
+
+def line_of_sight(occ, a, b):
+    """ThetaStar.lineOfSight / ThetaStar3D.lineOfSight for pairs a[i] -> b[i] ((n, ndim) arrays)"""
+    ndim, dims, occ_c, _, _ = _prep(occ, None, None)
+    a = np.asarray(a, dtype=np.int32).reshape(-1, ndim)
+    b = np.asarray(b, dtype=np.int32).reshape(-1, ndim)
+    a3 = np.zeros((len(a), 3), dtype=np.int32)
+    b3 = np.zeros((len(a), 3), dtype=np.int32)
+    a3[:, :ndim] = a
+    b3[:, :ndim] = b
+    out = np.zeros(len(a), dtype=np.uint8)
+    rc = lib().pmp_oracle_line_of_sight(ndim, _p(dims), _p(occ_c), len(a), _p(a3), _p(b3), _p(out))
+    if rc != 0:
+        raise RuntimeError(f"pmp_oracle_line_of_sight failed: {rc}")
+    return out.astype(bool)
 
 
 def max_threads():

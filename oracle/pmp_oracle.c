@@ -479,3 +479,92 @@ int pmp_oracle_plan_batch(int ndim, const int32_t *dims, const uint8_t *occ,
     free(th);
     return b.rc;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * Line of sight (any-angle planners).
+ * ------------------------------------------------------------------------------------------- */
+
+/* ThetaStar.lineOfSight, global_planner/graph_search/theta_star.py:110-171.  The reference runs
+ * this Bresenham variant on Python floats (s_x = (x2 - x1) / d_x, tau = (d_y - d_x) / 2); every
+ * quantity is an integer or a half-integer, so it is restated on integers with e and tau doubled
+ * (e2 = 2 e, tau2 = 2 tau): the comparisons e > tau, e < tau are unchanged. */
+static int los2d(grid_t *g, int64_t x1, int64_t y1, int64_t x2, int64_t y2)
+{
+    if (occ_at(g, x1, y1, 0) || occ_at(g, x2, y2, 0)) return 0;        /* :122, :128-131 */
+    const int64_t d_x = llabs(x2 - x1), d_y = llabs(y2 - y1);
+    const int64_t s_x = (x2 > x1) - (x2 < x1), s_y = (y2 > y1) - (y2 < y1);
+    int64_t x = x1, y = y1, e2 = 0;
+    int64_t guard = 4 * (d_x + d_y) + 8;
+    if (d_x > d_y) {                                                    /* :140-153 */
+        const int64_t tau2 = d_y - d_x;
+        while (x != x2) {
+            if (e2 > tau2) { x += s_x; e2 -= 2 * d_y; }
+            else if (e2 < tau2) { y += s_y; e2 += 2 * d_x; }
+            else { x += s_x; y += s_y; e2 += 2 * (d_x - d_y); }
+            if (occ_at(g, x, y, 0)) return 0;
+            if (--guard < 0) return 0;
+        }
+    } else {                                                            /* :155-169 */
+        const int64_t tau2 = d_x - d_y;
+        while (y != y2) {
+            if (e2 > tau2) { y += s_y; e2 -= 2 * d_x; }
+            else if (e2 < tau2) { x += s_x; e2 += 2 * d_y; }
+            else { x += s_x; y += s_y; e2 += 2 * (d_y - d_x); }
+            if (occ_at(g, x, y, 0)) return 0;
+            if (--guard < 0) return 0;
+        }
+    }
+    return 1;
+}
+
+/* ThetaStar3D.lineOfSight, theta_star3d.py:139-215 (LazyThetaStar3D.lineOfSight,
+ * lazy_theta_star3d.py:158-235, is the same walk): integer 3D Bresenham along the dominant
+ * axis; in_bounds() = membership in env.grid_map = the box. */
+static int los3d(grid_t *g, int64_t x0, int64_t y0, int64_t z0, int64_t x1, int64_t y1, int64_t z1)
+{
+    if (occ_at(g, x0, y0, z0) || occ_at(g, x1, y1, z1)) return 0;      /* :148-149 */
+    const int64_t dx = llabs(x1 - x0), dy = llabs(y1 - y0), dz = llabs(z1 - z0);
+    const int64_t sx = x1 >= x0 ? 1 : -1, sy = y1 >= y0 ? 1 : -1, sz = z1 >= z0 ? 1 : -1;
+    int64_t x = x0, y = y0, z = z0;
+    if (dx >= dy && dx >= dz) {                                         /* :164-178 */
+        int64_t err_y = dx / 2, err_z = dx / 2;
+        while (x != x1) {
+            x += sx; err_y -= dy; err_z -= dz;
+            if (err_y < 0) { y += sy; err_y += dx; }
+            if (err_z < 0) { z += sz; err_z += dx; }
+            if (occ_at(g, x, y, z)) return 0;
+        }
+        return 1;
+    }
+    if (dy >= dx && dy >= dz) {                                         /* :180-194 */
+        int64_t err_x = dy / 2, err_z = dy / 2;
+        while (y != y1) {
+            y += sy; err_x -= dx; err_z -= dz;
+            if (err_x < 0) { x += sx; err_x += dy; }
+            if (err_z < 0) { z += sz; err_z += dy; }
+            if (occ_at(g, x, y, z)) return 0;
+        }
+        return 1;
+    }
+    int64_t err_x = dz / 2, err_y = dz / 2;                             /* :197-214 */
+    while (z != z1) {
+        z += sz; err_x -= dx; err_y -= dy;
+        if (err_x < 0) { x += sx; err_x += dz; }
+        if (err_y < 0) { y += sy; err_y += dz; }
+        if (occ_at(g, x, y, z)) return 0;
+    }
+    return 1;
+}
+
+int pmp_oracle_line_of_sight(int ndim, const int32_t *dims, const uint8_t *occ, int64_t n,
+                             const int32_t *a, const int32_t *b, uint8_t *out)
+{
+    if ((ndim != 2 && ndim != 3) || !dims || !occ || n < 0 || (n && (!a || !b || !out))) return -1;
+    grid_t g = { ndim, dims[0], dims[1], ndim == 3 ? dims[2] : 1, occ, 0 };
+    for (int64_t i = 0; i < n; ++i) {
+        const int32_t *p = a + 3 * i, *q = b + 3 * i;
+        out[i] = (uint8_t)(ndim == 2 ? los2d(&g, p[0], p[1], q[0], q[1])
+                                     : los3d(&g, p[0], p[1], p[2], q[0], q[1], q[2]));
+    }
+    return 0;
+}

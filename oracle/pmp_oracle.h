@@ -74,6 +74,12 @@ int pmp_oracle_plan_batch(int ndim, const int32_t *dims, const uint8_t *occ,
                           double *cost_out, int64_t *n_expand_out, int64_t *path_len_out,
                           int32_t *flags_out, int n_threads);
 
+/* ThetaStar.lineOfSight (theta_star.py:110-171, ndim 2) / ThetaStar3D.lineOfSight
+ * (theta_star3d.py:139-215, ndim 3) for n ordered pairs a[i] -> b[i] (n x 3 each);
+ * out[i] = 1 if the reference returns True.  Cells outside the box count as blocked. */
+int pmp_oracle_line_of_sight(int ndim, const int32_t *dims, const uint8_t *occ, int64_t n,
+                             const int32_t *a, const int32_t *b, uint8_t *out);
+
 /* GraphSearcher.isCollision (graph_search.py:61-87) / GraphSearcher3D.isCollision
  * (graph_search_3d.py:66-107) for one ordered pair of cells; 1 = collision. */
 int pmp_oracle_is_collision(int ndim, const int32_t *dims, const uint8_t *occ,

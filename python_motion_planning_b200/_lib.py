@@ -25,6 +25,7 @@ SYMBOLS = (
     "pmp_grid_set_motions", "pmp_sssp_sizes", "pmp_sssp", "pmp_field_finalize",
     "pmp_count_settled", "pmp_extract_paths", "pmp_verify_field", "pmp_gbfs",
     "pmp_slab_begin", "pmp_slab_run", "pmp_slab_merge", "pmp_replan_begin", "pmp_replan_update",
+    "pmp_line_of_sight", "pmp_shortcut_paths",
 )
 
 
@@ -92,6 +93,8 @@ def lib():
         "pmp_slab_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, i64, vp],
         "pmp_slab_run": [vp, ctypes.POINTER(SsspParams), vp, vp, i64, dbl, vp, vp],
         "pmp_slab_merge": [vp, i32, vp, vp, i64, i32, i32, vp, vp, vp],
+        "pmp_line_of_sight": [vp, i64, vp, vp, vp, vp],
+        "pmp_shortcut_paths": [vp, i64, vp, i64, vp, vp, vp, vp, vp],
         "pmp_replan_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, vp, i64, vp, vp, vp, vp],
         "pmp_replan_update": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, vp, i64, vp, vp, i64, vp, i64,
                               vp, vp, vp, vp],

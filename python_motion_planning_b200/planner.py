@@ -478,4 +478,10 @@ class SearchFactory(object):
         elif planner_name == "lpa_star":
             from .replan import LPAStar
             return LPAStar(**config)
+        elif planner_name == "theta_star":
+            from .anyangle import ThetaStar
+            return ThetaStar(**config)
+        elif planner_name == "lazy_theta_star":
+            from .anyangle import LazyThetaStar
+            return LazyThetaStar(**config)
         raise ValueError("The `planner_name` must be set correctly.")
