@@ -42,7 +42,23 @@ class Workspace:
             self.path_cap = cap
 
 
+_small_pool = {}   # (device, padded dims, nq, weight) -> Workspace, for grids whose field is snapshotted
+
+
 def get_workspace(dg, nq, weight):
+    """Buffers for nq searches on dg, reused across calls.  Small grids (<= 4 Mi cells, where
+    plan() hands out a private copy of the field for `expand`) share one pool across
+    environments of the same shape, so that planning on a freshly built Grid does not pay for
+    device and pinned-host allocations again; large grids keep their buffers per DeviceGrid."""
+    if dg.pcells <= (1 << 22):
+        key = (str(dg.device), dg.ndim, dg.padded, nq, weight)
+        ws = _small_pool.get(key)
+        if ws is None:
+            if len(_small_pool) >= 8:
+                _small_pool.clear()
+            ws = _small_pool[key] = Workspace(dg, nq, weight)
+        ws.dg = dg
+        return ws
     cache = dg.__dict__.setdefault("_ws_cache", {})
     key = (nq, weight)
     ws = cache.get(key)

@@ -12,6 +12,8 @@ import math
 import weakref
 from math import sqrt
 
+import itertools
+
 import numpy as np
 
 from . import _lib
@@ -320,7 +322,7 @@ class _EnvBase:
                 dg.set_dense(self._dense)
             else:
                 n = len(self._obstacles)
-                coords = np.fromiter((c for p in self._obstacles for c in p), dtype=np.int32,
+                coords = np.fromiter(itertools.chain.from_iterable(self._obstacles), dtype=np.int32,
                                      count=n * self._ndim).reshape(n, self._ndim)
                 dg.set_cells(coords)
             self._device_version = self._version

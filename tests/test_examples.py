@@ -1,0 +1,45 @@
+"""examples/benchmark.py: same CSV schema as the reference's
+benchmark writer (benchmark.py:39), and the rows it writes for the replayed instances agree with
+the reference's own 3d_pathfinding_results.csv (values committed in tests/golden/csv_replay.npz)."""
+import csv
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from tests import golden_io as gio
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = ["Scenario", "Algorithm", "Runtime (s)", "Distance", "Visited Nodes", "Start", "Goal", "Seed"]
+
+
+@pytest.mark.gpu
+def test_benchmark_writer_schema_and_known_answers(tmp_path):
+    out = tmp_path / "results.csv"
+    subprocess.run([sys.executable, os.path.join(ROOT, "examples", "benchmark.py"), "--out", str(out),
+                    "--iterations", "4", "--repeats", "2"], check=True, cwd=str(tmp_path), timeout=600)
+    rows = list(csv.reader(open(out)))
+    assert rows[0] == HEADER
+    body = [dict(zip(HEADER, r)) for r in rows[1:]]
+    assert len(body) == 5 * 6 * 4 * 2
+    z = gio.load("csv_replay.npz")
+    lz = gio.load("los.npz")
+    names = [str(s) for s in z["scen_names"]]
+    index = {(names[int(z["scen_idx"][k])], int(z["seeds"][k])): k for k in range(len(z["seeds"]))}
+    for r in body:
+        k = index[(r["Scenario"], int(r["Seed"]))]
+        assert eval(r["Start"]) == tuple(int(v) for v in z["starts"][k])
+        assert eval(r["Goal"]) == tuple(int(v) for v in z["goals"][k])
+        d, a = float(r["Distance"]), r["Algorithm"]
+        assert float(r["Runtime (s)"]) >= 0.0 and int(r["Visited Nodes"]) >= 1
+        if a in ("astar", "dijkstra", "gbfs"):
+            assert abs(d - float(z[f"{a}_csv_dist"][k])) <= 1e-9 * max(d, 1.0)
+        if a == "gbfs":
+            assert int(r["Visited Nodes"]) == int(z["gbfs_csv_vis"][k])
+        if a == "lpastar":                              # the reference's greedy extraction is never shorter
+            assert abs(d - float(z["dijkstra_csv_dist"][k])) <= 1e-9 * max(d, 1.0)
+        if a in ("theta_star", "lazy_theta_star"):
+            assert d <= float(z["astar_csv_dist"][k]) * (1 + 1e-9)
+            assert d <= float(lz[f"{a}_csv_dist"][k]) * 1.25
