@@ -50,29 +50,77 @@ def measured_peak():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled during the timed region"""
+    """SM clock and throttle reasons sampled DURING the timed region: NVML (nvidia_ml_py) polled by
+    a thread every few ms plus one explicit sample per step while the GPU is busy; nvidia-smi as
+    the fallback when NVML cannot be loaded."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"),
+               (0x4, "sw_power_cap"))
 
-    def __init__(self, index):
-        self.rows, self.proc = [], None
+    def __init__(self, index, uuid=None):
+        self.sm, self.mx, self.bits, self.rows = [], None, 0, []
+        self.proc, self.nvml, self.h, self.stop_flag = None, None, None, False
+        self.lock = threading.Lock()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid if isinstance(uuid, bytes) else str(uuid).encode()) \
+                    if uuid else pynvml.nvmlDeviceGetHandleByIndex(index)
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.th = threading.Thread(target=self._poll, daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
         except Exception:
             self.proc = None
 
+    def sample(self):
+        """one NVML sample now (called from the timed loop while kernels are in flight)"""
+        if self.nvml is None:
+            return
+        try:
+            c = float(self.nvml.nvmlDeviceGetClockInfo(self.h, self.nvml.NVML_CLOCK_SM))
+            try:
+                r = int(self.nvml.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+            except Exception:
+                r = int(self.nvml.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            with self.lock:
+                self.sm.append(c)
+                self.bits |= r
+        except Exception:
+            pass
+
+    def _poll(self):
+        while not self.stop_flag:
+            self.sample()
+            time.sleep(0.005)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self):
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.th.join(timeout=1)
+            reasons = sorted(n for b, n in self.REASONS if self.bits & b)
+            return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.mx,
+                    "reasons": reasons, "samples": len(self.sm), "source": "nvml"}
         if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
@@ -89,7 +137,7 @@ class ClockSampler:
             except Exception:
                 pass
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -371,7 +419,11 @@ def main():
         W["run"](i)
     torch.cuda.synchronize()
     edges, settled, abytes, check = W["account"]()
-    sampler = ClockSampler(local_rank)
+    try:
+        uuid = "GPU-" + str(torch.cuda.get_device_properties(local_rank).uuid)
+    except Exception:
+        uuid = None
+    sampler = ClockSampler(local_rank, uuid)
     barrier()
     evs, launches = [], 0
     t_wall0 = time.perf_counter()
@@ -381,6 +433,7 @@ def main():
         e0.record()
         launches += W["run"](i)
         e1.record()
+        sampler.sample()                           # the step's kernels are still in flight
         evs.append((e0, e1))
     barrier()
     t_wall = time.perf_counter() - t_wall0

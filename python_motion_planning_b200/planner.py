@@ -478,6 +478,12 @@ class SearchFactory(object):
         elif planner_name == "lpa_star":
             from .replan import LPAStar
             return LPAStar(**config)
+        elif planner_name == "d_star":
+            from .replan import DStar
+            return DStar(**config)
+        elif planner_name == "d_star_lite":
+            from .replan import DStarLite
+            return DStarLite(**config)
         elif planner_name == "theta_star":
             from .anyangle import ThetaStar
             return ThetaStar(**config)

@@ -220,6 +220,56 @@ class LPAStar3D(_ReplanMixin, GraphSearcher3D):
         self.plot.animation(path, str(self), cost, self.EXPAND)
 
 
+class DStarLite(LPAStar):
+    """d_star_lite.py:14-187: same (g, rhs) repair as LPA*, searched from the goal; plan() and
+    the toggling OnPress have the LPA* signatures, the path is start -> goal"""
+
+    def __str__(self) -> str:
+        return "D* Lite"
+
+
+class DStar(_ReplanMixin, GraphSearcher):
+    """d_star.py:38-291: plan() -> (cost, path start -> goal, None); OnPress only ADDS an obstacle
+    (d_star.py:102-134) and repairs"""
+    _node_cls = Node
+
+    def __init__(self, start: tuple, goal: tuple, env) -> None:
+        GraphSearcher.__init__(self, start, goal, env, None)
+        self._init_replan()
+
+    def __str__(self) -> str:
+        return "Dynamic A*(D*)"
+
+    def OnPress(self, event) -> None:
+        xy = (int(event.xdata), int(event.ydata))
+        if any(v < 0 or v > r - 1 for v, r in zip(xy, self.env._dims())):
+            print("Please choose right area!")
+        elif xy not in self.obstacles:
+            print("Add obstacle at: ({}, {})".format(*xy))
+            self.apply_change(xy, True)
+
+    def run(self) -> None:
+        cost, path, _ = self.plan()
+        self.plot.animation(path, str(self), cost=cost)
+
+
+class DStar3D(_ReplanMixin, GraphSearcher3D):
+    """d_star3d.py:60-280: plan() -> (cost, path start -> goal, expand);
+    apply_dynamic_obstacles(newly_blocked) -> (cost, path) (d_star3d.py:115-151)"""
+    _node_cls = Node3D
+
+    def __init__(self, start: tuple, goal: tuple, env) -> None:
+        GraphSearcher3D.__init__(self, start, goal, env, None)
+        self._init_replan()
+
+    def __str__(self) -> str:
+        return "Dynamic A* (D*) 3D"
+
+    def run(self) -> None:
+        cost, path, expand = self.plan()
+        self.plot.animation(path, str(self), cost, expand)
+
+
 class DynamicField:
     """A full cost-to-go field that follows map edits: cost_field() once, then update()."""
 

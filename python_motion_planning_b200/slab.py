@@ -51,7 +51,7 @@ class CudaSlabEngine:
         self.dg = env.device_grid()
         self.dg.set_motions(*motion_table(env, 3))
         self.weight = _lib.W_U32 if weight == "u32" else _lib.W_F64
-        self.ws = _engine.get_workspace(self.dg, 1, self.weight)
+        self.ws = _engine.Workspace(self.dg, 1, self.weight)   # private: the slab field lives across calls
         t = self.dg.torch
         self.torch = t
         self.P = _lib.SsspParams(algo=_lib.DIJKSTRA, heuristic=0, weight=self.weight, full_field=1,

@@ -236,3 +236,45 @@ def test_lpa_star_unreachable_then_reachable_and_start_toggle():
     want = optimum(occ, (5, 5), (35, 25))
     assert math.isfinite(want) and abs(cost - want) <= REL * want
     check_path(occ, path, (5, 5), (35, 25))
+
+
+@pytest.mark.gpu
+def test_d_star_entry_points():
+    """DStar / DStar3D / DStarLite: the reference's signatures over the same repair engine"""
+    import types
+    import python_motion_planning_b200 as pmp
+    occ = np.zeros((30, 24), dtype=bool)
+    occ[0, :] = occ[-1, :] = True
+    occ[:, 0] = occ[:, -1] = True
+    occ[15, 1:12] = True
+    env = make_env(pmp, occ)
+    d = pmp.SearchFactory()("d_star", start=(3, 3), goal=(26, 20), env=env)
+    cost, path, none = d.plan()
+    assert none is None and path[0] == (3, 3) and path[-1] == (26, 20)
+    assert abs(cost - optimum(occ, (3, 3), (26, 20))) <= REL * cost
+    blocked = path[len(path) // 2]
+    d.OnPress(types.SimpleNamespace(xdata=blocked[0] + 0.3, ydata=blocked[1] + 0.6))   # adds an obstacle
+    occ[blocked] = True
+    cost2, path2, _ = d.plan()
+    assert blocked in env.obstacles and blocked not in path2
+    assert abs(cost2 - optimum(occ, (3, 3), (26, 20))) <= REL * cost2
+    d.OnPress(types.SimpleNamespace(xdata=blocked[0], ydata=blocked[1]))               # D* never removes
+    assert blocked in env.obstacles
+    lite = pmp.SearchFactory()("d_star_lite", start=(3, 3), goal=(26, 20), env=make_env(pmp, occ))
+    assert abs(lite.plan()[0] - cost2) <= REL * cost2
+    lite.OnPress(types.SimpleNamespace(xdata=blocked[0], ydata=blocked[1]))            # D* Lite toggles
+    assert abs(lite.plan()[0] - cost) <= REL * cost
+    occ3 = random_boxes((20, 16, 12), 25, 4, 9)
+    free = np.argwhere(~occ3)
+    s, g = tuple(int(v) for v in free[0]), tuple(int(v) for v in free[-1])
+    d3 = pmp.DStar3D(s, g, make_env(pmp, occ3))
+    c3, p3, e3 = d3.plan()
+    want = optimum(occ3, s, g)
+    if math.isfinite(want):
+        assert abs(c3 - want) <= REL * want and len(e3) > 0
+        mid = p3[len(p3) // 2]
+        if mid not in (s, g):
+            occ3[mid] = True
+            c4, p4 = d3.apply_dynamic_obstacles([mid])
+            want = optimum(occ3, s, g)
+            assert (math.isinf(want) and p4 == []) or abs(c4 - want) <= REL * want
