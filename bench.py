@@ -239,7 +239,7 @@ def build_workload(args, rank, torch, pmp, workloads):
         blk, _ = workloads.replicated_boxes3d(base=128, reps=max(1, n // 128))
         h0, h1 = slab.ghost_range(n, rank, world)
         eng = slab.CudaSlabEngine(slab.build_local_env(workloads.replicated_slab(blk, (n, n, n), h0, h1), "6"), "u32")
-        drv = slab.SlabDriver(eng, n, rank, world, dist, outer_window=256.0)
+        drv = slab.SlabDriver(eng, n, rank, world, dist, outer_window=512.0)
         src = (1, 1, 1)
 
         def run(step):
@@ -258,7 +258,7 @@ def build_workload(args, rank, torch, pmp, workloads):
 
         return dict(run=run, account=account, e2e=e2e, dtype="u32", queries=1, scaling="strong",
                     name=f"c5: full cost-to-go field, {n}^3 6-connected unit weights (u32), {world} z-slabs, NCCL halo exchange",
-                    cfg={"grid": [n, n, n], "connectivity": 6, "slabs": world, "outer_window": 256})
+                    cfg={"grid": [n, n, n], "connectivity": 6, "slabs": world, "outer_window": 512})
     if wl == "c5":
         n = args.n or 768
         blk, _ = workloads.replicated_boxes3d(base=128, reps=max(1, n // 128))

@@ -1044,8 +1044,11 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
     // only bounds how far ahead of the smallest pending key work may run: wide for full sweeps
     // (few rounds), narrow for A-star, whose keys g + h span a small range and where everything
     // above the final cost is wasted.  Integer (unit) weights re-relax least when run far ahead.
+    // The bit-parallel unit-weight solver settles whole tiles per activation and the ring is FIFO, so
+    // the cascade already runs in near-BFS order: no window at all is fastest there (768^3: 22 ms
+    // against 31 ms with a 256-wide window).
     if (!(window > 0.0))
-        window = (A.use_h ? 6.0 : (P->weight == PMP_W_U32 ? 256.0 : 48.0)) * g->wmin;
+        window = A.bfs ? 4.0e9 : (A.use_h ? 6.0 : (P->weight == PMP_W_U32 ? 256.0 : 96.0)) * g->wmin;
     if (P->weight == PMP_W_U32 && window < 1.0) window = 1.0;
     A.window = window;
 

@@ -132,7 +132,7 @@ class CudaSlabEngine:
 class SlabDriver:
     """The exchange protocol of one rank.  `dist` is torch.distributed (or None / world 1)."""
 
-    def __init__(self, engine, Z, rank=0, world=1, dist=None, outer_window=64.0):
+    def __init__(self, engine, Z, rank=0, world=1, dist=None, outer_window=512.0):
         self.e, self.Z, self.rank, self.world, self.dist = engine, Z, rank, world, dist
         self.z0, self.z1 = slab_range(Z, rank, world)
         self.h0, self.h1 = ghost_range(Z, rank, world)
@@ -245,7 +245,7 @@ def build_local_env(occ_local, motions="6"):
     return env
 
 
-def solve_in_process(engines, Z, source_global, outer_window=64.0, max_iterations=1_000_000):
+def solve_in_process(engines, Z, source_global, outer_window=512.0, max_iterations=1_000_000):
     """The same protocol with every slab held by ONE process (slabs of a grid too large for one
     field buffer processed in turn on one GPU, or the single-GPU check of the multi-GPU path):
     `engines[p]` holds slab p of `len(engines)`; planes are handed over by device copies instead

@@ -20,7 +20,7 @@ sys.path.insert(0, ROOT)
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--size", dest="n", type=int, default=768)
-    ap.add_argument("--outer-window", type=float, default=256.0)
+    ap.add_argument("--outer-window", type=float, default=512.0)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=1)
     ap.add_argument("--verify", action="store_true")
