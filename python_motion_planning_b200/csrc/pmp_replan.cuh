@@ -247,8 +247,7 @@ extern "C" int pmp_replan_update(pmp_grid *g, const pmp_sssp_params *P, const in
     }
     cudaStream_t s = (cudaStream_t)stream;
     SsspArgs A;
-    fill_args(g, P, 1, start_dev, goal_dev, g_dev, ws_dev, L, A);
-    A.no_prune = 1;
+    fill_args(g, P, 1, start_dev, goal_dev, g_dev, ws_dev, L, A, 1);
     u32 *ctl = scratch_dev, *queue = scratch_dev + PMP_REPLAN_CTL;
     int64_t cap64 = (scratch_words - PMP_REPLAN_CTL) / 2;
     const u32 qcap = cap64 > 0x7FFFFFFF ? 0x7FFFFFFFu : (u32)cap64;

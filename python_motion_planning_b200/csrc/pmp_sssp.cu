@@ -92,6 +92,7 @@ struct TileSmem {
     u64 nbrmin[27];         // smallest key pushed into each neighbour tile
     u64 kmin[2];            // min key of the pending cells (computed on empty sub-iterations)
     u64 T, U, k0;
+    u64 Tlim;               // banded mode: the popped band's upper key bound (KEY_INF otherwise)
     u32 chg[C::NCW];        // cells (tile + halo, by halo'd index) lowered during this activation
     union {
         ulonglong2 fq[NT / 32][C::NCELL / (NT / 32)]; // per-warp frontier records: .x = value, .y = free mask | halo'd index << 32
@@ -131,6 +132,9 @@ struct SsspArgs {
     u32 *ctr;      // per round parity p: [p] ring tail, [2+p] ring head, [4+p] live tiles, [6+p] tiles in flight
     u64 *stats;    // 16 counters, see include/pmp_b200.h (pmp_sssp)
     double window, sub, he, hm;
+    int nbands;   // > 1: the ring is split into key bands served lowest first (single A-star queries)
+    double inv_band_w; // 1 / band width
+    u32 *rb;      // banded mode: [parity][avail | head | tail][32] counters
     int no_prune; // replanning: keep relaxations that cannot beat the current g[goal] (pmp_replan.cuh)
     u64 key_cap; // slab mode: only keys below this bound are processed (KEY_INF otherwise)
     int use_h, full_field, max_rounds;
@@ -399,6 +403,56 @@ __device__ PMP_BFS_ATTR BfsIo solve_bfs(TileSmem<C> &S, const SsspArgs &A, const
 }
 
 // ---------------------------------------------------------------------------------------------
+// Banded ring (single A-star queries).  Inside a round the window [T - W, T) is cut into `nbands`
+// key bands, each with its own FIFO ring; CTAs always serve the lowest non-empty band and a tile
+// popped from band b only works up to that band's upper bound, re-queueing itself for the rest.
+// The cascade therefore runs in approximate key order (little re-relaxation, like a narrow
+// window) while every band of the wide window is available as parallel work (no barrier per band).
+// Counters per band: avail (a semaphore: completed pushes minus reservations), head (pop tickets),
+// tail (push tickets).  A pop reserves an item on the semaphore first and only then takes a
+// ticket, so a ticket never runs ahead of the pushes; the slot of a ticket may still be in flight
+// (a later push completed first) and is then awaited for a moment.
+// ---------------------------------------------------------------------------------------------
+#define PMP_MAXBANDS 16
+#ifndef PMP_DEFAULT_BANDS
+#define PMP_DEFAULT_BANDS 12 // measured on c4 (512^3 A-star): FIFO ring + window 6: 6.6 ms; 12 bands x 3: 5.6 ms
+#endif
+#ifndef PMP_BANDED_WINDOW
+#define PMP_BANDED_WINDOW 36.0 // key window of a round in banded mode (x smallest edge cost)
+#endif
+__device__ static inline u64 band_top(const SsspArgs &A, int b, u64 Tw) {
+    if (b >= A.nbands - 1) return Tw;
+    const double t = __longlong_as_double((long long)Tw) - (double)(A.nbands - 1 - b) / A.inv_band_w;
+    return t > 0.0 ? (u64)__double_as_longlong(t) : 0ull;
+}
+// the band of key k (< Tw) = the first band whose top lies above k.  Defined through band_top so
+// that a tile served up to band_top(b) always continues in a band > b, also for keys that sit
+// exactly on a boundary (an independent rounding here could send it back to band b for ever).
+__device__ static inline int band_of(const SsspArgs &A, u64 k, u64 Tw) {
+    const double d = __longlong_as_double((long long)Tw) - __longlong_as_double((long long)k); // > 0
+    int b = A.nbands - 1 - (int)(d * A.inv_band_w);
+    b = b < 0 ? 0 : (b > A.nbands - 1 ? A.nbands - 1 : b);
+    while (b < A.nbands - 1 && k >= band_top(A, b, Tw)) ++b;
+    while (b > 0 && k < band_top(A, b - 1, Tw)) --b;
+    return b;
+}
+// append (query, tile) gt to the ring of round parity `cur`; k = the key that brings it in
+__device__ static inline void ring_push(const SsspArgs &A, int cur, u32 gt, u64 k, u64 Tw) {
+    atomicAdd(&A.ctr[6 + cur], 1u); // in flight (queued or being processed)
+    if (A.nbands <= 1) {
+        const u32 pos = atomicAdd(&A.ctr[cur], 1u);
+        *(volatile u32 *)&A.wl[0][pos % A.ring_cap] = gt + 1u;
+        return;
+    }
+    const int b = band_of(A, k, Tw);
+    u32 *c = A.rb + cur * 96;
+    const u32 pos = atomicAdd(&c[64 + b], 1u);
+    *(volatile u32 *)&A.wl[0][(size_t)b * A.ring_cap + pos % A.ring_cap] = gt + 1u;
+    fence_gpu();
+    atomicAdd(&c[b], 1u);
+}
+
+// ---------------------------------------------------------------------------------------------
 // one tile activation
 //
 // Owner-computes push.  Every thread owns 4 cells of the tile and keeps their search state in
@@ -458,6 +512,17 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     }
     for (int i = tid; i < C::NCW; i += NT) S.chg[i] = 0;
     __syncthreads(); // the claim is ordered before every load of g below
+    if (A.nbands > 1) {
+        const u64 k0 = S.k0, tw = S.T, tl = S.Tlim < tw ? S.Tlim : tw;
+        if (k0 == KEY_INF) return; // a duplicate entry of a tile that was served already
+        if (k0 >= tl) {            // queued for an earlier band than its keys: hand it on unopened
+            if (tid == 0) {
+                const u64 was = atomicMin(&A.minkey[gt], k0);
+                if (k0 < tw && was >= tw) ring_push(A, cur, gt, k0, tw);
+            }
+            return;
+        }
+    }
 
     // ---- stage the raw cost words (tile + halo); while the loads are in flight, set up the
     // per-thread state of the owned cells that depends only on the occupancy and the position ----
@@ -517,7 +582,8 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
     ulonglong2 *wq = S.fq[tid >> 5];
 
     const u32 t_loaded = (u32)clock64();
-    const u64 T = S.T, U = S.U;
+    const u64 Tw = S.T, U = S.U;                       // Tw: top of the round's window
+    const u64 T = S.Tlim < Tw ? S.Tlim : Tw;          // this activation works on keys below T
     // exclusive upper key of the current sub-bucket.  The claimed minkey is a lower bound of the
     // smallest pending key, so the first bucket is usually non-empty.
     u64 B = 0;
@@ -680,15 +746,19 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
             const int sx = tid % 3 - 1, sy = (tid / 3) % 3 - 1, sz = tid / 9 - 1;
             const u32 ngt = q * Gd.ntiles + (u32)(((ttz + sz) * Gd.nty + (tty + sy)) * Gd.ntx + (ttx + sx));
             const u64 was = atomicMin(&A.minkey[ngt], k);
-            if (k < T && was >= T) { // enters the window now: not queued yet (see the claim)
-                atomicAdd(&A.ctr[6 + cur], 1u);
-                const u32 pos = atomicAdd(&A.ctr[cur], 1u);
-                *(volatile u32 *)&A.wl[0][pos % A.ring_cap] = ngt + 1u;
+            if (k < Tw) {
+                if (was >= Tw) ring_push(A, cur, ngt, k, Tw); // enters the window now: not queued yet (see the claim)
+                else if (A.nbands > 1 && band_of(A, k, Tw) < band_of(A, was, Tw))
+                    ring_push(A, cur, ngt, k, Tw);            // queued in a later band: a second, earlier entry
             }
         }
     }
     if (tid == 32) {
-        if (km_final != KEY_INF) atomicMin(&A.minkey[gt], km_final);
+        if (km_final != KEY_INF) {
+            const u64 was = atomicMin(&A.minkey[gt], km_final);
+            // banded mode: the rest of this tile's window keys belongs to a later band
+            if (km_final < Tw && was >= Tw) ring_push(A, cur, gt, km_final, Tw);
+        }
         const u32 t_end = (u32)clock64();
         S.stat[1] += 1; S.stat[2] += S.n_exp; S.n_exp = 0;   // per-CTA counters, flushed once at kernel end
         S.stat[3] += S.n_edge; S.n_edge = 0;
@@ -698,6 +768,50 @@ __device__ void process_tile(const SsspArgs &A, const u32 gt, const int cur, Til
         S.stat[12] += n_iter;
     }
     __syncthreads();
+}
+
+// warp 0 of the CTA: take the next tile from the lowest non-empty band (S.item = 0: round over)
+template <class C>
+__device__ void banded_pop(const SsspArgs &A, const int cur, TileSmem<C> &S) {
+    const int lane = threadIdx.x & 31;
+    u32 *c = A.rb + cur * 96;
+    u32 v = 0;
+    int bsel = 0;
+    unsigned ns = 20, spins = 0;
+    for (;;) {
+        const int av = lane < A.nbands ? (int)ld_cg(&c[lane]) : 0;
+        const u32 m = __ballot_sync(0xFFFFFFFFu, av > 0);
+        if (m) {
+            const int b = __ffs(m) - 1;
+            u32 ticket = 0xFFFFFFFFu;
+            if (lane == b) {
+                if ((int)atomicSub(&c[b], 1u) > 0) ticket = atomicAdd(&c[32 + b], 1u); // reserved, then numbered
+                else atomicAdd(&c[b], 1u);                                             // lost the race: give it back
+            }
+            ticket = __shfl_sync(0xFFFFFFFFu, ticket, b);
+            if (ticket == 0xFFFFFFFFu) continue;
+            if (lane == 0) {
+                u32 *slot = &A.wl[0][(size_t)b * A.ring_cap + ticket % A.ring_cap];
+                unsigned w = 0;
+                while ((v = ld_cg(slot)) == 0 && ++w < (1u << 24)) { } // the push of this ticket is in flight
+                if (v) { fence_gpu(); *(volatile u32 *)slot = 0; }
+                else A.stats[15] = 0xDEADu;
+            }
+            bsel = b;
+            break;
+        }
+        int fl = 0;
+        if (lane == 0) fl = ld_cg(&A.ctr[6 + cur]) == 0;
+        if (__shfl_sync(0xFFFFFFFFu, fl, 0)) break; // nothing queued or being processed: nobody can append
+        __nanosleep(ns);
+        if (ns < 160) ns *= 2;
+        if (++spins > (1u << 22)) { if (lane == 0) A.stats[15] = 0xDEADu; break; } // safety net (seconds)
+    }
+    if (lane == 0) {
+        S.item = v;
+        const u32 q = v ? (v - 1u) / A.G.ntiles : 0u;
+        S.Tlim = v ? band_top(A, bsel, ld_cg(&A.T[cur][q])) : KEY_INF;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -731,6 +845,7 @@ __global__ void __launch_bounds__(NT, MINB) k_sssp(const __grid_constant__ SsspA
         for (u32 base = blockIdx.x * NT; base < total; base += gstride) {
             const u32 gt = base + tid;
             bool live = false, take = false;
+            u64 kk = KEY_INF, tw = 0;
             if (gt < total) {
                 const u64 k = ld_cg(&A.minkey[gt]);
                 if (k != KEY_INF) {
@@ -739,12 +854,18 @@ __global__ void __launch_bounds__(NT, MINB) k_sssp(const __grid_constant__ SsspA
                         if (k < ld_cg(&A.qmin[cur][q])) atomicMin(&A.qmin[cur][q], k);
                         if (k < A.key_cap) {
                             live = true;
-                            take = k < ld_cg(&A.T[cur][q]);
+                            kk = k;
+                            tw = ld_cg(&A.T[cur][q]);
+                            take = k < tw;
                         }
                     }
                 }
             }
             my_live += live;
+            if (A.nbands > 1) { // banded ring: every tile goes to the band of its key
+                if (take) ring_push(A, cur, gt, kk, tw);
+                continue;
+            }
             const u32 m = __ballot_sync(0xFFFFFFFFu, take);
             if (m) {
                 u32 pos = 0;
@@ -791,13 +912,17 @@ __global__ void __launch_bounds__(NT, MINB) k_sssp(const __grid_constant__ SsspA
             A.ctr[nxt] = 0; A.ctr[2 + nxt] = 0; A.ctr[4 + nxt] = 0; A.ctr[6 + nxt] = 0;
             A.stats[0] = (u64)(r + 1);
         }
+        if (A.nbands > 1 && blockIdx.x == 0 && tid < 96) A.rb[nxt * 96 + tid] = 0;
 
         // ---- PROCESS: asynchronous cascade.  The ring holds the tiles whose smallest pending key
         // lies inside the window; a tile that pushes such a key into a neighbour appends the
         // neighbour itself (process_tile), so the wave crosses many tiles per round without a
         // grid barrier.  The round ends when no tile is queued or being processed.
         for (;;) {
-            if (tid == 0) {
+            if (A.nbands > 1) {
+                if (tid < 32) banded_pop<C>(A, cur, S);
+            } else if (tid == 0) {
+                S.Tlim = KEY_INF;
                 const u32 ticket = atomicAdd(&A.ctr[2 + cur], 1u);
                 u32 *slot = &A.wl[0][ticket % A.ring_cap];
                 u32 v;
@@ -956,7 +1081,8 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 // the slot of a queued tile (at most one ticket per CTA is outstanding beyond the tail).
 #define RING_SLACK 1024
 struct WsLayout {
-    size_t minkey, wl0, wl1, qmin0, qmin1, T0, T1, done, goalcell, ctr, stats, total;
+    size_t minkey, wl0, wl1, qmin0, qmin1, T0, T1, done, goalcell, ctr, stats, rb, total;
+    size_t ring_words; // u32 words of the ring area (all bands)
 };
 
 static WsLayout ws_layout(const pmp_grid *g, int64_t nq) {
@@ -964,7 +1090,9 @@ static WsLayout ws_layout(const pmp_grid *g, int64_t nq) {
     const size_t nt = (size_t)nq * g->d.ntiles;
     size_t o = 0;
     L.minkey = o; o = align_up(o + nt * 8, 256);
-    L.wl0 = o; o = align_up(o + (nt + RING_SLACK) * 4, 256);
+    // a single query may run the banded ring: one ring per band
+    L.ring_words = (nt + RING_SLACK) * (size_t)(nq == 1 ? PMP_MAXBANDS : 1);
+    L.wl0 = o; o = align_up(o + L.ring_words * 4, 256);
     L.wl1 = o; o = align_up(o + nt * 4, 256);
     L.qmin0 = o; o = align_up(o + (size_t)nq * 8, 256);
     L.qmin1 = o; o = align_up(o + (size_t)nq * 8, 256);
@@ -974,6 +1102,7 @@ static WsLayout ws_layout(const pmp_grid *g, int64_t nq) {
     L.goalcell = o; o = align_up(o + (size_t)nq * 4, 256);
     L.ctr = o; o = align_up(o + 16 * 4, 256);
     L.stats = o; o = align_up(o + 16 * 8, 256);
+    L.rb = o; o = align_up(o + 2 * 96 * 4, 256);
     L.total = o;
     return L;
 }
@@ -1043,10 +1172,12 @@ static int dispatch_sssp(pmp_grid *g, int weight, SsspArgs &A, double *gcost_dev
 }
 
 static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const int32_t *starts_dev,
-                      const int32_t *goals_dev, void *g_dev, void *ws_dev, const WsLayout &L, SsspArgs &A) {
+                      const int32_t *goals_dev, void *g_dev, void *ws_dev, const WsLayout &L, SsspArgs &A,
+                      int no_prune = 0) {
     char *ws = (char *)ws_dev;
     memset(&A, 0, sizeof A);
     A.key_cap = KEY_INF;
+    A.no_prune = no_prune;
 
     A.G = g->d;
     for (int d = 0; d < 27; ++d) { A.wdir[d] = ~0ull; A.need[d] = 0xFFFFFFFFu; }
@@ -1081,6 +1212,7 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
     A.goalcell = (u32 *)(ws + L.goalcell);
     A.ctr = (u32 *)(ws + L.ctr);
     A.stats = (u64 *)(ws + L.stats);
+    A.rb = (u32 *)(ws + L.rb);
     A.full_field = P->full_field ? 1 : 0;
     A.max_rounds = P->max_rounds;
     A.sub = g->wmin;
@@ -1108,6 +1240,19 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
     if (!(window > 0.0))
         window = A.bfs ? 4.0e9 : (A.use_h ? 6.0 : (P->weight == PMP_W_U32 ? 256.0 : 96.0)) * g->wmin;
     if (P->weight == PMP_W_U32 && window < 1.0) window = 1.0;
+    // Single A-star queries on fp64 fields: banded ring (see ring_push).  PMP_B200_BANDS overrides.
+    A.nbands = 1;
+    // (not for repairable searches: without the g[goal] pruning a wide window is all wasted work)
+    if (A.use_h && nq == 1 && P->weight == PMP_W_F64 && !no_prune) {
+        const char *e = getenv("PMP_B200_BANDS");
+        int nb = e ? atoi(e) : (g->d.ntiles >= 256 ? PMP_DEFAULT_BANDS : 1); // tiny grids: launch-bound, keep the plain ring
+        if (nb > PMP_MAXBANDS) nb = PMP_MAXBANDS;
+        if (nb > 1) {
+            A.nbands = nb;
+            if (!(P->window > 0.0) && !getenv("PMP_B200_WINDOW")) window = PMP_BANDED_WINDOW * g->wmin;
+        }
+    }
+    A.inv_band_w = (double)A.nbands / window;
     A.window = window;
 
 }
@@ -1141,13 +1286,13 @@ static int sssp_from_scratch(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, 
     }
     cudaStream_t s = (cudaStream_t)stream;
     SsspArgs A;
-    fill_args(g, P, nq, starts_dev, goals_dev, g_dev, ws_dev, L, A);
-    A.no_prune = no_prune;
+    fill_args(g, P, nq, starts_dev, goals_dev, g_dev, ws_dev, L, A, no_prune);
     const size_t gsz = (size_t)nq * g->d.pcells * (P->weight == PMP_W_F64 ? 8 : 4);
     PMP_CHECK_CUDA(cudaMemsetAsync(g_dev, 0xFF, gsz, s));
     const size_t nt = (size_t)nq * g->d.ntiles;
     PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, nt * 8, s));
-    PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[0], 0, (nt + RING_SLACK) * 4, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[0], 0, L.ring_words * 4, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.rb, 0, 2 * 96 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 16 * 8, s));
 
@@ -1272,7 +1417,8 @@ extern "C" int pmp_slab_begin(pmp_grid *g, const pmp_sssp_params *P, const int32
     fill_args(g, &Q, 1, start_dev, nullptr, g_dev, ws_dev, L, A);
     PMP_CHECK_CUDA(cudaMemsetAsync(g_dev, 0xFF, (size_t)g->d.pcells * (Q.weight == PMP_W_F64 ? 8 : 4), s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.minkey, 0xFF, (size_t)g->d.ntiles * 8, s));
-    PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[0], 0, ((size_t)g->d.ntiles + RING_SLACK) * 4, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.wl[0], 0, L.ring_words * 4, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.rb, 0, 2 * 96 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, 16 * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 16 * 8, s));
     if (start_dev) return dispatch_sssp(g, Q.weight, A, nullptr, nullptr, s, 1);
