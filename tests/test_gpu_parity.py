@@ -449,3 +449,43 @@ def test_abi_rejects_bad_arguments():
     assert L.pmp_sssp(h, ctypes.byref(P), 1, q.data_ptr(), q.data_ptr(), g.data_ptr(), ws.data_ptr(), 16,
                       None, None, None, None) < 0 and b"workspace" in L.pmp_last_error()
     assert L.pmp_grid_destroy(h) == 0
+
+
+@pytest.mark.parametrize("bands,window", [("12", None), ("16", "4"), ("3", "1.5"), ("1", None)])
+def test_astar_banded_ring_vs_oracle(monkeypatch, bands, window):
+    """single A* queries use the banded ring on grids of >= 256 tiles; force it (and narrow,
+    multi-round windows) on mazes small enough for the oracle, in 2D and 3D"""
+    monkeypatch.setenv("PMP_B200_BANDS", bands)
+    if window:
+        monkeypatch.setenv("PMP_B200_WINDOW", window)
+    rng = np.random.default_rng(21)
+    occ2 = rng.random((190, 170)) < 0.28
+    occ2[0, :] = occ2[-1, :] = True
+    occ2[:, 0] = occ2[:, -1] = True
+    occ2[60, 1:150] = True                       # long detours: the key range spans many bands
+    occ2[120, 20:-1] = True
+    free = np.argwhere(~occ2)
+    env = make_env(occ2)
+    for i in range(6):
+        s, g = tuple(int(v) for v in free[7 + 31 * i]), tuple(int(v) for v in free[-(11 + 57 * i)])
+        want = oracle.plan(occ2, s, g, algo=oracle.DIJKSTRA, want_expand=False)
+        res = pmp.AStar(s, g, env).plan()
+        if not want.reached:
+            assert res == ([], [], [])
+            continue
+        cost, path, _ = res
+        assert abs(cost - want.cost) <= REL * want.cost
+        check_path(occ2, path, s, g, "goal_first", oracle.MOTIONS_2D)
+    occ3 = random_boxes((61, 47, 39), 260, 7, 13)
+    occ3[30, 1:40, 1:-1] = True                  # a wall with a gap at the far end
+    free = np.argwhere(~occ3)
+    env3 = make_env(occ3)
+    for i in range(4):
+        s, g = tuple(int(v) for v in free[5 + 17 * i]), tuple(int(v) for v in free[-(9 + 23 * i)])
+        want = oracle.plan(occ3, s, g, algo=oracle.DIJKSTRA, want_expand=False)
+        cost, path, _ = pmp.AStar3D(s, g, env3).plan()
+        if not want.reached:
+            assert math.isinf(cost) and path == []
+            continue
+        assert abs(cost - want.cost) <= REL * want.cost
+        check_path(occ3, path, s, g, "start_first", oracle.MOTIONS_3D)
