@@ -11,6 +11,8 @@
 // query, lanes evaluate the motions of the popped cell in parallel, lane 0 keeps the binary
 // heap with CPython heapq's sift order (the 2D heap is ordered by Node.__lt__,
 // utils/environment/node.py:51-54, which is not a total order).
+#include <stdlib.h>
+
 #include "pmp_common.cuh"
 
 // 64-bit / 32-bit warp minimum with the hardware reductions (REDUX works on 32-bit words)
@@ -93,6 +95,92 @@ __global__ void k_extract_paths(const GridDev G, const __grid_constant__ Motions
     if (lane == 0) { plen[q] = result; cost[q] = c; }
 }
 
+// Few queries (one CTA each): the walk is a chain of dependent loads, ~1.2 us per step from
+// L2.  Here the CTA stages a 16^3 (2D: 16^2) box of the field and its occupancy rows around the
+// current cell in shared memory, warp 0 walks inside it -- same candidates, same tie-break, same
+// summation as k_extract_paths, so the path is identical -- and the box is re-centred when the walk
+// reaches its border (every ~7 steps).
+#define XB 16
+template <class W>
+__global__ void __launch_bounds__(256) k_extract_paths_box(const GridDev G, const __grid_constant__ Motions M, u32 nq,
+                                                           const int32_t *starts, const int32_t *goals,
+                                                           const typename W::G *g, u32 *path, int64_t cap,
+                                                           int32_t *plen, double *cost) {
+    typedef typename W::G GT;
+    __shared__ GT box[XB * XB * XB];
+    __shared__ u32 occ[XB * XB];   // bit i of row (y, z): cell (bx + i, by + y, bz + z) blocked
+    __shared__ int st[8];          // vx, vy, vz, finished
+    const u32 q = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const GT *gq = g + (size_t)q * G.pcells;
+    const double INF_D = __longlong_as_double(0x7ff0000000000000LL);
+    const int BZ = G.ndim == 3 ? XB : 1;
+    int vx = goals[3 * q], vy = goals[3 * q + 1], vz = G.ndim == 3 ? goals[3 * q + 2] : 0;
+    const int sx = starts[3 * q], sy = starts[3 * q + 1], sz = G.ndim == 3 ? starts[3 * q + 2] : 0;
+    const bool ok = vx >= 0 && vy >= 0 && vz >= 0 && vx < G.X && vy < G.Y && vz < G.Z &&
+                    sx >= 0 && sy >= 0 && sz >= 0 && sx < G.X && sy < G.Y && sz < G.Z;
+    if (!ok || gq[((size_t)vz * G.PY + vy) * G.PX + vx] == W::ginf()) {
+        if (tid == 0) { plen[q] = 0; cost[q] = INF_D; }
+        return;
+    }
+    const bool has = lane < M.k;
+    const int dx = has ? M.dx[lane] : 0, dy = has ? M.dy[lane] : 0, dz = has ? M.dz[lane] : 0;
+    const int nax = (dx != 0) + (dy != 0) + (dz != 0);
+    const double mylen = has ? M.len[lane] : 0.0;
+    int64_t n = 0;     // warp 0's copy is the authoritative one
+    double c = 0.0;
+    int32_t result = 0;
+    for (;;) {
+        const int bx = vx - XB / 2, by = vy - XB / 2, bz = G.ndim == 3 ? vz - XB / 2 : 0;
+        for (int i = tid; i < XB * XB * BZ; i += 256) {
+            const int x = bx + (i % XB), y = by + (i / XB) % XB, z = bz + i / (XB * XB);
+            GT w = W::ginf();
+            if ((unsigned)x < (unsigned)G.PX && (unsigned)y < (unsigned)G.PY && (unsigned)z < (unsigned)G.PZ)
+                w = gq[((size_t)z * G.PY + y) * G.PX + x];
+            box[i] = w;
+        }
+        for (int r = tid; r < XB * BZ; r += 256) occ[r] = (u32)row_bits(G, bx, by + r % XB, bz + r / XB, XB);
+        __syncthreads();
+        if (tid < 32) {
+            int finished = 0;
+            for (;;) {
+                const int lx = vx - bx, ly = vy - by, lz = vz - bz;
+                const bool inside = lx >= 1 && lx <= XB - 2 && ly >= 1 && ly <= XB - 2 && (G.ndim == 2 || (lz >= 1 && lz <= XB - 2));
+                if (!inside) break; // re-centre the box (the first cell of a fresh box is always inside)
+                if (lane == 0 && n < cap) path[(size_t)q * cap + n] = (u32)(((size_t)vz * G.PY + vy) * G.PX + vx);
+                ++n;
+                if (vx == sx && vy == sy && vz == sz) { result = n <= cap ? (int32_t)n : -1; finished = 1; break; }
+                GT cand = W::inf();
+                if (has) {
+                    const int ux = lx - dx, uy = ly - dy, uz = lz - dz;
+                    const GT gu = W::dec(box[(uz * XB + uy) * XB + ux]);
+                    int blocked = 0;
+                    if (nax >= 2) {
+                        if (dx) blocked |= (occ[uz * XB + uy] >> (ux + dx)) & 1u;
+                        if (dy) blocked |= (occ[uz * XB + uy + dy] >> ux) & 1u;
+                        if (dz) blocked |= (occ[(uz + dz) * XB + uy] >> ux) & 1u;
+                    }
+                    if (!blocked && gu != W::inf()) cand = W::add(gu, M, lane);
+                }
+                const GT best = warp_min(cand);
+                if (best == W::inf()) { result = 0; c = INF_D; finished = 1; break; }
+                const u32 who = __ballot_sync(0xFFFFFFFFu, cand == best);
+                const int m = __ffs(who) - 1;
+                c += __shfl_sync(0xFFFFFFFFu, mylen, m);
+                vx -= __shfl_sync(0xFFFFFFFFu, dx, m); vy -= __shfl_sync(0xFFFFFFFFu, dy, m); vz -= __shfl_sync(0xFFFFFFFFu, dz, m);
+                if (n > (int64_t)G.pcells) { result = 0; c = INF_D; finished = 1; break; }
+            }
+            if (lane == 0) { st[0] = vx; st[1] = vy; st[2] = vz; st[3] = finished; }
+        }
+        __syncthreads();
+        vx = st[0]; vy = st[1]; vz = st[2];
+        const int fin = st[3];
+        __syncthreads();
+        if (fin) break;
+    }
+    if (tid == 0) { plen[q] = result; cost[q] = c; }
+}
+
 extern "C" int pmp_extract_paths(const pmp_grid *g, int weight, int64_t nq,
                                  const int32_t *starts_dev, const int32_t *goals_dev, const void *g_dev,
                                  uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
@@ -103,6 +191,15 @@ extern "C" int pmp_extract_paths(const pmp_grid *g, int weight, int64_t nq,
     }
     const unsigned blocks = (unsigned)((nq * 32 + 127) / 128);
     cudaStream_t s = (cudaStream_t)stream;
+    if (nq <= 64 && (weight == PMP_W_F64 || weight == PMP_W_U32) && !getenv("PMP_B200_WARP_EXTRACT")) {
+        // few queries: one CTA per query with the field staged in shared memory
+        if (weight == PMP_W_F64)
+            k_extract_paths_box<WF64><<<(unsigned)nq, 256, 0, s>>>(g->d, g->mot, (u32)nq, starts_dev, goals_dev, (const u64 *)g_dev, path_dev, path_cap, path_len_dev, cost_dev);
+        else
+            k_extract_paths_box<WU32><<<(unsigned)nq, 256, 0, s>>>(g->d, g->mot, (u32)nq, starts_dev, goals_dev, (const u32 *)g_dev, path_dev, path_cap, path_len_dev, cost_dev);
+        PMP_CHECK_CUDA(cudaGetLastError());
+        return 0;
+    }
     if (weight == PMP_W_F64)
         k_extract_paths<WF64><<<blocks, 128, 0, s>>>(g->d, g->mot, (u32)nq, starts_dev, goals_dev, (const u64 *)g_dev, path_dev, path_cap, path_len_dev, cost_dev);
     else if (weight == PMP_W_U32)
