@@ -1,3 +1,7 @@
+"""Ring pop latency of k_sssp on c4 (needs a -DPMP_POPSTAT build of the library:
+    make -C python_motion_planning_b200/csrc EXTRA=-DPMP_POPSTAT   (or nvcc ... -DPMP_POPSTAT -o libpmp_b200_pop.so)
+    PMP_B200_BANDS=1 PMP_B200_LIB=.../libpmp_b200_pop.so python tools/popstat.py
+The counters cover the plain FIFO ring only.)"""
 import sys, os
 sys.path.insert(0, "/root/repo")
 import numpy as np, torch
