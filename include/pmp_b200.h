@@ -91,6 +91,11 @@ int pmp_grid_count_free(const pmp_grid *g, int64_t *n_free);
  * planners use the Euclidean length of the offset (a_star3d.py:67) -- the host layer passes the
  * right numbers.  Returns <0 for offsets outside {-1,0,1}. */
 int pmp_grid_set_motions(pmp_grid *g, int k, const int32_t *offsets_host, const double *cost_host);
+/* Edge rule.  allow = 0 (default): a diagonal move also needs the face neighbours of its source free
+ * (GraphSearcher.isCollision, graph_search.py:61-87; GraphSearcher3D.isCollision,
+ * graph_search_3d.py:66-107).  allow = 1: only the target must be free -- the graph the
+ * reference's JPS searches (JPS.jump / detectForceNeighbor, jps.py:85-165, never call isCollision). */
+int pmp_grid_set_corner_cutting(pmp_grid *g, int allow);
 
 /* ---- search: replaces AStar/Dijkstra(.plan) expansion loops
  *      (global_planner/graph_search/a_star.py:39-83, dijkstra.py:36-85, a_star3d.py:33-78,

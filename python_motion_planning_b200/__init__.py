@@ -12,6 +12,7 @@ from .planner import (AStar, AStar3D, Dijkstra, Dijkstra3D, GBFS, GBFS3D, GraphS
                       GraphSearcher3D, Planner, Planner3D, SearchFactory, ExpandView)
 from .batch import plan_batch, plan_batch_sharded, cost_field, shard_range
 from .replan import LPAStar, LPAStar3D, DStar, DStar3D, DStarLite, DynamicField, ReplanSession
+from .jps import JPS, JPS3D
 from .anyangle import ThetaStar, ThetaStar3D, LazyThetaStar, LazyThetaStar3D, line_of_sight
 from ._lib import PmpError
 
@@ -19,4 +20,4 @@ __all__ = ["Env", "Env3D", "Grid", "Grid3D", "Node", "Node3D", "AStar", "AStar3D
            "Dijkstra3D", "GBFS", "GBFS3D", "GraphSearcher", "GraphSearcher3D", "Planner",
            "Planner3D", "SearchFactory", "ExpandView", "plan_batch", "plan_batch_sharded", "shard_range", "cost_field", "PmpError",
            "LPAStar", "LPAStar3D", "DStar", "DStar3D", "DStarLite", "DynamicField", "ReplanSession",
-           "ThetaStar", "ThetaStar3D", "LazyThetaStar", "LazyThetaStar3D", "line_of_sight"]
+           "JPS", "JPS3D", "ThetaStar", "ThetaStar3D", "LazyThetaStar", "LazyThetaStar3D", "line_of_sight"]

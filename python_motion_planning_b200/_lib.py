@@ -22,7 +22,7 @@ SYMBOLS = (
     "pmp_last_error", "pmp_abi_version", "pmp_device_count",
     "pmp_grid_create", "pmp_grid_destroy", "pmp_grid_layout", "pmp_grid_set_cells",
     "pmp_grid_set_dense", "pmp_grid_set_dense_xyz", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
-    "pmp_grid_set_motions", "pmp_sssp_sizes", "pmp_sssp", "pmp_field_finalize",
+    "pmp_grid_set_motions", "pmp_grid_set_corner_cutting", "pmp_sssp_sizes", "pmp_sssp", "pmp_field_finalize",
     "pmp_count_settled", "pmp_extract_paths", "pmp_verify_field", "pmp_gbfs",
     "pmp_slab_begin", "pmp_slab_run", "pmp_slab_merge", "pmp_replan_begin", "pmp_replan_update",
     "pmp_line_of_sight", "pmp_shortcut_paths",
@@ -83,6 +83,7 @@ def lib():
         "pmp_grid_read_bits": [vp, vp, i64],
         "pmp_grid_count_free": [vp, vp],
         "pmp_grid_set_motions": [vp, i32, vp, vp],
+        "pmp_grid_set_corner_cutting": [vp, i32],
         "pmp_sssp_sizes": [vp, i64, i32, vp, vp],
         "pmp_sssp": [vp, ctypes.POINTER(SsspParams), i64, vp, vp, vp, vp, i64, vp, vp, vp, vp],
         "pmp_field_finalize": [vp, i32, i64, vp],

@@ -21,6 +21,7 @@ typedef uint32_t u32;
 // (graph_search_3d.py:66-107).
 struct Motions {
     int k;
+    int cut; // 1: diagonal moves may cut corners (only the target must be free) -- the graph of the reference's JPS (jps.py:85-121)
     int8_t dx[PMP_MAXM], dy[PMP_MAXM], dz[PMP_MAXM];
     u32 need[PMP_MAXM];
     u32 wi[PMP_MAXM];     // integer cost (u32 fields)
@@ -49,6 +50,7 @@ struct pmp_grid {
     double he_scale; // largest a with a*euclid admissible for this motion table
     double hm_scale; // largest a with a*manhattan admissible
     bool integer_costs;
+    int cut; // corner cutting allowed (pmp_grid_set_corner_cutting)
 };
 
 // ---- weight traits: how a cost field element is stored, compared and advanced ----
@@ -139,7 +141,7 @@ __device__ static inline bool edge_legal(const GridDev &G, const Motions &M, int
     const int dx = M.dx[m], dy = M.dy[m], dz = M.dz[m];
     if (cell_blocked(G, ux, uy, uz) || cell_blocked(G, ux + dx, uy + dy, uz + dz)) return false;
     const int nz = (dx != 0) + (dy != 0) + (dz != 0);
-    if (nz >= 2) {
+    if (nz >= 2 && !M.cut) {
         if (dx && cell_blocked(G, ux + dx, uy, uz)) return false;
         if (dy && cell_blocked(G, ux, uy + dy, uz)) return false;
         if (dz && cell_blocked(G, ux, uy, uz + dz)) return false;

@@ -144,6 +144,7 @@ static int install_motions(pmp_grid *g, int k, const int32_t *off, const double 
     Motions M;
     memset(&M, 0, sizeof M);
     M.k = k;
+    M.cut = g->cut;
     double wmin = INFINITY, he = INFINITY, hm = INFINITY;
     bool integer = true;
     for (int m = 0; m < k; ++m) {
@@ -165,7 +166,7 @@ static int install_motions(pmp_grid *g, int k, const int32_t *off, const double 
         M.len[m] = sqrt((double)(dx * dx + dy * dy + dz * dz));
         auto bit = [](int ax, int ay, int az) { return 1u << ((az + 1) * 9 + (ay + 1) * 3 + (ax + 1)); };
         u32 need = bit(dx, dy, dz);
-        if (nz >= 2) { // face neighbours of the source along every moving axis
+        if (nz >= 2 && !g->cut) { // face neighbours of the source along every moving axis
             if (dx) need |= bit(dx, 0, 0);
             if (dy) need |= bit(0, dy, 0);
             if (dz) need |= bit(0, 0, dz);
@@ -255,6 +256,20 @@ extern "C" int pmp_grid_create(int ndim, const int32_t *dims, pmp_grid **out) {
     }
     *out = g;
     return 0;
+}
+
+extern "C" int pmp_grid_set_corner_cutting(pmp_grid *g, int allow) {
+    if (!g) { pmp_set_error("pmp_grid_set_corner_cutting: null"); return -1; }
+    if (g->cut == (allow != 0)) return 0;
+    g->cut = allow != 0;
+    int32_t off[3 * PMP_MAXM];
+    double cost[PMP_MAXM];
+    const int k = g->mot.k;
+    for (int m = 0; m < k; ++m) {
+        off[3 * m] = g->mot.dx[m]; off[3 * m + 1] = g->mot.dy[m]; off[3 * m + 2] = g->mot.dz[m];
+        cost[m] = g->mot.w[m];
+    }
+    return install_motions(g, k, off, cost);
 }
 
 extern "C" int pmp_grid_destroy(pmp_grid *g) {

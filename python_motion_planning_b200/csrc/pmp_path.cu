@@ -64,7 +64,7 @@ __global__ void k_extract_paths(const GridDev G, const __grid_constant__ Motions
             // independent loads: the value of u and the (0, 2 or 3) face cells
             const GT gu = W::dec(gq[((size_t)uz * G.PY + uy) * G.PX + ux]);
             int blocked = 0;
-            if (nax >= 2) {
+            if (nax >= 2 && !M.cut) {
                 if (dx) blocked |= cell_blocked(G, ux + dx, uy, uz);
                 if (dy) blocked |= cell_blocked(G, ux, uy + dy, uz);
                 if (dz) blocked |= cell_blocked(G, ux, uy, uz + dz);
@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(256) k_extract_paths_box(const GridDev G, cons
                     const int ux = lx - dx, uy = ly - dy, uz = lz - dz;
                     const GT gu = W::dec(box[(uz * XB + uy) * XB + ux]);
                     int blocked = 0;
-                    if (nax >= 2) {
+                    if (nax >= 2 && !M.cut) {
                         if (dx) blocked |= (occ[uz * XB + uy] >> (ux + dx)) & 1u;
                         if (dy) blocked |= (occ[uz * XB + uy + dy] >> ux) & 1u;
                         if (dz) blocked |= (occ[(uz + dz) * XB + uy] >> ux) & 1u;

@@ -206,17 +206,21 @@ class DeviceGrid:
                    "pmp_grid_set_dense_xyz")
         self._keep = dev
 
-    def set_motions(self, offsets, costs):
+    def set_motions(self, offsets, costs, cut=False):
+        """motion table + edge rule (cut = True: diagonal moves may cut corners, the JPS graph)"""
         key = (tuple(map(tuple, offsets)), tuple(costs))
-        if key == self._motion_key:
-            return
-        off = np.zeros((len(offsets), 3), dtype=np.int32)
-        for i, o in enumerate(offsets):
-            off[i, :len(o)] = o
-        c = np.ascontiguousarray(costs, dtype=np.float64)
-        _lib.check(self.L.pmp_grid_set_motions(self.handle, len(off), off.ctypes.data, c.ctypes.data),
-                   "pmp_grid_set_motions")
-        self._motion_key = key
+        if key != self._motion_key:
+            off = np.zeros((len(offsets), 3), dtype=np.int32)
+            for i, o in enumerate(offsets):
+                off[i, :len(o)] = o
+            c = np.ascontiguousarray(costs, dtype=np.float64)
+            _lib.check(self.L.pmp_grid_set_motions(self.handle, len(off), off.ctypes.data, c.ctypes.data),
+                       "pmp_grid_set_motions")
+            self._motion_key = key
+        if bool(cut) != getattr(self, "_cut", False):
+            _lib.check(self.L.pmp_grid_set_corner_cutting(self.handle, 1 if cut else 0),
+                       "pmp_grid_set_corner_cutting")
+            self._cut = bool(cut)
 
     def read_bits(self):
         """bool array [x, y(, z)] of the device occupancy (box only)."""

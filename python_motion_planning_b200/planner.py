@@ -170,7 +170,7 @@ class _SearchMixin:
     def _prepare(self):
         dg = self.env.device_grid()
         offsets, costs = motion_table(self.env if self.motions is self.env.motions else self, self._ndim)
-        dg.set_motions(offsets, costs)
+        dg.set_motions(offsets, costs, cut=getattr(self, "_cut", False))
         return dg
 
     def _no_path(self, expand):
@@ -478,6 +478,9 @@ class SearchFactory(object):
         elif planner_name == "lpa_star":
             from .replan import LPAStar
             return LPAStar(**config)
+        elif planner_name == "jps":
+            from .jps import JPS
+            return JPS(**config)
         elif planner_name == "d_star":
             from .replan import DStar
             return DStar(**config)
