@@ -34,11 +34,13 @@ import python_motion_planning_b200 as pmp  # noqa: E402
 
 algorithms = {                     # examples/algorithms.py, the entries this package implements
     "astar": pmp.AStar3D,
+    "dstar": pmp.DStar3D,
     "dijkstra": pmp.Dijkstra3D,
     "gbfs": pmp.GBFS3D,
     "lazy_theta_star": pmp.LazyThetaStar3D,
     "theta_star": pmp.ThetaStar3D,
     "lpastar": pmp.LPAStar3D,
+    "jps": pmp.JPS3D,
 }
 
 
@@ -80,7 +82,7 @@ def main():
     ap.add_argument("--out", default="3d_pathfinding_results.csv")
     ap.add_argument("--repeats", type=int, default=10, help="rows per (scenario, algorithm, seed); the reference writes 10")
     ap.add_argument("--iterations", type=int, default=100)
-    ap.add_argument("--algorithms", default="astar,dijkstra,gbfs,lazy_theta_star,theta_star,lpastar")
+    ap.add_argument("--algorithms", default="astar,dstar,dijkstra,gbfs,lazy_theta_star,theta_star,lpastar")
     ap.add_argument("--scenarios-module", default=None)
     args = ap.parse_args()
     names = [a for a in args.algorithms.split(",") if a]

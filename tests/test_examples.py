@@ -23,7 +23,7 @@ def test_benchmark_writer_schema_and_known_answers(tmp_path):
     rows = list(csv.reader(open(out)))
     assert rows[0] == HEADER
     body = [dict(zip(HEADER, r)) for r in rows[1:]]
-    assert len(body) == 5 * 6 * 4 * 2
+    assert len(body) == 5 * 7 * 4 * 2
     z = gio.load("csv_replay.npz")
     lz = gio.load("los.npz")
     names = [str(s) for s in z["scen_names"]]
@@ -38,7 +38,7 @@ def test_benchmark_writer_schema_and_known_answers(tmp_path):
             assert abs(d - float(z[f"{a}_csv_dist"][k])) <= 1e-9 * max(d, 1.0)
         if a == "gbfs":
             assert int(r["Visited Nodes"]) == int(z["gbfs_csv_vis"][k])
-        if a == "lpastar":                              # the reference's greedy extraction is never shorter
+        if a in ("lpastar", "dstar"):                              # the reference's greedy extraction is never shorter
             assert abs(d - float(z["dijkstra_csv_dist"][k])) <= 1e-9 * max(d, 1.0)
         if a in ("theta_star", "lazy_theta_star"):
             assert d <= float(z["astar_csv_dist"][k]) * (1 + 1e-9)
