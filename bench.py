@@ -143,6 +143,18 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # workloads
 # ------------------------------------------------------------------------------------------------
+KERNEL_EVENTS = []   # (start, stop) CUDA events around the search phase of every step
+
+
+def timed_search(torch, fn):
+    """run fn (the pmp_sssp call of a step) between two CUDA events on the launching stream"""
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    fn()
+    e1.record()
+    KERNEL_EVENTS.append((e0, e1))
+
+
 def build_workload(args, rank, torch, pmp, workloads):
     """returns dict(env, run(step) -> (edges, settled, algorithmic bytes), e2e(step), meta)"""
     from python_motion_planning_b200 import engine, _lib
@@ -174,7 +186,7 @@ def build_workload(args, rank, torch, pmp, workloads):
 
         def run(step):
             engine.upload_queries(ws, [start], [goal], 3)
-            engine.sssp(ws, _lib.ASTAR, 0)
+            timed_search(torch, lambda: engine.sssp(ws, _lib.ASTAR, 0))
             engine.extract_paths(ws, path_cap)
             return 4   # my kernel launches: init, k_sssp, finish, extract
 
@@ -216,7 +228,7 @@ def build_workload(args, rank, torch, pmp, workloads):
 
         def run(step):
             engine.upload_queries(ws, starts, goals, 2)
-            engine.sssp(ws, _lib.DIJKSTRA, 0)
+            timed_search(torch, lambda: engine.sssp(ws, _lib.DIJKSTRA, 0))
             engine.extract_paths(ws, path_cap)
             return 4
 
@@ -273,7 +285,7 @@ def build_workload(args, rank, torch, pmp, workloads):
 
         def run(step):
             engine.upload_queries(ws, [src], None, 3)
-            engine.sssp(ws, _lib.DIJKSTRA, 0, full_field=True, have_goals=False)
+            timed_search(torch, lambda: engine.sssp(ws, _lib.DIJKSTRA, 0, full_field=True, have_goals=False))
             return 3
 
         def account():
@@ -440,6 +452,9 @@ def main():
     clocks = sampler.stop()
     ms = [a.elapsed_time(b) for a, b in evs]
     t_dev = sum(ms) / 1e3
+    # the dominant kernel alone: events around the search phase of the timed steps
+    kms = [a.elapsed_time(b) for a, b in KERNEL_EVENTS[-args.steps:]] if len(KERNEL_EVENTS) >= args.steps else []
+    t_kernel = (sum(kms) / len(kms) / 1e3) if kms else t_dev / args.steps
     # ---- end-to-end leg through the public API with host buffers ----
     for i in range(2):
         W["e2e"](i)
@@ -467,7 +482,7 @@ def main():
     st = [int(v) for v in W["stats"]().tolist()] if "stats" in W else None
     peak, peak_src = measured_peak()
     value = edges_all * args.steps / t_dev_max / 1e9
-    achieved = abytes / (t_dev / args.steps) / 1e9          # this rank's dominant kernel (k_sssp)
+    achieved = abytes / t_kernel / 1e9                      # this rank's dominant kernel (k_sssp)
     line = {
         "metric": "edge relaxations/s", "value": value, "unit": "GTEPS", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_dev_max / args.steps * 1e3,
@@ -485,7 +500,9 @@ def main():
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                     "kernel": "k_sssp (+init/finish/extract, ~1% of the step)",
+                     "kernel": "k_sssp, timed per step with CUDA events around the search phase on its stream "
+                               "(field fill + k_sssp_init + k_sssp + k_sssp_finish; k_sssp is > 95 % of it)",
+                     "kernel_ms": t_kernel * 1e3,
                      "algorithmic_bytes_per_step": abytes},
     }
     if "phases" in W:
