@@ -131,7 +131,10 @@ __global__ void __launch_bounds__(256) k_extract_paths_box(const GridDev G, cons
     double c = 0.0;
     int32_t result = 0;
     for (;;) {
-        const int bx = vx - XB / 2, by = vy - XB / 2, bz = G.ndim == 3 ? vz - XB / 2 : 0;
+        // the walk heads for the start: put the current cell near the far side of the box
+        const int bx = vx - (sx < vx ? XB - 4 : (sx > vx ? 3 : XB / 2));
+        const int by = vy - (sy < vy ? XB - 4 : (sy > vy ? 3 : XB / 2));
+        const int bz = G.ndim == 3 ? vz - (sz < vz ? XB - 4 : (sz > vz ? 3 : XB / 2)) : 0;
         for (int i = tid; i < XB * XB * BZ; i += 256) {
             const int x = bx + (i % XB), y = by + (i / XB) % XB, z = bz + i / (XB * XB);
             GT w = W::ginf();
