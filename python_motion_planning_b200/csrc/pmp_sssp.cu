@@ -5,22 +5,26 @@
 // getNeighbor (a_star.py:85-96, a_star3d.py:80-89, dijkstra3d.py:89-126) and isCollision
 // (graph_search.py:61-87, graph_search_3d.py:66-107).
 //
-// Scheme (DESIGN.md has the long form):
+// Scheme (DESIGN.md section 3.1 has the long form):
 //   * the grid is cut into tiles (32x32 cells in 2D, 16x8x8 in 3D); a cost field g is a dense
-//     array per query; per (query, tile) there is a `minkey` (smallest key of a cell that still
-//     has to propagate) and a 1024-bit `dirty` mask of those cells;
-//   * one persistent cooperative kernel runs rounds: SCAN every (query, tile), collect those
-//     whose minkey lies inside the query's key window [min, min + delta) into a worklist;
-//     PROCESS each listed tile in one CTA: stage g (tile + 1-cell halo) and the occupancy rows in
-//     shared memory, settle cells in key order with sub-buckets of the smallest edge cost
-//     (ballot-compacted frontier, shared-memory atomic min), then publish: changed cells go
-//     back with an atomic min, improved halo cells additionally raise the neighbour tile's
-//     dirty bit and minkey.  Global g only ever decreases, every value is fl(g(u) + w) for a
-//     legal edge, and a cell stays dirty until it has propagated, so the fixed point is the
-//     same field a sequential Dijkstra produces -- bit for bit, also for the sqrt(2)/sqrt(3)
-//     weights.
+//     array per query whose words carry the value and a "still has to propagate" flag
+//     ((value << 1) | clean); per (query, tile) there is a `minkey`, the smallest key pushed into
+//     the tile since it was last claimed;
+//   * one persistent cooperative kernel (k_sssp) runs rounds: SCAN every (query, tile) and queue
+//     those whose minkey lies inside the query's key window; then an asynchronous cascade: CTAs
+//     pop tiles from a ring, process_tile stages g (tile + 1-cell halo) and the occupancy rows in
+//     shared memory, settles cells in key order (owner threads keep the per-cell state in
+//     registers, frontier records are expanded with one lane per direction; unit-weight grids
+//     use the bit-parallel level sweep solve_bfs), publishes with atomic min and queues the
+//     neighbour tiles it lowered -- no grid barrier inside a round.  Single A-star queries use
+//     the banded ring (ring_push / banded_pop): the window is cut into key bands served lowest
+//     first.  Global g only ever decreases, every value is fl(g(u) + w) for a legal edge, and a
+//     cell keeps its flag until it has propagated, so the fixed point is the same field a
+//     sequential Dijkstra produces -- bit for bit, also for the sqrt(2)/sqrt(3) weights;
 //   * A-star = the same with key g + h (h an admissible round-down heuristic), pruning by the best
-//     g[goal] seen, and termination once no pending key is below g[goal].
+//     g[goal] seen, and termination once no pending key is below g[goal];
+//   * slab mode (pmp_slab_*: one z-slab per GPU, planes exchanged by the host) and incremental
+//     replanning (pmp_replan.cuh) resume the same kernel from a stored field.
 #include <cooperative_groups.h>
 #include <stdlib.h>
 #include <string.h>
