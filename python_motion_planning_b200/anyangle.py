@@ -81,7 +81,7 @@ class _AnyAngleMixin:
         expand = self._expand_view(ws, gcost if np.isfinite(gcost) else None)
         if status == _lib.ST_BAD_QUERY or plen <= 0:
             return self._no_path(expand)
-        pts = [tuple(int(v) for v in p) for p in engine.cells_to_coords(wp[0, :plen].cpu().numpy(), dg)]
+        pts = engine.cells_to_points(wp[0, :plen].cpu().numpy(), dg)
         if self._ndim == 3:
             pts.reverse()
         return cost, pts, expand

@@ -34,6 +34,9 @@ class Workspace:
         self.path_cap = 0
         self.path_len = t.empty(nq, dtype=t.int32, device=dg.device)
         self.cost = t.empty(nq, dtype=t.float64, device=dg.device)
+        # pinned landing buffers of the single-query result: scalars and the head of the path in one sync
+        self.host_res = t.empty(4, dtype=t.float64).pin_memory()
+        self.host_path = t.empty(16384, dtype=t.int32).pin_memory()
 
     def ensure_path(self, cap):
         if self.path is None or self.path_cap < cap:
@@ -140,6 +143,11 @@ def cells_to_coords(cells, dg):
     if dg.ndim == 2:
         return np.stack([x, y], axis=1)
     return np.stack([x, y, c // (PX * PY)], axis=1)
+
+
+def cells_to_points(cells, dg):
+    """padded cell indices -> list of coordinate tuples of Python ints (the reference's path form)"""
+    return list(map(tuple, cells_to_coords(cells, dg).tolist()))
 
 
 def field_to_numpy(ws, q=0, raw=None):

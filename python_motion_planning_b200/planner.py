@@ -110,8 +110,21 @@ class _SearchMixin:
     def _init_search(self, heuristic_type):
         self.heuristic_type = heuristic_type
         self.motions = self.env.motions        # alias, as graph_search.py:26
-        self.stats = None                      # filled by plan(): rounds, tiles, cells, edges
+        self._stats = None                     # device counters of the last plan(): rounds, tiles, cells, edges
+        self._stats_dev = None
         self.last_field = None                 # (Workspace) device cost field of the last plan()
+
+    @property
+    def stats(self):
+        """counters of the last plan() (rounds, tile activations, cells, edges, ...), fetched on demand"""
+        if self._stats is None and self._stats_dev is not None:
+            self._stats = self._stats_dev.cpu().numpy().copy()
+        return self._stats
+
+    @stats.setter
+    def stats(self, value):
+        self._stats = value
+        self._stats_dev = None
 
     @property
     def obstacles(self):
@@ -185,10 +198,17 @@ class _SearchMixin:
         engine.upload_queries(ws, [self.start.current], [self.goal.current], self._ndim)
         engine.sssp(ws, self._algo, self._heuristic_id())
         engine.extract_paths(ws, self._path_cap(dg))
-        res = t.stack([ws.gcost[0], ws.cost[0], ws.path_len[0].to(t.float64),
-                       ws.status[0].to(t.float64)]).cpu()       # one D2H of the scalars
-        self.stats = ws.stats.cpu().numpy().copy()
+        # one synchronisation for everything plan() returns: the scalars and the head of the path
+        # land in pinned host buffers, the counters are cloned on the device and read on demand
+        ws.host_res.copy_(t.stack([ws.gcost[0], ws.cost[0], ws.path_len[0].to(t.float64),
+                                   ws.status[0].to(t.float64)]), non_blocking=True)
+        nhead = min(ws.path_cap, ws.host_path.numel())
+        ws.host_path[:nhead].copy_(ws.path[0, :nhead], non_blocking=True)
+        self._stats_dev = ws.stats.clone()
+        self._stats = None
+        t.cuda.current_stream().synchronize()
         self.last_field = ws
+        res = ws.host_res
         gcost, cost, plen, status = float(res[0]), float(res[1]), int(res[2]), int(res[3])
         if status == _lib.ST_BAD_QUERY:
             return self._no_path(self._expand_view(ws, None))
@@ -196,11 +216,12 @@ class _SearchMixin:
             engine.extract_paths(ws, dg.pcells)
             plen = int(ws.path_len[0].item())
             cost = float(ws.cost[0].item())
+            nhead = 0
         expand = self._expand_view(ws, gcost if math.isfinite(gcost) else None)
         if plen <= 0:
             return self._no_path(expand)
-        cells = ws.path[0, :plen].cpu().numpy()
-        pts = [tuple(int(v) for v in p) for p in engine.cells_to_coords(cells, dg)]
+        cells = ws.host_path[:plen].numpy().copy() if plen <= nhead else ws.path[0, :plen].cpu().numpy()
+        pts = engine.cells_to_points(cells, dg)
         if self._ndim == 3:
             pts.reverse()                      # a_star3d.py:105: start -> goal
         return cost, pts, expand
@@ -459,7 +480,7 @@ def _plan_gbfs(planner):
     expand = ExpandView(planner._node_cls, coords, np.zeros(len(coords)), h, parents)
     if plen == 0:
         return planner._no_path(expand)
-    pts = [tuple(int(v) for v in p) for p in engine.cells_to_coords(ws.path[0, :plen].cpu().numpy(), dg)]
+    pts = engine.cells_to_points(ws.path[0, :plen].cpu().numpy(), dg)
     if ndim == 3:
         pts.reverse()
     return cost, pts, expand

@@ -181,7 +181,7 @@ class _ReplanMixin:
         if status == _lib.ST_BAD_QUERY or plen <= 0:
             return float("inf"), [], expand
         cells = ws.path[0, :plen].cpu().numpy()
-        pts = [tuple(int(v) for v in p) for p in engine.cells_to_coords(cells, dg)]
+        pts = engine.cells_to_points(cells, dg)
         pts.reverse()                                      # start -> goal (lpa_star.py:229, lpa_star3d.py:224)
         return cost, pts, expand
 
