@@ -10,8 +10,9 @@ with the iteration index and draws start / goal (benchmark.py:46-75).  Those 500
 (5 scenarios x 100 seeds: occupancy after carve_safety_bubble, start, goal) are committed in
 tests/golden/csv_replay.npz, written from the unmodified reference by tools/make_golden.py, so this
 script replays exactly the instances behind the reference's 3d_pathfinding_results.csv and its
-output can be compared with that file row by row (Distance for astar / dijkstra, Distance and
-Visited Nodes for gbfs are equal; see tests/test_gpu_parity.py::test_csv_replay_known_answers).
+output can be compared with that file row by row: with --order reference (default) Distance and
+Visited Nodes of the astar / dijkstra / gbfs / theta_star / lazy_theta_star rows are equal
+(tests/test_examples.py); with --order wavefront Distance of astar / dijkstra.
 With --scenarios-module the maps are generated live instead, from a module that offers the
 reference's interface (`scenarios` dict of env -> obstacle set, `carve_safety_bubble`).
 
@@ -84,6 +85,9 @@ def main():
     ap.add_argument("--iterations", type=int, default=100)
     ap.add_argument("--algorithms", default="astar,dstar,dijkstra,gbfs,lazy_theta_star,theta_star,lpastar")
     ap.add_argument("--scenarios-module", default=None)
+    ap.add_argument("--order", choices=("reference", "wavefront"), default="reference",
+                    help="reference: plan() in the reference's pop order (pmp_bestfirst), so Distance AND Visited "
+                         "Nodes equal the reference's rows; wavefront: the tiled relaxation kernels (equal Distance)")
     args = ap.parse_args()
     names = [a for a in args.algorithms.split(",") if a]
     inst = list(live_instances(args.scenarios_module, args.iterations) if args.scenarios_module
@@ -102,6 +106,10 @@ def main():
                         env = pmp.Grid3D(*occ.shape, walls=False)
                         env.update(set(map(tuple, np.argwhere(occ).tolist())))
                         planner = cls(start=start, goal=goal, env=env)
+                        if args.order == "reference":
+                            planner.reference_order = True         # astar / dijkstra / gbfs
+                        elif hasattr(planner, "mode"):
+                            planner.mode = "shortcut"              # theta_star / lazy_theta_star
                         t0 = time.time()
                         cost, path, expand = planner.plan()
                         t1 = time.time()

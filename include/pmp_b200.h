@@ -38,7 +38,10 @@ extern "C" {
 
 typedef struct pmp_grid pmp_grid; /* opaque: occupancy bitmask + motion table on one device */
 
-enum pmp_algo { PMP_ASTAR = 0, PMP_DIJKSTRA = 1, PMP_GBFS = 2 };
+enum pmp_algo {
+    PMP_ASTAR = 0, PMP_DIJKSTRA = 1, PMP_GBFS = 2,
+    PMP_THETA_STAR = 3, PMP_LAZY_THETA_STAR = 4 /* pmp_bestfirst only */
+};
 enum pmp_heuristic { PMP_H_EUCLIDEAN = 0, PMP_H_MANHATTAN = 1 };
 enum pmp_weight { PMP_W_F64 = 0, PMP_W_U32 = 1 };
 
@@ -177,6 +180,29 @@ int pmp_gbfs(const pmp_grid *g, int heuristic, int64_t nq,
              uint32_t *parent_dev, void *heap_dev, int64_t heap_cap,
              uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
              double *cost_dev, int32_t *n_expand_dev, void *stream);
+
+/* ---- reference-order search: AStar / Dijkstra / GBFS / ThetaStar / LazyThetaStar .plan() and their
+ *      3D classes run with the reference's own heap discipline (a_star.py:39-117, dijkstra.py:36-85,
+ *      gbfs.py:36-86, theta_star.py:44-108, lazy_theta_star.py:44-118, a_star3d.py:33-106,
+ *      dijkstra3d.py:39-143, gbfs3d.py:34-110, theta_star3d.py:38-107,
+ *      lazy_theta_star3d.py:41-133): CPython heapq sift order, Node.__lt__ (2D handles) or
+ *      (f, h, counter) tuples (3D handles), dict-ordered CLOSED, parent-pointer extractPath.
+ *      Unlike pmp_sssp + pmp_extract_paths, which guarantee the cost only, this reproduces the
+ *      returned path among equal-cost ones, len(expand) ("Visited Nodes", examples/benchmark.py:85)
+ *      and every expand record.  One warp per query; meant for the reference's own grid sizes.
+ *   heap_dev          : nq x heap_cap records of PMP_BESTFIRST_HEAP_REC_BYTES (OPEN)
+ *   closed_g/h_dev    : nq x padded cells doubles, closed_parent_dev: nq x padded cells uint32
+ *                       (CLOSED[cell].g / .h / .parent as padded cell index; 0xFFFFFFFF = not closed)
+ *   order_dev         : nq x order_cap uint32, the keys of CLOSED in insertion order = `expand`
+ *   path_dev, path_len_dev, cost_dev as pmp_extract_paths (goal first; -2 = heap or order
+ *   capacity exceeded); n_expand_dev = len(CLOSED). */
+#define PMP_BESTFIRST_HEAP_REC_BYTES 40
+int pmp_bestfirst(const pmp_grid *g, int algo, int heuristic, int64_t nq,
+                  const int32_t *starts_dev, const int32_t *goals_dev,
+                  void *heap_dev, int64_t heap_cap, double *closed_g_dev, double *closed_h_dev,
+                  uint32_t *closed_parent_dev, uint32_t *order_dev, int64_t order_cap,
+                  uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev, double *cost_dev,
+                  int32_t *n_expand_dev, void *stream);
 
 /* ---- slab mode: one z-slab (plus one ghost plane per interior side) of a large 3D grid per
  *      GPU; the cost-to-go field of BASELINE.json config 5.  The handle describes the LOCAL slab.

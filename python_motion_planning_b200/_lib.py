@@ -13,6 +13,8 @@ LIB_PATH = os.environ.get("PMP_B200_LIB") or os.path.join(_HERE, "libpmp_b200.so
 CSRC = os.path.join(_HERE, "csrc")
 
 ASTAR, DIJKSTRA, GBFS = 0, 1, 2
+THETA_STAR, LAZY_THETA_STAR = 3, 4          # pmp_bestfirst only
+BESTFIRST_HEAP_REC_BYTES = 40
 H_EUCLIDEAN, H_MANHATTAN = 0, 1
 W_F64, W_U32 = 0, 1
 ST_RUNNING, ST_EXHAUSTED, ST_REACHED, ST_BAD_QUERY, ST_REPLAN_OVERFLOW = 0, 1, 2, 3, 4
@@ -23,7 +25,7 @@ SYMBOLS = (
     "pmp_grid_create", "pmp_grid_destroy", "pmp_grid_layout", "pmp_grid_set_cells",
     "pmp_grid_set_dense", "pmp_grid_set_dense_xyz", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
     "pmp_grid_set_motions", "pmp_grid_set_corner_cutting", "pmp_sssp_sizes", "pmp_sssp", "pmp_field_finalize",
-    "pmp_count_settled", "pmp_extract_paths", "pmp_verify_field", "pmp_gbfs",
+    "pmp_count_settled", "pmp_extract_paths", "pmp_verify_field", "pmp_gbfs", "pmp_bestfirst",
     "pmp_slab_begin", "pmp_slab_run", "pmp_slab_merge", "pmp_replan_begin", "pmp_replan_update",
     "pmp_line_of_sight", "pmp_shortcut_paths",
 )
@@ -41,7 +43,7 @@ class SsspParams(ctypes.Structure):
 
 def build(force=False, verbose=False):
     """Compile csrc/*.cu for sm_100a into libpmp_b200.so (nvcc cross-compiles without a GPU)."""
-    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))]
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
     srcs.append(os.path.join(_HERE, "..", "include", "pmp_b200.h"))
     if (not force and os.path.exists(LIB_PATH)
             and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs)):
@@ -91,6 +93,7 @@ def lib():
         "pmp_extract_paths": [vp, i32, i64, vp, vp, vp, vp, i64, vp, vp, vp],
         "pmp_verify_field": [vp, i32, vp, vp, i32, i32, vp, vp],
         "pmp_gbfs": [vp, i32, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp, vp],
+        "pmp_bestfirst": [vp, i32, i32, i64, vp, vp, vp, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp, vp],
         "pmp_slab_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, i64, vp],
         "pmp_slab_run": [vp, ctypes.POINTER(SsspParams), vp, vp, i64, dbl, vp, vp],
         "pmp_slab_merge": [vp, i32, vp, vp, i64, i32, i32, vp, vp, vp],

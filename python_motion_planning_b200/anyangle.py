@@ -1,25 +1,31 @@
-"""Any-angle planning on top of the grid search.
+"""Any-angle planning.
 
 The reference's Theta* family (global_planner/graph_search/theta_star.py:14-171,
-lazy_theta_star.py:12-114, theta_star3d.py:24-232, lazy_theta_star3d.py:24-252) is A* whose
-updateVertex tries to connect a node to its grandparent when `lineOfSight` allows it.  Here
-the two halves are separate device steps: the A* field + path extraction of the main path,
-then `pmp_shortcut_paths`, which walks the extracted path and keeps a waypoint only where the
-line of sight from the previous kept waypoint ends -- the same lineOfSight predicate
-(`pmp_line_of_sight`, bit-exact against the reference's on committed vectors), applied after the
-search instead of inside it.
+lazy_theta_star.py:12-118, theta_star3d.py:24-232, lazy_theta_star3d.py:24-252) is A* whose
+updateVertex tries to connect a node to the parent of the node being expanded when `lineOfSight`
+allows it (Lazy Theta*: assumes it does and repairs the parent when the node is popped).  Two modes:
 
-Result contract: a collision-free any-angle path (every segment passes the reference's own
-lineOfSight) with cost <= the grid A* cost.  It is not the reference's Theta* path: Theta*
-shortcuts during the search and can leave the grid-optimal corridor, so its cost can be lower
-(tests/test_anyangle.py compares with the Theta* column of the reference's CSV) -- documented
-divergence of this row.
+* `mode="reference"` -- Theta* / Lazy Theta* proper, in the reference's own pop order
+  (`pmp_bestfirst`, csrc/pmp_bestfirst.cu: one warp per query, the line-of-sight tests of a node's
+  neighbours run in parallel lanes).  cost, path, len(expand) and every expand record equal the
+  reference's, including the Distance / Visited Nodes columns of the theta_star and
+  lazy_theta_star rows of its 3d_pathfinding_results.csv.  Default for grids up to 2 Mi padded
+  cells (the reference's own sizes and well beyond).
+* `mode="shortcut"` -- for large maps: the tiled wavefront A* (`pmp_sssp`) + path extraction, then
+  `pmp_shortcut_paths` walks the extracted path and keeps a waypoint only where the line of sight
+  from the previous kept waypoint ends -- the same lineOfSight predicate (`pmp_line_of_sight`,
+  bit-exact against the reference's on committed vectors), applied after the search instead of
+  inside it.  Result: a collision-free any-angle path with cost <= the grid A* cost; not the
+  reference's Theta* path (Theta* may leave the grid-optimal corridor), documented divergence of
+  this mode.  Default above 2 Mi cells.
 """
 import numpy as np
 
 from . import _lib, engine
 from .environment import Node, Node3D
-from .planner import GraphSearcher, GraphSearcher3D
+from .planner import GraphSearcher, GraphSearcher3D, _plan_bestfirst
+
+REFERENCE_MODE_MAX_CELLS = 1 << 21
 
 
 def line_of_sight(env, a, b):
@@ -57,6 +63,11 @@ def shortcut(ws):
 
 class _AnyAngleMixin:
     _algo = _lib.ASTAR
+    _bf_algo = _lib.THETA_STAR
+
+    def __init__(self, start, goal, env, heuristic_type: str = "euclidean", *, mode: str = None) -> None:
+        super().__init__(start, goal, env, heuristic_type)
+        self.mode = mode   # "reference" | "shortcut" | None: by grid size (REFERENCE_MODE_MAX_CELLS)
 
     def lineOfSight(self, node1, node2) -> bool:
         """theta_star.py:110-171 / theta_star3d.py:139-215 (evaluated on the device bitmask)"""
@@ -65,6 +76,12 @@ class _AnyAngleMixin:
     def plan(self) -> tuple:
         """(cost, path, expand): path in the family's order (2D goal -> start, 3D start -> goal)"""
         dg = self._prepare()
+        mode = self.mode or ("reference" if dg.pcells <= REFERENCE_MODE_MAX_CELLS else "shortcut")
+        if mode == "reference":
+            self.grid_cost = None
+            return _plan_bestfirst(self, self._bf_algo)
+        if mode != "shortcut":
+            raise ValueError("mode must be 'reference', 'shortcut' or None")
         t = dg.torch
         ws = engine.get_workspace(dg, 1, _lib.W_F64)
         engine.upload_queries(ws, [self.start.current], [self.goal.current], self._ndim)
@@ -100,7 +117,8 @@ class ThetaStar(_AnyAngleMixin, GraphSearcher):
 
 
 class LazyThetaStar(ThetaStar):
-    """lazy_theta_star.py:12-114"""
+    """lazy_theta_star.py:12-118"""
+    _bf_algo = _lib.LAZY_THETA_STAR
 
     def __str__(self) -> str:
         return "Lazy Theta*"
@@ -120,6 +138,7 @@ class ThetaStar3D(_AnyAngleMixin, GraphSearcher3D):
 
 class LazyThetaStar3D(ThetaStar3D):
     """lazy_theta_star3d.py:24-252"""
+    _bf_algo = _lib.LAZY_THETA_STAR
 
     def __str__(self) -> str:
         return "Lazy Theta* 3D"

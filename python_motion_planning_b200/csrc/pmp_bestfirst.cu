@@ -1,0 +1,155 @@
+// pmp_bestfirst.cu -- the reference's best-first planners in the reference's own pop order.
+//
+// pmp_sssp (pmp_sssp.cu) settles the same costs as the reference with a tiled wavefront, but which
+// of several equal-cost paths comes back, and the content and order of `expand`, follow from the
+// reference's heap discipline.  pmp_bestfirst runs that discipline as written --
+// AStar / Dijkstra / GBFS / ThetaStar / LazyThetaStar .plan() and their 3D classes
+// (global_planner/graph_search/a_star.py:39-117, dijkstra.py:36-85, gbfs.py:36-86,
+// theta_star.py:44-108, lazy_theta_star.py:44-118, a_star3d.py:33-106, dijkstra3d.py:39-143,
+// gbfs3d.py:34-110, theta_star3d.py:38-107, lazy_theta_star3d.py:41-133) -- so cost, path,
+// len(expand) and every expand record equal the reference's.  One warp per query: lane 0 owns the
+// OPEN heap and the CLOSED table (pmp_bestfirst_core.h), the lanes evaluate the motions of the
+// popped node in parallel (edge legality, CLOSED dominance, heuristic, Theta* line of sight) and
+// lane 0 pushes the survivors in motion order.  Independent queries run in parallel warps.
+#include "pmp_common.cuh"
+#include "pmp_los.cuh"
+#include "pmp_bestfirst_core.h"
+
+struct BfEnvDev {
+    const GridDev &G;
+    const Motions &M;
+    __device__ bool legal(int m, int x, int y, int z) const { return edge_legal(G, M, m, x, y, z); }
+    __device__ bool los(int ax, int ay, int az, int bx, int by, int bz) const {
+        return ::los(G, ax, ay, az, bx, by, bz);
+    }
+    __device__ int k() const { return M.k; }
+    __device__ void offset(int m, int &dx, int &dy, int &dz) const { dx = M.dx[m]; dy = M.dy[m]; dz = M.dz[m]; }
+    __device__ double len(int m) const { return M.len[m]; }
+};
+
+template <int FAMILY>
+__global__ void k_bestfirst(const GridDev G, const __grid_constant__ Motions M, int algo, int heuristic,
+                            u32 nq, const int32_t *starts, const int32_t *goals, BfRec *heap_all,
+                            int64_t heap_cap, double *cg_all, double *ch_all, u32 *cpar_all,
+                            u32 *order_all, int64_t order_cap, u32 *path, int64_t cap, int32_t *plen,
+                            double *cost, int32_t *n_expand) {
+    const u32 q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    const unsigned FULL = 0xFFFFFFFFu;
+    const double INF_D = __longlong_as_double(0x7ff0000000000000LL);
+    const int sx = starts[3 * q], sy = starts[3 * q + 1], sz = G.ndim == 3 ? starts[3 * q + 2] : 0;
+    const int gx = goals[3 * q], gy = goals[3 * q + 1], gz = G.ndim == 3 ? goals[3 * q + 2] : 0;
+    const bool ok = gx >= 0 && gy >= 0 && gz >= 0 && gx < G.X && gy < G.Y && gz < G.Z &&
+                    sx >= 0 && sy >= 0 && sz >= 0 && sx < G.X && sy < G.Y && sz < G.Z;
+    if (!ok) { // outside the box; a blocked start or goal is searched as the reference does (CLOSED = {start} / exhaustion)
+        if (lane == 0) { plen[q] = 0; cost[q] = INF_D; n_expand[q] = 0; }
+        return;
+    }
+    // every lane holds the constant part of the state; hn / counter / n_order / status are
+    // lane 0's, the others only read CLOSED (global memory, ordered by __syncwarp)
+    BfState S;
+    S.heap = heap_all + (size_t)q * heap_cap;
+    S.heap_cap = heap_cap;
+    S.cg = cg_all + (size_t)q * G.pcells;
+    S.ch = ch_all + (size_t)q * G.pcells;
+    S.cpar = cpar_all + (size_t)q * G.pcells;
+    S.order = order_all + (size_t)q * order_cap;
+    S.order_cap = order_cap;
+    S.algo = algo;
+    S.heuristic = heuristic;
+    S.PX = G.PX;
+    S.PY = G.PY;
+    S.gx = gx; S.gy = gy; S.gz = gz;
+    S.start_cell = bf_cell(S, sx, sy, sz);
+    S.goal_cell = bf_cell(S, gx, gy, gz);
+    S.hn = 0; S.counter = 0; S.n_order = 0; S.status = BF_RUNNING;
+    const BfEnvDev env = {G, M};
+    if (lane == 0) bf_start<FAMILY>(S, sx, sy, sz);
+    const double myw = lane < M.k ? (FAMILY == 2 ? M.w[lane] : M.len[lane]) : 0.0;
+
+    for (;;) {
+        BfRec node;
+        node.f = node.h = node.g = 0.0;
+        node.cell = node.parent = node.counter = node.pad = 0;
+        int action = BF_DONE;
+        if (lane == 0) action = bf_pop<FAMILY>(S, env, node);
+        action = __shfl_sync(FULL, action, 0);
+        if (action == BF_DONE) break;
+        if (action == BF_SKIP) continue;
+        node.g = __shfl_sync(FULL, node.g, 0);
+        node.h = __shfl_sync(FULL, node.h, 0);
+        node.cell = __shfl_sync(FULL, node.cell, 0);
+        node.parent = __shfl_sync(FULL, node.parent, 0);
+        __syncwarp(); // lane 0's CLOSED writes are visible to the evaluating lanes
+        BfRec cand;
+        cand.f = cand.h = cand.g = 0.0;
+        cand.cell = cand.parent = cand.counter = cand.pad = 0;
+        const bool push = lane < M.k && bf_eval<FAMILY>(S, env, node, lane, myw, cand);
+        const u32 mask = __ballot_sync(FULL, push);
+        int stop = 0;
+        for (int m = 0; m < M.k && !stop; ++m) { // lane 0 pushes in motion order
+            if (!((mask >> m) & 1u)) continue;
+            BfRec r;
+            r.f = __shfl_sync(FULL, cand.f, m);
+            r.h = __shfl_sync(FULL, cand.h, m);
+            r.g = __shfl_sync(FULL, cand.g, m);
+            r.cell = __shfl_sync(FULL, cand.cell, m);
+            r.parent = __shfl_sync(FULL, cand.parent, m);
+            r.counter = 0; r.pad = 0;
+            if (lane == 0) stop = bf_push<FAMILY>(S, r) ? 1 : 0;
+            stop = __shfl_sync(FULL, stop, 0);
+        }
+        if (lane == 0 && FAMILY == 2) bf_close(S, node); // a_star.py:82
+        const int st = __shfl_sync(FULL, S.status, 0);
+        if (st != BF_RUNNING) break;
+        __syncwarp();
+    }
+    if (lane != 0) return;
+    n_expand[q] = (int32_t)S.n_order;
+    if (S.status != BF_REACHED) {
+        plen[q] = S.status == BF_OVERFLOW ? -2 : 0;
+        cost[q] = INF_D;
+        return;
+    }
+    bf_extract(S, path + (size_t)q * cap, cap, &plen[q], &cost[q]);
+}
+
+extern "C" int pmp_bestfirst(const pmp_grid *g, int algo, int heuristic, int64_t nq,
+                             const int32_t *starts_dev, const int32_t *goals_dev,
+                             void *heap_dev, int64_t heap_cap, double *closed_g_dev,
+                             double *closed_h_dev, uint32_t *closed_parent_dev, uint32_t *order_dev,
+                             int64_t order_cap, uint32_t *path_dev, int64_t path_cap,
+                             int32_t *path_len_dev, double *cost_dev, int32_t *n_expand_dev,
+                             void *stream) {
+    if (!g || nq < 1 || !starts_dev || !goals_dev || !heap_dev || heap_cap < 1 || !closed_g_dev ||
+        !closed_h_dev || !closed_parent_dev || !order_dev || order_cap < 1 || !path_dev ||
+        path_cap < 1 || !path_len_dev || !cost_dev || !n_expand_dev) {
+        pmp_set_error("pmp_bestfirst: bad arguments");
+        return -1;
+    }
+    if (algo < PMP_ASTAR || algo > PMP_LAZY_THETA_STAR) {
+        pmp_set_error("pmp_bestfirst: unknown algorithm %d", algo);
+        return -1;
+    }
+    if (g->d.pcells >= 0xFFFFFFFFull) {
+        pmp_set_error("pmp_bestfirst: grid too large for 32-bit cell indices");
+        return -1;
+    }
+    static_assert(sizeof(BfRec) == PMP_BESTFIRST_HEAP_REC_BYTES, "heap record size is part of the ABI");
+    cudaStream_t s = (cudaStream_t)stream;
+    PMP_CHECK_CUDA(cudaMemsetAsync(closed_parent_dev, 0xFF, (size_t)nq * g->d.pcells * 4, s));
+    const unsigned blocks = (unsigned)((nq * 32 + 63) / 64);
+    if (g->d.ndim == 2)
+        k_bestfirst<2><<<blocks, 64, 0, s>>>(g->d, g->mot, algo, heuristic, (u32)nq, starts_dev, goals_dev,
+                                             (BfRec *)heap_dev, heap_cap, closed_g_dev, closed_h_dev,
+                                             closed_parent_dev, order_dev, order_cap, path_dev, path_cap,
+                                             path_len_dev, cost_dev, n_expand_dev);
+    else
+        k_bestfirst<3><<<blocks, 64, 0, s>>>(g->d, g->mot, algo, heuristic, (u32)nq, starts_dev, goals_dev,
+                                             (BfRec *)heap_dev, heap_cap, closed_g_dev, closed_h_dev,
+                                             closed_parent_dev, order_dev, order_cap, path_dev, path_cap,
+                                             path_len_dev, cost_dev, n_expand_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}

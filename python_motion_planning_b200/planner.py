@@ -14,14 +14,31 @@ different one may be returned; `expand` is the set of cells the wavefront settle
 cells with g + h <= cost), not the reference's pop order; A* with an inadmissible heuristic
 (manhattan on 8/26-connected grids) returns the optimal cost, which can be lower than the
 reference's.
+
+`reference_order=True` (constructor keyword, `planner.reference_order`, the module default
+`set_reference_order()`, or PMP_B200_REFERENCE_ORDER=1) removes those differences: plan() then runs
+the reference's own heap discipline on one warp (`pmp_bestfirst`, csrc/pmp_bestfirst.cu) and cost,
+path, len(expand) and every expand record (current, parent, g, h, in CLOSED order) equal the
+reference's.  It is the mode for the reference's own grid sizes; the wavefront is the mode for
+large grids and batches.
 """
 import math
+import os
 from collections.abc import Sequence
 
 import numpy as np
 
 from . import _lib, engine
 from .environment import Env, Env3D, Grid, Grid3D, Node, Node3D, motion_table
+
+
+_REFERENCE_ORDER = os.environ.get("PMP_B200_REFERENCE_ORDER", "0") not in ("", "0")
+
+
+def set_reference_order(on: bool) -> None:
+    """module default of `reference_order` for planners constructed afterwards"""
+    global _REFERENCE_ORDER
+    _REFERENCE_ORDER = bool(on)
 
 
 class HeadlessPlot:
@@ -107,8 +124,9 @@ class _SearchMixin:
     """What GraphSearcher / GraphSearcher3D add: heuristic, cost, isCollision, and the GPU plan."""
     _algo = _lib.ASTAR
 
-    def _init_search(self, heuristic_type):
+    def _init_search(self, heuristic_type, reference_order=None):
         self.heuristic_type = heuristic_type
+        self.reference_order = _REFERENCE_ORDER if reference_order is None else bool(reference_order)
         self.motions = self.env.motions        # alias, as graph_search.py:26
         self._stats = None                     # device counters of the last plan(): rounds, tiles, cells, edges
         self._stats_dev = None
@@ -328,17 +346,19 @@ def _parents_from_field(f, occ, coords, g, table):
 class GraphSearcher(_SearchMixin, Planner):
     """graph_search.py:11-87"""
 
-    def __init__(self, start: tuple, goal: tuple, env: Grid, heuristic_type: str = "euclidean") -> None:
+    def __init__(self, start: tuple, goal: tuple, env: Grid, heuristic_type: str = "euclidean", *,
+                 reference_order: bool = None) -> None:
         Planner.__init__(self, start, goal, env)
-        self._init_search(heuristic_type)
+        self._init_search(heuristic_type, reference_order)
 
 
 class GraphSearcher3D(_SearchMixin, Planner3D):
     """graph_search_3d.py:11-107"""
 
-    def __init__(self, start: tuple, goal: tuple, env: Grid3D, heuristic_type: str = "euclidean") -> None:
+    def __init__(self, start: tuple, goal: tuple, env: Grid3D, heuristic_type: str = "euclidean", *,
+                 reference_order: bool = None) -> None:
         Planner3D.__init__(self, start, goal, env)
-        self._init_search(heuristic_type)
+        self._init_search(heuristic_type, reference_order)
 
 
 class AStar(GraphSearcher):
@@ -349,6 +369,8 @@ class AStar(GraphSearcher):
         return "A*"
 
     def plan(self) -> tuple:
+        if self.reference_order:
+            return _plan_bestfirst(self, self._algo)
         return self._plan_sssp()
 
     def extractPath(self, closed_list: dict) -> tuple:
@@ -384,6 +406,8 @@ class GBFS(AStar):
         return "Greedy Best First Search(GBFS)"
 
     def plan(self) -> tuple:
+        if self.reference_order:               # also CLOSED order and the g / h of every record
+            return _plan_bestfirst(self, _lib.GBFS)
         return _plan_gbfs(self)
 
 
@@ -391,8 +415,9 @@ class AStar3D(GraphSearcher3D):
     """a_star3d.py:18-111.  plan() -> (cost, path start->goal, expand)."""
     _algo = _lib.ASTAR
 
-    def __init__(self, start: tuple, goal: tuple, env: Grid3D, heuristic_type: str = "euclidean") -> None:
-        super().__init__(start, goal, env, heuristic_type)
+    def __init__(self, start: tuple, goal: tuple, env: Grid3D, heuristic_type: str = "euclidean", *,
+                 reference_order: bool = None) -> None:
+        super().__init__(start, goal, env, heuristic_type, reference_order=reference_order)
         self.start.g = 0.0
         self.start.h = self.h(self.start, self.goal)
 
@@ -400,6 +425,8 @@ class AStar3D(GraphSearcher3D):
         return "A*"
 
     def plan(self) -> tuple:
+        if self.reference_order:
+            return _plan_bestfirst(self, self._algo)
         return self._plan_sssp()
 
     def extractPath(self, closed_list: dict) -> tuple:
@@ -423,8 +450,8 @@ class Dijkstra3D(AStar3D):
     """dijkstra3d.py:19-147: the constructor takes no heuristic argument (dijkstra3d.py:29-31)."""
     _algo = _lib.DIJKSTRA
 
-    def __init__(self, start: tuple, goal: tuple, env: Grid3D) -> None:
-        GraphSearcher3D.__init__(self, start, goal, env, None)
+    def __init__(self, start: tuple, goal: tuple, env: Grid3D, *, reference_order: bool = None) -> None:
+        GraphSearcher3D.__init__(self, start, goal, env, None, reference_order=reference_order)
         self.start.g = 0.0
         self.start.h = 0.0
 
@@ -440,6 +467,8 @@ class GBFS3D(AStar3D):
         return "Greedy Best First Search (GBFS) 3D"
 
     def plan(self) -> tuple:
+        if self.reference_order:               # also CLOSED order and the g / h of every record
+            return _plan_bestfirst(self, _lib.GBFS)
         return _plan_gbfs(self)
 
 
@@ -483,6 +512,56 @@ def _plan_gbfs(planner):
     pts = engine.cells_to_points(ws.path[0, :plen].cpu().numpy(), dg)
     if ndim == 3:
         pts.reverse()
+    return cost, pts, expand
+
+
+def _plan_bestfirst(planner, algo):
+    """plan() in the reference's pop order (pmp_bestfirst): (cost, path, expand) equal to the
+    reference's, expand records included.  algo: _lib.ASTAR / DIJKSTRA / GBFS / THETA_STAR /
+    LAZY_THETA_STAR."""
+    dg = planner._prepare()
+    t = dg.torch
+    ndim = planner._ndim
+    ws = engine.get_workspace(dg, 1, _lib.W_F64)
+    engine.upload_queries(ws, [planner.start.current], [planner.goal.current], ndim)
+    heap_cap = int(min(len(planner.motions) * dg.pcells + 1, 1 << 23))
+    cache = dg.__dict__.setdefault("_bestfirst_cache", {})
+    if cache.get("cap", 0) < heap_cap:
+        cache["heap"] = t.empty(heap_cap * _lib.BESTFIRST_HEAP_REC_BYTES, dtype=t.uint8, device=dg.device)
+        cache["g"] = t.empty(dg.pcells, dtype=t.float64, device=dg.device)
+        cache["h"] = t.empty(dg.pcells, dtype=t.float64, device=dg.device)
+        cache["parent"] = t.empty(dg.pcells, dtype=t.int32, device=dg.device)
+        cache["order"] = t.empty(dg.pcells, dtype=t.int32, device=dg.device)
+        cache["nexp"] = t.empty(1, dtype=t.int32, device=dg.device)
+        cache["cap"] = heap_cap
+    ws.ensure_path(dg.pcells if dg.pcells <= (1 << 22) else planner._path_cap(dg))
+    heur = planner._heuristic_id() if planner.heuristic_type is not None else _lib.H_EUCLIDEAN
+    _lib.check(dg.L.pmp_bestfirst(dg.handle, algo, heur, 1, ws.starts.data_ptr(), ws.goals.data_ptr(),
+                                  cache["heap"].data_ptr(), heap_cap, cache["g"].data_ptr(),
+                                  cache["h"].data_ptr(), cache["parent"].data_ptr(),
+                                  cache["order"].data_ptr(), dg.pcells, ws.path.data_ptr(), ws.path_cap,
+                                  ws.path_len.data_ptr(), ws.cost.data_ptr(), cache["nexp"].data_ptr(),
+                                  dg.stream()), "pmp_bestfirst")
+    res = t.stack([ws.cost[0], ws.path_len[0].to(t.float64), cache["nexp"][0].to(t.float64)]).cpu()
+    cost, plen, n = float(res[0]), int(res[1]), int(res[2])
+    if plen == -2:
+        raise _lib.PmpError("pmp_bestfirst: OPEN / CLOSED capacity exceeded; use the wavefront mode "
+                            "(reference_order=False) for grids of this size")
+    if plen == -1:
+        raise _lib.PmpError("pmp_bestfirst: path longer than the path buffer")
+    # expand = list(CLOSED.values()): insertion order, latest values
+    order = cache["order"][:n].to(t.int64)
+    e_g = cache["g"][order].cpu().numpy()
+    e_h = cache["h"][order].cpu().numpy()
+    e_par = cache["parent"][order].cpu().numpy()
+    coords = engine.cells_to_coords(order.cpu().numpy(), dg)
+    parents = engine.cells_to_coords(e_par, dg)
+    expand = ExpandView(planner._node_cls, coords, e_g, e_h, parents)
+    if plen == 0:
+        return planner._no_path(expand)
+    pts = engine.cells_to_points(ws.path[0, :plen].cpu().numpy(), dg)
+    if ndim == 3:
+        pts.reverse()                          # a_star3d.py:105: start -> goal
     return cost, pts, expand
 
 

@@ -54,8 +54,11 @@ def test_product_never_imports_oracle():
 
 def test_python_surface_matches_reference_contract():
     # constructor signatures (planner.py:13, graph_search.py:21, dijkstra3d.py:29)
-    assert list(inspect.signature(pmp.AStar.__init__).parameters) == ["self", "start", "goal", "env", "heuristic_type"]
-    assert list(inspect.signature(pmp.Dijkstra3D.__init__).parameters) == ["self", "start", "goal", "env"]
+    def positional(fn):   # the reference's parameters; this package only adds keyword-only options
+        return [n for n, p in inspect.signature(fn).parameters.items() if p.kind != p.KEYWORD_ONLY]
+    assert positional(pmp.AStar.__init__) == ["self", "start", "goal", "env", "heuristic_type"]
+    assert positional(pmp.Dijkstra3D.__init__) == ["self", "start", "goal", "env"]
+    assert positional(pmp.ThetaStar3D.__init__) == ["self", "start", "goal", "env", "heuristic_type"]
     env = pmp.Grid(51, 31)
     assert len(env.motions) == 8 and len(env.obstacles) == 2 * 51 + 2 * 31 - 4
     assert [m.current for m in env.motions][:3] == [(-1, 0), (-1, 1), (0, 1)]

@@ -2,8 +2,9 @@
 
 lineOfSight is a predicate, so the bar is exact equality: the oracle's restatement against the
 committed answers of the unmodified reference (tests/golden/los.npz, tools/make_golden_los.py),
-the device kernel against both.  The shortcut kernel has no reference counterpart (the reference
-shortcuts inside the search); it is checked against a plain-Python statement of the same greedy
+the device kernel against both.  Theta* proper (mode="reference") is tested in
+tests/test_bestfirst_gpu.py.  The shortcut kernel (mode="shortcut", for large maps) has no reference
+counterpart (the reference shortcuts inside the search); it is checked against a plain-Python statement of the same greedy
 rule driven by the oracle's lineOfSight (waypoints identical), by properties (every segment
 visible under the reference predicate, cost = sum of segment lengths <= grid A* cost), and its
 cost is compared with the Theta* column of the reference's own CSV.
@@ -105,7 +106,7 @@ def test_theta_star_3d_on_benchmark_scenarios():
         occ = gio.unpack_occ(z["occ_bits"][k], dims)
         s, g = tuple(int(v) for v in z["starts"][k]), tuple(int(v) for v in z["goals"][k])
         env = make_env(pmp, occ)
-        cost, path, expand = pmp.ThetaStar3D(s, g, env).plan()
+        cost, path, expand = pmp.ThetaStar3D(s, g, env, mode="shortcut").plan()
         a_cost, a_path, _ = pmp.AStar3D(s, g, env).plan()
         assert path[0] == s and path[-1] == g
         # every segment passes the reference predicate in the direction updateVertex uses it
@@ -133,7 +134,7 @@ def test_theta_star_2d_vs_reference_costs():
         occ = grids[int(gi)]
         s, g = (int(sx), int(sy)), (int(gx), int(gy))
         env = make_env(pmp, occ)
-        res = pmp.ThetaStar(s, g, env).plan()
+        res = pmp.ThetaStar(s, g, env, mode="shortcut").plan()
         if not math.isfinite(ref_cost):
             assert res == ([], [], [])
             continue
