@@ -40,7 +40,7 @@ typedef struct pmp_grid pmp_grid; /* opaque: occupancy bitmask + motion table on
 
 enum pmp_algo {
     PMP_ASTAR = 0, PMP_DIJKSTRA = 1, PMP_GBFS = 2,
-    PMP_THETA_STAR = 3, PMP_LAZY_THETA_STAR = 4 /* pmp_bestfirst only */
+    PMP_THETA_STAR = 3, PMP_LAZY_THETA_STAR = 4, PMP_JPS = 5 /* pmp_bestfirst only */
 };
 enum pmp_heuristic { PMP_H_EUCLIDEAN = 0, PMP_H_MANHATTAN = 1 };
 enum pmp_weight { PMP_W_F64 = 0, PMP_W_U32 = 1 };
@@ -181,11 +181,11 @@ int pmp_gbfs(const pmp_grid *g, int heuristic, int64_t nq,
              uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
              double *cost_dev, int32_t *n_expand_dev, void *stream);
 
-/* ---- reference-order search: AStar / Dijkstra / GBFS / ThetaStar / LazyThetaStar .plan() and their
- *      3D classes run with the reference's own heap discipline (a_star.py:39-117, dijkstra.py:36-85,
- *      gbfs.py:36-86, theta_star.py:44-108, lazy_theta_star.py:44-118, a_star3d.py:33-106,
- *      dijkstra3d.py:39-143, gbfs3d.py:34-110, theta_star3d.py:38-107,
- *      lazy_theta_star3d.py:41-133): CPython heapq sift order, Node.__lt__ (2D handles) or
+/* ---- reference-order search: AStar / Dijkstra / GBFS / ThetaStar / LazyThetaStar / JPS .plan() and
+ *      their 3D classes run with the reference's own heap discipline (a_star.py:39-117,
+ *      dijkstra.py:36-85, gbfs.py:36-86, theta_star.py:44-108, lazy_theta_star.py:44-118,
+ *      jps.py:38-165, a_star3d.py:33-106, dijkstra3d.py:39-143, gbfs3d.py:34-110,
+ *      theta_star3d.py:38-107, lazy_theta_star3d.py:41-133, jps3d.py:42-246): CPython heapq sift order, Node.__lt__ (2D handles) or
  *      (f, h, counter) tuples (3D handles), dict-ordered CLOSED, parent-pointer extractPath.
  *      Unlike pmp_sssp + pmp_extract_paths, which guarantee the cost only, this reproduces the
  *      returned path among equal-cost ones, len(expand) ("Visited Nodes", examples/benchmark.py:85)

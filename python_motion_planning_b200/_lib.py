@@ -13,7 +13,7 @@ LIB_PATH = os.environ.get("PMP_B200_LIB") or os.path.join(_HERE, "libpmp_b200.so
 CSRC = os.path.join(_HERE, "csrc")
 
 ASTAR, DIJKSTRA, GBFS = 0, 1, 2
-THETA_STAR, LAZY_THETA_STAR = 3, 4          # pmp_bestfirst only
+THETA_STAR, LAZY_THETA_STAR, JPS = 3, 4, 5    # pmp_bestfirst only
 BESTFIRST_HEAP_REC_BYTES = 40
 H_EUCLIDEAN, H_MANHATTAN = 0, 1
 W_F64, W_U32 = 0, 1

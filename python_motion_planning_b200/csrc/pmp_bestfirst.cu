@@ -3,17 +3,20 @@
 // pmp_sssp (pmp_sssp.cu) settles the same costs as the reference with a tiled wavefront, but which
 // of several equal-cost paths comes back, and the content and order of `expand`, follow from the
 // reference's heap discipline.  pmp_bestfirst runs that discipline as written --
-// AStar / Dijkstra / GBFS / ThetaStar / LazyThetaStar .plan() and their 3D classes
+// AStar / Dijkstra / GBFS / ThetaStar / LazyThetaStar / JPS .plan() and their 3D classes
 // (global_planner/graph_search/a_star.py:39-117, dijkstra.py:36-85, gbfs.py:36-86,
 // theta_star.py:44-108, lazy_theta_star.py:44-118, a_star3d.py:33-106, dijkstra3d.py:39-143,
-// gbfs3d.py:34-110, theta_star3d.py:38-107, lazy_theta_star3d.py:41-133) -- so cost, path,
+// gbfs3d.py:34-110, theta_star3d.py:38-107, lazy_theta_star3d.py:41-133, jps.py:38-165,
+// jps3d.py:42-246) -- so cost, path,
 // len(expand) and every expand record equal the reference's.  One warp per query: lane 0 owns the
 // OPEN heap and the CLOSED table (pmp_bestfirst_core.h), the lanes evaluate the motions of the
-// popped node in parallel (edge legality, CLOSED dominance, heuristic, Theta* line of sight) and
+// popped node in parallel (edge legality, CLOSED dominance, heuristic, Theta* line of sight, a whole
+// jump of JPS per lane) and
 // lane 0 pushes the survivors in motion order.  Independent queries run in parallel warps.
 #include "pmp_common.cuh"
 #include "pmp_los.cuh"
 #include "pmp_bestfirst_core.h"
+#include "pmp_jps_core.h"
 
 struct BfEnvDev {
     const GridDev &G;
@@ -21,6 +24,20 @@ struct BfEnvDev {
     __device__ bool legal(int m, int x, int y, int z) const { return edge_legal(G, M, m, x, y, z); }
     __device__ bool los(int ax, int ay, int az, int bx, int by, int bz) const {
         return ::los(G, ax, ay, az, bx, by, bz);
+    }
+    __device__ bool inbox(int x, int y, int z) const {
+        return x >= 0 && y >= 0 && z >= 0 && x < G.X && y < G.Y && z < G.Z;
+    }
+    __device__ bool obst(int x, int y, int z) const { return inbox(x, y, z) && cell_blocked(G, x, y, z); }
+    // not isCollision((x,y,z), (x,y,z) + d) for any unit offset d (graph_search_3d.py:66-107)
+    __device__ bool legal_dir(int dx, int dy, int dz, int x, int y, int z) const {
+        if (cell_blocked(G, x, y, z) || cell_blocked(G, x + dx, y + dy, z + dz)) return false;
+        if ((dx != 0) + (dy != 0) + (dz != 0) >= 2) {
+            if (dx && cell_blocked(G, x + dx, y, z)) return false;
+            if (dy && cell_blocked(G, x, y + dy, z)) return false;
+            if (dz && cell_blocked(G, x, y, z + dz)) return false;
+        }
+        return true;
     }
     __device__ int k() const { return M.k; }
     __device__ void offset(int m, int &dx, int &dy, int &dz) const { dx = M.dx[m]; dy = M.dy[m]; dz = M.dz[m]; }
@@ -85,7 +102,13 @@ __global__ void k_bestfirst(const GridDev G, const __grid_constant__ Motions M, 
         BfRec cand;
         cand.f = cand.h = cand.g = 0.0;
         cand.cell = cand.parent = cand.counter = cand.pad = 0;
-        const bool push = lane < M.k && bf_eval<FAMILY>(S, env, node, lane, myw, cand);
+        bool push = false;
+        if (lane < M.k) {
+            if (algo == BF_JPS)
+                push = FAMILY == 2 ? jps2d_eval(S, env, node, lane, myw, cand) : jps3d_eval(S, env, node, lane, cand);
+            else
+                push = bf_eval<FAMILY>(S, env, node, lane, myw, cand);
+        }
         const u32 mask = __ballot_sync(FULL, push);
         int stop = 0;
         for (int m = 0; m < M.k && !stop; ++m) { // lane 0 pushes in motion order
@@ -128,7 +151,7 @@ extern "C" int pmp_bestfirst(const pmp_grid *g, int algo, int heuristic, int64_t
         pmp_set_error("pmp_bestfirst: bad arguments");
         return -1;
     }
-    if (algo < PMP_ASTAR || algo > PMP_LAZY_THETA_STAR) {
+    if (algo < PMP_ASTAR || algo > PMP_JPS) {
         pmp_set_error("pmp_bestfirst: unknown algorithm %d", algo);
         return -1;
     }

@@ -9,7 +9,7 @@
 
 #include <vector>
 
-#include "../python_motion_planning_b200/csrc/pmp_bestfirst_core.h"
+#include "../python_motion_planning_b200/csrc/pmp_jps_core.h"
 
 typedef int (*los_fn_t)(int ndim, const int32_t *dims, const uint8_t *occ, int64_t n, const int32_t *a,
                         const int32_t *b, uint8_t *out);
@@ -43,6 +43,19 @@ struct HostEnv {
         los_fn(ndim, dims, occ, 1, a, b, &out);
         return out != 0;
     }
+    bool inbox(int x, int y, int z) const {
+        return x >= 0 && y >= 0 && z >= 0 && x < dims[0] && y < dims[1] && z < dims[2];
+    }
+    bool obst(int x, int y, int z) const { return inbox(x, y, z) && blocked(x, y, z); }
+    bool legal_dir(int dx, int dy, int dz, int x, int y, int z) const {
+        if (blocked(x, y, z) || blocked(x + dx, y + dy, z + dz)) return false;
+        if ((dx != 0) + (dy != 0) + (dz != 0) >= 2) {
+            if (dx && blocked(x + dx, y, z)) return false;
+            if (dy && blocked(x, y + dy, z)) return false;
+            if (dz && blocked(x, y, z + dz)) return false;
+        }
+        return true;
+    }
     int k() const { return nk; }
     void offset(int m, int &dx, int &dy, int &dz) const { dx = mot[3 * m]; dy = mot[3 * m + 1]; dz = mot[3 * m + 2]; }
     double len(int m) const {
@@ -62,7 +75,9 @@ static void run(BfState &S, const HostEnv &env, const double *w, const int32_t *
         BfRec cand[32];
         bool push[32];
         for (int lane = 0; lane < env.nk; ++lane)
-            push[lane] = bf_eval<FAMILY>(S, env, node, lane, w[lane], cand[lane]);
+            push[lane] = S.algo == BF_JPS
+                ? (FAMILY == 2 ? jps2d_eval(S, env, node, lane, w[lane], cand[lane]) : jps3d_eval(S, env, node, lane, cand[lane]))
+                : bf_eval<FAMILY>(S, env, node, lane, w[lane], cand[lane]);
         for (int m = 0; m < env.nk; ++m) {
             if (!push[m]) continue;
             if (bf_push<FAMILY>(S, cand[m])) break;
