@@ -108,8 +108,8 @@ def main():
                         planner = cls(start=start, goal=goal, env=env)
                         if args.order == "reference":
                             planner.reference_order = True         # astar / dijkstra / gbfs
-                        elif hasattr(planner, "mode"):
-                            planner.mode = "shortcut"              # theta_star / lazy_theta_star
+                        elif hasattr(planner, "mode"):             # theta_star / lazy_theta_star; jps
+                            planner.mode = "wavefront" if name == "jps" else "shortcut"
                         t0 = time.time()
                         cost, path, expand = planner.plan()
                         t1 = time.time()

@@ -4,7 +4,8 @@ tests/bestfirst_host.cpp compiles that header with g++ and drives it exactly as 
 (lane 0: pop / push / close, one bf_eval per motion).  Here its outputs are compared, EXACTLY, with
 outputs of the unmodified reference committed under tests/golden/ -- A*, Dijkstra, GBFS
 (cases2d / cases3d / the reference's own CSV) and Theta*, Lazy Theta* (anyangle2d / anyangle3d /
-the CSV's theta_star and lazy_theta_star rows): cost, path, CLOSED order, g, h, parent.
+the CSV's theta_star and lazy_theta_star rows) and JPS / JPS3D (jpscases2d / jpscases3d; jump functions
+in csrc/pmp_jps_core.h): cost, path, CLOSED order, g, h, parent.
 The kernel itself is checked the same way on the GPU (tests/test_bestfirst_gpu.py).
 """
 import ctypes
@@ -27,7 +28,7 @@ THETA, LAZY = 3, 4
 
 @pytest.fixture(scope="module")
 def host():
-    newest = max(os.path.getmtime(SRC), os.path.getmtime(CORE))
+    newest = max(os.path.getmtime(f) for f in (SRC, CORE, os.path.join(os.path.dirname(CORE), "pmp_jps_core.h")))
     if not os.path.exists(SO) or os.path.getmtime(SO) < newest:
         subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-Wall", "-shared", "-o", SO, SRC], check=True)
     L = ctypes.CDLL(SO)
@@ -84,7 +85,8 @@ def check_cases(L, cases):
 
 
 @pytest.mark.parametrize("fname,ndim", [("cases2d.npz", 2), ("cases3d.npz", 3),
-                                        ("anyangle2d.npz", 2), ("anyangle3d.npz", 3)])
+                                        ("anyangle2d.npz", 2), ("anyangle3d.npz", 3),
+                                        ("jpscases2d.npz", 2), ("jpscases3d.npz", 3)])
 def test_core_equals_reference(host, fname, ndim):
     check_cases(host, gio.Cases(fname, ndim))
 

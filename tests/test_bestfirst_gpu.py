@@ -15,8 +15,9 @@ from tests.test_gpu_parity import make_env
 
 pytestmark = pytest.mark.gpu
 
-CLS = {2: {0: pmp.AStar, 1: pmp.Dijkstra, 2: pmp.GBFS, 3: pmp.ThetaStar, 4: pmp.LazyThetaStar},
-       3: {0: pmp.AStar3D, 1: pmp.Dijkstra3D, 2: pmp.GBFS3D, 3: pmp.ThetaStar3D, 4: pmp.LazyThetaStar3D}}
+CLS = {2: {0: pmp.AStar, 1: pmp.Dijkstra, 2: pmp.GBFS, 3: pmp.ThetaStar, 4: pmp.LazyThetaStar, 5: pmp.JPS},
+       3: {0: pmp.AStar3D, 1: pmp.Dijkstra3D, 2: pmp.GBFS3D, 3: pmp.ThetaStar3D, 4: pmp.LazyThetaStar3D,
+           5: pmp.JPS3D}}
 
 
 def make_planner(ndim, algo, start, goal, env, heur="euclidean"):
@@ -36,7 +37,8 @@ def flat(coords, shape):
 
 
 @pytest.mark.parametrize("fname,ndim", [("cases2d.npz", 2), ("cases3d.npz", 3),
-                                        ("anyangle2d.npz", 2), ("anyangle3d.npz", 3)])
+                                        ("anyangle2d.npz", 2), ("anyangle3d.npz", 3),
+                                        ("jpscases2d.npz", 2), ("jpscases3d.npz", 3)])
 def test_reference_order_equals_reference(fname, ndim):
     cases = gio.Cases(fname, ndim)
     n_found = 0

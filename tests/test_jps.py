@@ -104,7 +104,7 @@ def test_jps_matches_reference_costs():
     for k, (gi, sx, sy, gx, gy, ref) in enumerate(z["jps2d_queries"]):
         occ, env = g2[int(gi)], envs[int(gi)]
         s, g = (int(sx), int(sy)), (int(gx), int(gy))
-        res = pmp.JPS(s, g, env).plan()
+        res = pmp.JPS(s, g, env, mode="wavefront").plan()
         if math.isinf(ref):
             assert res == ([], [], [])
             continue
@@ -125,7 +125,7 @@ def test_jps_matches_reference_costs():
     for t, sx, sy, sz, gx, gy, gz, cj, ca in z["jps3d_queries"]:
         occ, env = g3[int(t)], envs3[int(t)]
         s, g = (int(sx), int(sy), int(sz)), (int(gx), int(gy), int(gz))
-        cost, path, _ = pmp.JPS3D(s, g, env).plan()
+        cost, path, _ = pmp.JPS3D(s, g, env, mode="wavefront").plan()
         if math.isinf(ca):
             assert math.isinf(cost) and path == []
             continue

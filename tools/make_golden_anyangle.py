@@ -10,6 +10,9 @@ written from the UNMODIFIED reference in the build container (needs /root/refere
     rows of the reference's 3d_pathfinding_results.csv for the 500 instances of csv_replay.npz,
     next to what the reference returns when run here.
 
+  * jpscases2d.npz / jpscases3d.npz -- JPS (jps.py) and JPS3D (jps3d.py) in the same layout, algo id 5:
+    the jump-point path, CLOSED order, g, h, parent.
+
     python tools/make_golden_anyangle.py
 """
 import csv
@@ -25,7 +28,7 @@ import ref_harness  # noqa: E402
 import make_golden as mg  # noqa: E402
 from tests import golden_io as gio  # noqa: E402
 
-THETA, LAZY = 3, 4
+THETA, LAZY, JPS = 3, 4, 5
 
 
 def env2d_from(pmp, occ):
@@ -84,6 +87,61 @@ def make_3d(pmp):
     print("anyangle3d:", len(cw.meta), "cases;", sum(cw.found), "with a path")
 
 
+def make_jps(pmp):
+    sys.setrecursionlimit(100000)
+    ref_harness.fast_grid_map(pmp)
+    cw = mg.CaseWriter(2)
+    c2 = gio.Cases("cases2d.npz", 2)
+    env = mg.readme_env(pmp)
+    gi = cw.add_grid("readme", mg.dense(env, 2))
+    for heur in ("euclidean", "manhattan"):
+        res = mg.run(pmp.JPS(start=(5, 5), goal=(45, 25), env=env, heuristic_type=heur), (51, 31))
+        cw.add(gi, JPS, mg.HEUR_ID[heur], 8, (5, 5), (45, 25), res)
+        print("readme jps", heur, repr(res["cost"]), len(res["path"]), len(res["e_cell"]))
+    cw.add(gi, JPS, 0, 8, (5, 5), (5, 5), mg.run(pmp.JPS(start=(5, 5), goal=(5, 5), env=env), (51, 31)))
+    for name, occ in zip(c2.grid_names[1:5], c2.grids[1:5]):
+        env = env2d_from(pmp, occ)
+        gi = cw.add_grid(name, occ)
+        pts = mg.free_cells(occ, np.random.default_rng(700 + gi), 16)
+        for qi in range(8):
+            s, g = pts[2 * qi], pts[2 * qi + 1]
+            cw.add(gi, JPS, 0, 8, s, g, mg.run(pmp.JPS(start=s, goal=g, env=env), occ.shape))
+    cw.save("jpscases2d.npz")
+    print("jpscases2d:", len(cw.meta), "cases;", sum(cw.found), "with a path")
+    cw = mg.CaseWriter(3)
+    for mset, dims, seed, nb in ((26, (18, 14, 10), 41, 14), (26, (16, 16, 12), 42, 24), (18, (16, 13, 10), 43, 14),
+                                 (6, (14, 12, 10), 44, 12)):
+        env = mg.boxes_env3d(pmp, dims, nb, 4, seed)
+        if mset == 18:
+            env.motions = [m for m in env.motions if m.g < 1.5]
+        elif mset == 6:
+            env.motions = [m for m in env.motions if m.g == 1]
+        occ = mg.dense(env, 3)
+        gi = cw.add_grid(f"boxes_{mset}conn_{seed}", occ)
+        pts = mg.free_cells(occ, np.random.default_rng(500 + seed), 12)
+        for qi in range(6):
+            s, g = pts[2 * qi], pts[2 * qi + 1]
+            heur = "manhattan" if qi == 5 else "euclidean"
+            res = mg.run(pmp.JPS3D(start=s, goal=g, env=env, heuristic_type=heur), dims)
+            cw.add(gi, JPS, mg.HEUR_ID[heur], mset, s, g, res)
+        cw.add(gi, JPS, 0, mset, pts[0], pts[0], mg.run(pmp.JPS3D(start=pts[0], goal=pts[0], env=env), dims))
+        cw.add(gi, JPS, 0, mset, pts[0], (0, 0, 0), mg.run(pmp.JPS3D(start=pts[0], goal=(0, 0, 0), env=env), dims))
+    # the benchmark scenarios of examples/scenarios.py (21 x 15 x 11), first 4 seeds of each
+    z = gio.load("csv_replay.npz")
+    dims = tuple(int(v) for v in z["dims"])
+    for k in range(len(z["starts"])):
+        if int(z["seeds"][k]) >= 4:
+            continue
+        occ = gio.unpack_occ(z["occ_bits"][k], dims)
+        env = pmp.Grid3D(*dims)
+        env.update(set(map(tuple, np.argwhere(occ).tolist())))
+        gi = cw.add_grid(f"csv_{k}", occ)
+        s, g = tuple(int(v) for v in z["starts"][k]), tuple(int(v) for v in z["goals"][k])
+        cw.add(gi, JPS, 0, 26, s, g, mg.run(pmp.JPS3D(start=s, goal=g, env=env), dims))
+    cw.save("jpscases3d.npz")
+    print("jpscases3d:", len(cw.meta), "cases;", sum(cw.found), "with a path")
+
+
 def make_csv(pmp):
     ref_harness.fast_grid_map(pmp)
     z = gio.load("csv_replay.npz")
@@ -123,10 +181,12 @@ def make_csv(pmp):
 
 if __name__ == "__main__":
     pmp = ref_harness.load_reference()
-    which = sys.argv[1:] or ["2d", "3d", "csv"]
+    which = sys.argv[1:] or ["2d", "3d", "jps", "csv"]
     if "2d" in which:
         make_2d(pmp)
     if "3d" in which:
         make_3d(pmp)
+    if "jps" in which:
+        make_jps(pmp)
     if "csv" in which:
         make_csv(pmp)
