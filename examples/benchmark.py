@@ -11,7 +11,8 @@ with the iteration index and draws start / goal (benchmark.py:46-75).  Those 500
 tests/golden/csv_replay.npz, written from the unmodified reference by tools/make_golden.py, so this
 script replays exactly the instances behind the reference's 3d_pathfinding_results.csv and its
 output can be compared with that file row by row: with --order reference (default) Distance and
-Visited Nodes of the astar / dijkstra / gbfs / theta_star / lazy_theta_star rows are equal
+Visited Nodes of all seven algorithms' rows (astar, dstar, dijkstra, gbfs, lazy_theta_star, theta_star,
+lpastar) are equal
 (tests/test_examples.py); with --order wavefront Distance of astar / dijkstra.
 With --scenarios-module the maps are generated live instead, from a module that offers the
 reference's interface (`scenarios` dict of env -> obstacle set, `carve_safety_bubble`).
@@ -107,7 +108,7 @@ def main():
                         env.update(set(map(tuple, np.argwhere(occ).tolist())))
                         planner = cls(start=start, goal=goal, env=env)
                         if args.order == "reference":
-                            planner.reference_order = True         # astar / dijkstra / gbfs
+                            planner.reference_order = True         # astar / dijkstra / gbfs / lpastar / dstar
                         elif hasattr(planner, "mode"):             # theta_star / lazy_theta_star; jps
                             planner.mode = "wavefront" if name == "jps" else "shortcut"
                         t0 = time.time()

@@ -204,6 +204,37 @@ int pmp_bestfirst(const pmp_grid *g, int algo, int heuristic, int64_t nq,
                   uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev, double *cost_dev,
                   int32_t *n_expand_dev, void *stream);
 
+/* ---- LPA* / D* in the reference's processing order (row f1, reference-order mode).  LPAStar /
+ *      LPAStar3D (lpa_star.py:62-230, lpa_star3d.py:57-225: computeShortestPath, updateVertex,
+ *      calculateKey, greedy extractPath, apply_change / OnPress) and DStar / DStar3D (d_star.py:60-291,
+ *      d_star3d.py:68-280: processState, insert, delete, modify, extractPath, OnPress /
+ *      apply_dynamic_obstacles) with the reference's own containers -- OPEN as a Python list searched by
+ *      min() and edited by list.remove(), heapq.heappush on it -- so cost, path and len(EXPAND)
+ *      ("Visited Nodes") equal the reference's, also where it is not optimal.  pmp_replan_* is the
+ *      parallel repair that returns the optimum.  One thread runs the algorithm; for the
+ *      reference's own grid sizes.  All state lives in caller-owned device arrays that must be kept
+ *      between calls: per padded cell g, rhs, key[2] (LPA*) or h, k, parent, tag (D*), the list
+ *      (list_cap cells) and ctl_dev (4 x int64: [0] list length, [1] status).
+ *   op 0: initialise the state and plan.  start_goal_dev: 2 x 3 int32.
+ *   op 1: LPA*: change_dev = {x, y, z, freed}: the occupancy of that cell was just edited
+ *         (pmp_grid_edit_cells; freed = 1 if an obstacle was removed) -> updateVertex of the cell /
+ *         its neighbours, then plan.  D*: obstacles were just added -> walk the back pointers from the
+ *         start and repair (modify) where an edge collides.
+ *   outputs: expand_dev = EXPAND (cells), n_expand_dev its length; path_dev: LPA* goal first, D*
+ *   start first (the 2D D* walk of op 1 leaves the goal out, d_star.py:117-127); path_len_dev 0 = no
+ *   path, -2 = a capacity was exceeded; cost_dev as the reference sums it (inf when a D* back
+ *   pointer's reverse edge is illegal under the directed corner rule). */
+int pmp_lpa_star(const pmp_grid *g, int op, int heuristic, const int32_t *start_goal_dev,
+                 const int32_t *change_dev, double *g_dev, double *rhs_dev, double *key_dev,
+                 uint32_t *list_dev, int64_t list_cap, int64_t *ctl_dev, uint32_t *expand_dev,
+                 int64_t expand_cap, uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
+                 double *cost_dev, int32_t *n_expand_dev, void *stream);
+int pmp_d_star(const pmp_grid *g, int op, const int32_t *start_goal_dev, double *h_dev, double *k_dev,
+               uint32_t *parent_dev, uint8_t *tag_dev, uint32_t *list_dev, int64_t list_cap,
+               int64_t *ctl_dev, uint32_t *expand_dev, int64_t expand_cap, uint32_t *path_dev,
+               int64_t path_cap, int32_t *path_len_dev, double *cost_dev, int32_t *n_expand_dev,
+               void *stream);
+
 /* ---- slab mode: one z-slab (plus one ghost plane per interior side) of a large 3D grid per
  *      GPU; the cost-to-go field of BASELINE.json config 5.  The handle describes the LOCAL slab.
  *      Host loop (python_motion_planning_b200/slab.py): begin; repeat { run(bound); exchange

@@ -26,6 +26,7 @@ SYMBOLS = (
     "pmp_grid_set_dense", "pmp_grid_set_dense_xyz", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
     "pmp_grid_set_motions", "pmp_grid_set_corner_cutting", "pmp_sssp_sizes", "pmp_sssp", "pmp_field_finalize",
     "pmp_count_settled", "pmp_extract_paths", "pmp_verify_field", "pmp_gbfs", "pmp_bestfirst",
+    "pmp_lpa_star", "pmp_d_star",
     "pmp_slab_begin", "pmp_slab_run", "pmp_slab_merge", "pmp_replan_begin", "pmp_replan_update",
     "pmp_line_of_sight", "pmp_shortcut_paths",
 )
@@ -94,6 +95,8 @@ def lib():
         "pmp_verify_field": [vp, i32, vp, vp, i32, i32, vp, vp],
         "pmp_gbfs": [vp, i32, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp, vp],
         "pmp_bestfirst": [vp, i32, i32, i64, vp, vp, vp, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp, vp],
+        "pmp_lpa_star": [vp, i32, i32, vp, vp, vp, vp, vp, vp, i64, vp, vp, i64, vp, i64, vp, vp, vp, vp],
+        "pmp_d_star": [vp, i32, vp, vp, vp, vp, vp, vp, i64, vp, vp, i64, vp, i64, vp, vp, vp, vp],
         "pmp_slab_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, i64, vp],
         "pmp_slab_run": [vp, ctypes.POINTER(SsspParams), vp, vp, i64, dbl, vp, vp],
         "pmp_slab_merge": [vp, i32, vp, vp, i64, i32, i32, vp, vp, vp],

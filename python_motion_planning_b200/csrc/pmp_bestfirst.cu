@@ -17,6 +17,7 @@
 #include "pmp_los.cuh"
 #include "pmp_bestfirst_core.h"
 #include "pmp_jps_core.h"
+#include "pmp_incr_core.h"
 
 struct BfEnvDev {
     const GridDev &G;
@@ -173,6 +174,129 @@ extern "C" int pmp_bestfirst(const pmp_grid *g, int algo, int heuristic, int64_t
                                              (BfRec *)heap_dev, heap_cap, closed_g_dev, closed_h_dev,
                                              closed_parent_dev, order_dev, order_cap, path_dev, path_cap,
                                              path_len_dev, cost_dev, n_expand_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// LPA* / D* in the reference's processing order (pmp_incr_core.h).  Sequential algorithms on Python
+// lists: thread 0 of one CTA runs them, the CTA's other threads only initialise the per-cell state.
+// ---------------------------------------------------------------------------------------------
+__device__ static void incr_geometry(BfState &S, const GridDev &G, int heuristic, const int32_t *sg) {
+    S.heap = nullptr; S.hn = 0; S.heap_cap = 0;
+    S.cg = S.ch = nullptr; S.cpar = nullptr; S.order = nullptr; S.n_order = 0; S.order_cap = 0;
+    S.counter = 0; S.algo = 0; S.heuristic = heuristic;
+    S.PX = G.PX; S.PY = G.PY;
+    S.gx = sg[3]; S.gy = sg[4]; S.gz = G.ndim == 3 ? sg[5] : 0;
+    S.start_cell = bf_cell(S, sg[0], sg[1], G.ndim == 3 ? sg[2] : 0);
+    S.goal_cell = bf_cell(S, S.gx, S.gy, S.gz);
+    S.status = BF_RUNNING;
+}
+
+__device__ static bool incr_query_ok(const GridDev &G, const int32_t *sg) {
+    const int sz = G.ndim == 3 ? sg[2] : 0, gz = G.ndim == 3 ? sg[5] : 0;
+    return sg[0] >= 0 && sg[1] >= 0 && sz >= 0 && sg[0] < G.X && sg[1] < G.Y && sz < G.Z &&
+           sg[3] >= 0 && sg[4] >= 0 && gz >= 0 && sg[3] < G.X && sg[4] < G.Y && gz < G.Z;
+}
+
+__global__ void k_lpa_star(const GridDev G, const __grid_constant__ Motions M, int op, int heuristic,
+                           const int32_t *sg, const int32_t *change, double *g, double *rhs, double *key,
+                           u32 *list, int64_t list_cap, int64_t *ctl, u32 *expand, int64_t expand_cap,
+                           u32 *path, int64_t cap, int32_t *plen, double *cost, int32_t *n_expand) {
+    const double INF_D = __longlong_as_double(0x7ff0000000000000LL);
+    if (op == 0) {
+        for (size_t i = threadIdx.x; i < G.pcells; i += blockDim.x) { g[i] = INF_D; rhs[i] = INF_D; }
+        __syncthreads();
+    }
+    if (threadIdx.x != 0) return;
+    if (!incr_query_ok(G, sg)) { *plen = 0; *cost = INF_D; *n_expand = 0; return; }
+    LpaState L;
+    L.g = g; L.rhs = rhs; L.k1 = key; L.k2 = key + G.pcells;
+    L.U = list; L.ucap = list_cap; L.un = op == 0 ? 0 : ctl[0];
+    L.expand = expand; L.expand_cap = expand_cap; L.n_expand = 0;
+    L.family = G.ndim;
+    L.status = BF_RUNNING;
+    incr_geometry(L.S, G, heuristic, sg);
+    const BfEnvDev env = {G, M};
+    if (op == 0) lpa_init(L);
+    else lpa_apply_change(L, env, change[0], change[1], G.ndim == 3 ? change[2] : 0, change[3] != 0);
+    lpa_compute(L, env);
+    ctl[0] = L.un;
+    ctl[1] = L.status;
+    *n_expand = (int32_t)L.n_expand;
+    if (L.status == BF_OVERFLOW) { *plen = -2; *cost = INF_D; return; }
+    lpa_extract(L, env, path, cap, plen, cost);
+}
+
+__global__ void k_d_star(const GridDev G, const __grid_constant__ Motions M, int op, const int32_t *sg,
+                         double *h, double *k, u32 *parent, uint8_t *tag, u32 *list, int64_t list_cap,
+                         int64_t *ctl, u32 *expand, int64_t expand_cap, u32 *path, int64_t cap,
+                         int32_t *plen, double *cost, int32_t *n_expand) {
+    const double INF_D = __longlong_as_double(0x7ff0000000000000LL);
+    if (op == 0) {
+        for (size_t i = threadIdx.x; i < G.pcells; i += blockDim.x) {
+            h[i] = INF_D; k[i] = INF_D; parent[i] = BF_NONE; tag[i] = DS_NEW;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x != 0) return;
+    if (!incr_query_ok(G, sg)) { *plen = 0; *cost = INF_D; *n_expand = 0; return; }
+    DsState D;
+    D.h = h; D.k = k; D.parent = parent; D.t = tag;
+    D.OPEN = list; D.ocap = list_cap; D.on = op == 0 ? 0 : ctl[0];
+    D.expand = expand; D.expand_cap = expand_cap; D.n_expand = 0;
+    D.family = G.ndim;
+    D.status = BF_RUNNING;
+    incr_geometry(D.S, G, PMP_H_EUCLIDEAN, sg);
+    const BfEnvDev env = {G, M};
+    if (op == 0) {
+        ds_init(D);
+        ds_plan(D, env);
+        if (D.status != BF_OVERFLOW) ds_extract(D, env, path, cap, plen, cost);
+    } else {
+        ds_replan(D, env, path, cap, plen, cost);
+    }
+    ctl[0] = D.on;
+    ctl[1] = D.status;
+    *n_expand = (int32_t)D.n_expand;
+    if (D.status == BF_OVERFLOW) { *plen = -2; *cost = INF_D; }
+}
+
+extern "C" int pmp_lpa_star(const pmp_grid *g, int op, int heuristic, const int32_t *start_goal_dev,
+                            const int32_t *change_dev, double *g_dev, double *rhs_dev, double *key_dev,
+                            uint32_t *list_dev, int64_t list_cap, int64_t *ctl_dev, uint32_t *expand_dev,
+                            int64_t expand_cap, uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
+                            double *cost_dev, int32_t *n_expand_dev, void *stream) {
+    if (!g || (op != 0 && op != 1) || !start_goal_dev || (op == 1 && !change_dev) || !g_dev || !rhs_dev ||
+        !key_dev || !list_dev || list_cap < 1 || !ctl_dev || !expand_dev || expand_cap < 1 || !path_dev ||
+        path_cap < 1 || !path_len_dev || !cost_dev || !n_expand_dev) {
+        pmp_set_error("pmp_lpa_star: bad arguments");
+        return -1;
+    }
+    if (g->d.pcells >= 0xFFFFFFFFull) { pmp_set_error("pmp_lpa_star: grid too large for 32-bit cell indices"); return -1; }
+    k_lpa_star<<<1, 256, 0, (cudaStream_t)stream>>>(g->d, g->mot, op, heuristic, start_goal_dev, change_dev, g_dev,
+                                                    rhs_dev, key_dev, list_dev, list_cap, ctl_dev, expand_dev,
+                                                    expand_cap, path_dev, path_cap, path_len_dev, cost_dev,
+                                                    n_expand_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pmp_d_star(const pmp_grid *g, int op, const int32_t *start_goal_dev, double *h_dev, double *k_dev,
+                          uint32_t *parent_dev, uint8_t *tag_dev, uint32_t *list_dev, int64_t list_cap,
+                          int64_t *ctl_dev, uint32_t *expand_dev, int64_t expand_cap, uint32_t *path_dev,
+                          int64_t path_cap, int32_t *path_len_dev, double *cost_dev, int32_t *n_expand_dev,
+                          void *stream) {
+    if (!g || (op != 0 && op != 1) || !start_goal_dev || !h_dev || !k_dev || !parent_dev || !tag_dev ||
+        !list_dev || list_cap < 1 || !ctl_dev || !expand_dev || expand_cap < 1 || !path_dev || path_cap < 1 ||
+        !path_len_dev || !cost_dev || !n_expand_dev) {
+        pmp_set_error("pmp_d_star: bad arguments");
+        return -1;
+    }
+    if (g->d.pcells >= 0xFFFFFFFFull) { pmp_set_error("pmp_d_star: grid too large for 32-bit cell indices"); return -1; }
+    k_d_star<<<1, 256, 0, (cudaStream_t)stream>>>(g->d, g->mot, op, start_goal_dev, h_dev, k_dev, parent_dev, tag_dev,
+                                                  list_dev, list_cap, ctl_dev, expand_dev, expand_cap, path_dev,
+                                                  path_cap, path_len_dev, cost_dev, n_expand_dev);
     PMP_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

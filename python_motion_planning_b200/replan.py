@@ -11,6 +11,12 @@ The repaired field equals the field of a search from scratch on the new map (tes
 bit for bit), so the returned cost is the optimum; the reference's LPA* extracts its path by
 greedy descent on g alone (lpa_star.py:209-229) and returns a longer path in ~17 % of the rows of
 its own 3d_pathfinding_results.csv -- documented divergence: cost <= the reference's.
+
+`reference_order=True` removes that divergence for LPAStar / LPAStar3D / DStar / DStar3D: plan() and
+the change entry points then run the reference's own containers and processing order on the device
+(`pmp_lpa_star` / `pmp_d_star`, csrc/pmp_incr_core.h) and return the reference's cost, path and
+EXPAND -- greedy-descent detours, D*'s inf costs over directed corner edges and all.  Sequential; for
+the reference's own grid sizes.
 """
 import ctypes
 import math
@@ -19,7 +25,7 @@ import numpy as np
 
 from . import _lib, engine
 from .environment import Node, Node3D
-from .planner import GraphSearcher, GraphSearcher3D
+from .planner import ExpandView, GraphSearcher, GraphSearcher3D
 
 
 class ReplanSession:
@@ -83,20 +89,141 @@ class ReplanSession:
         return self.info
 
 
+class ReferenceIncrSession:
+    """Device state of pmp_lpa_star / pmp_d_star: the reference's own LPA* / D* containers (per-cell
+    g, rhs, key or h, k, parent, tag; the OPEN list; EXPAND), kept between calls so that
+    apply_change / apply_dynamic_obstacles continue where plan() stopped, as the reference's planner
+    objects do (csrc/pmp_incr_core.h)."""
+
+    def __init__(self, dg, kind, heuristic, start, goal):
+        t = dg.torch
+        n = dg.pcells
+        self.dg, self.kind, self.heuristic = dg, kind, heuristic      # kind 0: LPA*, 1: D*
+        dev = dg.device
+        self.a = t.empty(n, dtype=t.float64, device=dev)               # g   | h
+        self.b = t.empty(n, dtype=t.float64, device=dev)               # rhs | k
+        self.key = t.empty(2 * n, dtype=t.float64, device=dev) if kind == 0 else None
+        self.parent = t.empty(n, dtype=t.int32, device=dev) if kind == 1 else None
+        self.tag = t.empty(n, dtype=t.uint8, device=dev) if kind == 1 else None
+        self.list_cap = 8 * n + 64
+        self.list = t.empty(self.list_cap, dtype=t.int32, device=dev)
+        self.ctl = t.zeros(4, dtype=t.int64, device=dev)
+        self.expand_cap = int(min(16 * n + 1024, 1 << 24))
+        self.expand = t.empty(self.expand_cap, dtype=t.int32, device=dev)
+        self.path_cap = int(max(n, 4096))
+        self.path = t.empty(self.path_cap, dtype=t.int32, device=dev)
+        self.out_i = t.zeros(2, dtype=t.int32, device=dev)             # path_len, n_expand
+        self.out_cost = t.zeros(1, dtype=t.float64, device=dev)
+        sg = np.zeros((2, 3), dtype=np.int32)
+        sg[0, :dg.ndim] = start
+        sg[1, :dg.ndim] = goal
+        self.sg = t.from_numpy(sg).to(dev)
+        self.change = t.zeros(4, dtype=t.int32, device=dev)
+
+    def step(self, op, change=None):
+        """op 0: plan from scratch; op 1: continue after an occupancy edit (LPA*: change = (coord, freed)).
+        Returns (cost, path cells in kernel order, EXPAND cells)."""
+        dg = self.dg
+        t = dg.torch
+        if change is not None:
+            c = np.zeros(4, dtype=np.int32)
+            c[:dg.ndim] = change[0]
+            c[3] = 1 if change[1] else 0
+            self.change.copy_(t.from_numpy(c))
+        if self.kind == 0:
+            rc = dg.L.pmp_lpa_star(dg.handle, op, self.heuristic, self.sg.data_ptr(), self.change.data_ptr(),
+                                   self.a.data_ptr(), self.b.data_ptr(), self.key.data_ptr(), self.list.data_ptr(),
+                                   self.list_cap, self.ctl.data_ptr(), self.expand.data_ptr(), self.expand_cap,
+                                   self.path.data_ptr(), self.path_cap, self.out_i.data_ptr(),
+                                   self.out_cost.data_ptr(), self.out_i.data_ptr() + 4, dg.stream())
+            _lib.check(rc, "pmp_lpa_star")
+        else:
+            rc = dg.L.pmp_d_star(dg.handle, op, self.sg.data_ptr(), self.a.data_ptr(), self.b.data_ptr(),
+                                 self.parent.data_ptr(), self.tag.data_ptr(), self.list.data_ptr(), self.list_cap,
+                                 self.ctl.data_ptr(), self.expand.data_ptr(), self.expand_cap, self.path.data_ptr(),
+                                 self.path_cap, self.out_i.data_ptr(), self.out_cost.data_ptr(),
+                                 self.out_i.data_ptr() + 4, dg.stream())
+            _lib.check(rc, "pmp_d_star")
+        oi = self.out_i.cpu().numpy()
+        plen, nexp = int(oi[0]), int(oi[1])
+        if plen == -2:
+            raise _lib.PmpError("reference-order LPA*/D*: a list capacity was exceeded; use reference_order=False")
+        if plen == -1:
+            raise _lib.PmpError("reference-order LPA*/D*: path longer than the path buffer")
+        cost = float(self.out_cost.cpu()[0])
+        cells = self.path[:plen].cpu().numpy()
+        exp = self.expand[:nexp].cpu().numpy()
+        return cost, cells, exp
+
+    def edit(self, coords, value):
+        """set the occupancy of the listed cells on the device bitmask (pmp_grid_edit_cells)"""
+        dg = self.dg
+        t = dg.torch
+        c3 = np.zeros((len(coords), 3), dtype=np.int32)
+        c3[:, :dg.ndim] = np.asarray(coords, dtype=np.int32).reshape(-1, dg.ndim)
+        dev = t.from_numpy(c3).to(dg.device)
+        _lib.check(dg.L.pmp_grid_edit_cells(dg.handle, dev.data_ptr(), len(coords), 1 if value else 0, dg.stream()),
+                   "pmp_grid_edit_cells")
+        t.cuda.current_stream().synchronize()
+
+
 class _ReplanMixin:
     """plan() / apply_change() on top of a ReplanSession; shared by the 2D and 3D classes."""
     _algo = _lib.ASTAR
     _scratch_cells = 1 << 20
+
+    _ref_kind = 0          # reference-order mode: 0 = the LPA* containers, 1 = D*'s
 
     def _init_replan(self):
         self._session = None
         self._result = None
         self.EXPAND = []
         self.info = None
+        self._ref = None       # ReferenceIncrSession (reference_order=True)
+
+    # ---- reference-order mode (pmp_lpa_star / pmp_d_star): the reference's own processing order ----
+    def _ref_result(self, cost, cells, exp):
+        dg = self._ref.dg
+        pts = engine.cells_to_points(cells, dg)
+        if self._ref_kind == 0:
+            pts.reverse()                                  # start -> goal (lpa_star.py:229, lpa_star3d.py:224)
+        coords = engine.cells_to_coords(exp, dg)
+        t = dg.torch
+        vals = self._ref.a[t.from_numpy(exp.astype(np.int64) & 0xFFFFFFFF).to(dg.device)].cpu().numpy() if len(exp) else np.zeros(0)
+        self.EXPAND = ExpandView(self._node_cls, coords, vals, np.zeros(len(coords)), coords)
+        expand = self.EXPAND if self._ndim == 3 else None  # the 2D classes return None (lpa_star.py:89, d_star.py:88)
+        return cost, pts, expand
+
+    def _ref_plan(self):
+        if self._ref is None:
+            dg = self._prepare()
+            self._ref = ReferenceIncrSession(dg, self._ref_kind, self._heuristic_id(), self.start.current,
+                                             self.goal.current)
+            self._result = self._ref_result(*self._ref.step(0))
+        return self._result
+
+    def _ref_changes(self, coords, flags):
+        self._ref_plan()
+        if self._ref_kind == 0:                            # LPA*: one updateVertex round + plan() per cell
+            for c, b in zip(coords, flags):
+                was = c in self.obstacles
+                self._edit_host_map([c], [b])
+                self._ref.edit([c], b)
+                self._result = self._ref_result(*self._ref.step(1, (c, was and not b)))
+        else:                                              # D*: obstacles are only ever added
+            add = [c for c, b in zip(coords, flags) if b]
+            if len(add) != len(coords):
+                raise _lib.PmpError("reference-order D* only adds obstacles (d_star.py:102-127, d_star3d.py:115-151)")
+            self._edit_host_map(add, [True] * len(add))
+            self._ref.edit(add, True)
+            self._result = self._ref_result(*self._ref.step(1))
+        return self._result
 
     # ---- reference API ----
     def plan(self) -> tuple:
         """lpa_star.py:78-89 / lpa_star3d.py:88-92: (cost, path start -> goal, expand)."""
+        if self.reference_order:
+            return self._ref_plan()
         if self._session is None:
             dg = self._prepare()
             self._session = ReplanSession(dg, self._algo, self._heuristic_id(), scratch_cells=self._scratch_cells)
@@ -118,6 +245,8 @@ class _ReplanMixin:
         """several cells at once: one upload, one invalidation, one resumed search"""
         coords = [tuple(int(v) for v in c) for c in coords]
         flags = [bool(b) for b in (blocked if hasattr(blocked, "__len__") else [blocked] * len(coords))]
+        if self.reference_order:
+            return self._ref_changes(coords, flags)
         if self._session is None:
             self.plan()
         self._edit_host_map(coords, flags)
@@ -190,8 +319,9 @@ class LPAStar(_ReplanMixin, GraphSearcher):
     """lpa_star.py:38-230"""
     _node_cls = Node
 
-    def __init__(self, start: tuple, goal: tuple, env, heuristic_type: str = "euclidean") -> None:
-        GraphSearcher.__init__(self, start, goal, env, heuristic_type)
+    def __init__(self, start: tuple, goal: tuple, env, heuristic_type: str = "euclidean", *,
+                 reference_order: bool = None) -> None:
+        GraphSearcher.__init__(self, start, goal, env, heuristic_type, reference_order=reference_order)
         self._init_replan()
 
     def __str__(self) -> str:
@@ -206,8 +336,9 @@ class LPAStar3D(_ReplanMixin, GraphSearcher3D):
     """lpa_star3d.py:46-225"""
     _node_cls = Node3D
 
-    def __init__(self, start: tuple, goal: tuple, env, heuristic_type: str = "euclidean") -> None:
-        GraphSearcher3D.__init__(self, start, goal, env, heuristic_type)
+    def __init__(self, start: tuple, goal: tuple, env, heuristic_type: str = "euclidean", *,
+                 reference_order: bool = None) -> None:
+        GraphSearcher3D.__init__(self, start, goal, env, heuristic_type, reference_order=reference_order)
         self._init_replan()
 
     def __str__(self) -> str:
@@ -224,6 +355,9 @@ class DStarLite(LPAStar):
     """d_star_lite.py:14-187: same (g, rhs) repair as LPA*, searched from the goal; plan() and
     the toggling OnPress have the LPA* signatures, the path is start -> goal"""
 
+    def __init__(self, start: tuple, goal: tuple, env, heuristic_type: str = "euclidean") -> None:
+        super().__init__(start, goal, env, heuristic_type, reference_order=False)   # no reference-order kernel for D* Lite
+
     def __str__(self) -> str:
         return "D* Lite"
 
@@ -233,8 +367,10 @@ class DStar(_ReplanMixin, GraphSearcher):
     (d_star.py:102-134) and repairs"""
     _node_cls = Node
 
-    def __init__(self, start: tuple, goal: tuple, env) -> None:
-        GraphSearcher.__init__(self, start, goal, env, None)
+    _ref_kind = 1
+
+    def __init__(self, start: tuple, goal: tuple, env, *, reference_order: bool = None) -> None:
+        GraphSearcher.__init__(self, start, goal, env, None, reference_order=reference_order)
         self._init_replan()
 
     def __str__(self) -> str:
@@ -258,8 +394,10 @@ class DStar3D(_ReplanMixin, GraphSearcher3D):
     apply_dynamic_obstacles(newly_blocked) -> (cost, path) (d_star3d.py:115-151)"""
     _node_cls = Node3D
 
-    def __init__(self, start: tuple, goal: tuple, env) -> None:
-        GraphSearcher3D.__init__(self, start, goal, env, None)
+    _ref_kind = 1
+
+    def __init__(self, start: tuple, goal: tuple, env, *, reference_order: bool = None) -> None:
+        GraphSearcher3D.__init__(self, start, goal, env, None, reference_order=reference_order)
         self._init_replan()
 
     def __str__(self) -> str:

@@ -144,3 +144,103 @@ extern "C" int bf_host_plan(int ndim, const int32_t *dims, const uint8_t *occ, i
     }
     return 0;
 }
+
+// ---- LPA* / D* sessions (csrc/pmp_incr_core.h).  The occupancy array is referenced, not copied:
+// the test edits it between calls like the planners edit env.obstacles. ----
+#include "../python_motion_planning_b200/csrc/pmp_incr_core.h"
+
+struct IncrHost {
+    HostEnv env;
+    int kind; // 0 LPA*, 1 D*
+    std::vector<double> a, b, key;
+    std::vector<uint32_t> parent, list, expand;
+    std::vector<uint8_t> tag;
+    LpaState L;
+    DsState D;
+    int64_t cells;
+};
+
+static void host_geometry(BfState &S, const HostEnv &env, int heuristic, const int32_t *start, const int32_t *goal) {
+    memset(&S, 0, sizeof S);
+    S.heuristic = heuristic;
+    S.PX = env.dims[0]; S.PY = env.dims[1];
+    S.gx = goal[0]; S.gy = goal[1]; S.gz = env.ndim == 3 ? goal[2] : 0;
+    S.start_cell = bf_cell(S, start[0], start[1], env.ndim == 3 ? start[2] : 0);
+    S.goal_cell = bf_cell(S, S.gx, S.gy, S.gz);
+}
+
+extern "C" void *incr_host_create(int kind, int ndim, const int32_t *dims, const uint8_t *occ, int n_motions,
+                                  const int32_t *motions, int heuristic, const int32_t *start,
+                                  const int32_t *goal) {
+    IncrHost *H = new IncrHost();
+    H->kind = kind;
+    H->env.ndim = ndim;
+    H->env.dims[0] = dims[0]; H->env.dims[1] = dims[1]; H->env.dims[2] = ndim == 3 ? dims[2] : 1;
+    H->env.occ = occ; H->env.nk = n_motions; H->env.mot = motions; H->env.los_fn = nullptr;
+    const int64_t cells = H->cells = (int64_t)H->env.dims[0] * H->env.dims[1] * H->env.dims[2];
+    H->a.assign(cells, INFINITY); H->b.assign(cells, INFINITY); H->key.assign(2 * cells, 0.0);
+    H->parent.assign(cells, BF_NONE); H->tag.assign(cells, DS_NEW);
+    H->list.assign(8 * cells + 64, 0); H->expand.assign(64 * cells + 64, 0);
+    if (kind == 0) {
+        LpaState &L = H->L;
+        L.g = H->a.data(); L.rhs = H->b.data(); L.k1 = H->key.data(); L.k2 = H->key.data() + cells;
+        L.U = H->list.data(); L.ucap = (int64_t)H->list.size(); L.un = 0;
+        L.expand = H->expand.data(); L.expand_cap = (int64_t)H->expand.size(); L.n_expand = 0;
+        L.family = ndim; L.status = BF_RUNNING;
+        host_geometry(L.S, H->env, heuristic, start, goal);
+    } else {
+        DsState &D = H->D;
+        D.h = H->a.data(); D.k = H->b.data(); D.parent = H->parent.data(); D.t = H->tag.data();
+        D.OPEN = H->list.data(); D.ocap = (int64_t)H->list.size(); D.on = 0;
+        D.expand = H->expand.data(); D.expand_cap = (int64_t)H->expand.size(); D.n_expand = 0;
+        D.family = ndim; D.status = BF_RUNNING;
+        host_geometry(D.S, H->env, 0, start, goal);
+    }
+    return H;
+}
+
+extern "C" void incr_host_destroy(void *h) { delete (IncrHost *)h; }
+
+// op 0: plan from scratch; op 1: after an occupancy edit (LPA*: change = {x, y, z, freed}).
+// path_out: coordinates in the order the core wrote them (LPA* goal first, D* start first).
+extern "C" int incr_host_step(void *h, int op, const int32_t *change, double *cost_out, int32_t *path_out,
+                              int64_t path_cap, int64_t *path_len, int64_t *expand_cell, int64_t expand_cap,
+                              int64_t *n_expand) {
+    IncrHost *H = (IncrHost *)h;
+    std::vector<uint32_t> cellsv((size_t)path_cap);
+    int32_t n = 0;
+    const BfState *S;
+    int status;
+    if (H->kind == 0) {
+        LpaState &L = H->L;
+        if (op == 0) lpa_init(L);
+        else lpa_apply_change(L, H->env, change[0], change[1], H->env.ndim == 3 ? change[2] : 0, change[3] != 0);
+        lpa_compute(L, H->env);
+        status = L.status;
+        if (status != BF_OVERFLOW) lpa_extract(L, H->env, cellsv.data(), path_cap, &n, cost_out);
+        *n_expand = L.n_expand;
+        for (int64_t i = 0; i < L.n_expand && i < expand_cap; ++i) expand_cell[i] = L.expand[i];
+        S = &L.S;
+    } else {
+        DsState &D = H->D;
+        if (op == 0) {
+            ds_init(D);
+            ds_plan(D, H->env);
+            if (D.status != BF_OVERFLOW) ds_extract(D, H->env, cellsv.data(), path_cap, &n, cost_out);
+        } else {
+            ds_replan(D, H->env, cellsv.data(), path_cap, &n, cost_out);
+        }
+        status = D.status;
+        *n_expand = D.n_expand;
+        for (int64_t i = 0; i < D.n_expand && i < expand_cap; ++i) expand_cell[i] = D.expand[i];
+        S = &D.S;
+    }
+    if (status == BF_OVERFLOW || n < 0) return -2;
+    for (int32_t i = 0; i < n; ++i) {
+        int x, y, z;
+        bf_coords(*S, cellsv[i], x, y, z);
+        path_out[3 * i] = x; path_out[3 * i + 1] = y; path_out[3 * i + 2] = z;
+    }
+    *path_len = n;
+    return 0;
+}

@@ -28,7 +28,8 @@ THETA, LAZY = 3, 4
 
 @pytest.fixture(scope="module")
 def host():
-    newest = max(os.path.getmtime(f) for f in (SRC, CORE, os.path.join(os.path.dirname(CORE), "pmp_jps_core.h")))
+    newest = max(os.path.getmtime(f) for f in (SRC, CORE, os.path.join(os.path.dirname(CORE), "pmp_jps_core.h"),
+                                             os.path.join(os.path.dirname(CORE), "pmp_incr_core.h")))
     if not os.path.exists(SO) or os.path.getmtime(SO) < newest:
         subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-Wall", "-shared", "-o", SO, SRC], check=True)
     L = ctypes.CDLL(SO)

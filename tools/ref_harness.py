@@ -63,6 +63,9 @@ class BoxMap:
     def __contains__(self, p):
         return 0 <= p[0] < self.r[0] and 0 <= p[1] < self.r[1] and 0 <= p[2] < self.r[2]
 
+    def __iter__(self):   # LPAStar3D / DStar3D build their node map from it (lpa_star3d.py:68, d_star3d.py:87)
+        return ((x, y, z) for x in range(self.r[0]) for y in range(self.r[1]) for z in range(self.r[2]))
+
 
 def fast_grid_map(pmp):
     """Patch Grid3D.grid_map in THIS process with the O(1) membership object."""
