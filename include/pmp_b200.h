@@ -215,6 +215,11 @@ int pmp_bestfirst(const pmp_grid *g, int algo, int heuristic, int64_t nq,
  *      reference's own grid sizes.  All state lives in caller-owned device arrays that must be kept
  *      between calls: per padded cell g, rhs, key[2] (LPA*) or h, k, parent, tag (D*), the list
  *      (list_cap cells) and ctl_dev (4 x int64: [0] list length, [1] status).
+ *   variant (pmp_lpa_star): 0 = LPA*, 1 = D* Lite (DStarLite, d_star_lite.py:34-187, 2D grids: LPA* run
+ *         from the goal with keys shifted by km; ctl_dev[2] keeps km).  With variant 1, op 1 is
+ *         DStarLite.OnPress: the greedy walk from the start that toggles cell change_dev = {x, y, z, -}
+ *         ITSELF after its first step (the kernel flips the bit of the handle's bitmask; the caller
+ *         must not edit it beforehand) and repairs; path_dev then holds the walked cells, start first.
  *   op 0: initialise the state and plan.  start_goal_dev: 2 x 3 int32.
  *   op 1: LPA*: change_dev = {x, y, z, freed}: the occupancy of that cell was just edited
  *         (pmp_grid_edit_cells; freed = 1 if an obstacle was removed) -> updateVertex of the cell /
@@ -224,7 +229,7 @@ int pmp_bestfirst(const pmp_grid *g, int algo, int heuristic, int64_t nq,
  *   start first (the 2D D* walk of op 1 leaves the goal out, d_star.py:117-127); path_len_dev 0 = no
  *   path, -2 = a capacity was exceeded; cost_dev as the reference sums it (inf when a D* back
  *   pointer's reverse edge is illegal under the directed corner rule). */
-int pmp_lpa_star(const pmp_grid *g, int op, int heuristic, const int32_t *start_goal_dev,
+int pmp_lpa_star(const pmp_grid *g, int variant, int op, int heuristic, const int32_t *start_goal_dev,
                  const int32_t *change_dev, double *g_dev, double *rhs_dev, double *key_dev,
                  uint32_t *list_dev, int64_t list_cap, int64_t *ctl_dev, uint32_t *expand_dev,
                  int64_t expand_cap, uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,

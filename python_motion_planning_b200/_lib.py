@@ -95,7 +95,7 @@ def lib():
         "pmp_verify_field": [vp, i32, vp, vp, i32, i32, vp, vp],
         "pmp_gbfs": [vp, i32, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp, vp],
         "pmp_bestfirst": [vp, i32, i32, i64, vp, vp, vp, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp, vp],
-        "pmp_lpa_star": [vp, i32, i32, vp, vp, vp, vp, vp, vp, i64, vp, vp, i64, vp, i64, vp, vp, vp, vp],
+        "pmp_lpa_star": [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, i64, vp, vp, i64, vp, i64, vp, vp, vp, vp],
         "pmp_d_star": [vp, i32, vp, vp, vp, vp, vp, vp, i64, vp, vp, i64, vp, i64, vp, vp, vp, vp],
         "pmp_slab_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, i64, vp],
         "pmp_slab_run": [vp, ctypes.POINTER(SsspParams), vp, vp, i64, dbl, vp, vp],

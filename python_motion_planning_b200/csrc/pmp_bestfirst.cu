@@ -182,6 +182,41 @@ extern "C" int pmp_bestfirst(const pmp_grid *g, int algo, int heuristic, int64_t
 // LPA* / D* in the reference's processing order (pmp_incr_core.h).  Sequential algorithms on Python
 // lists: thread 0 of one CTA runs them, the CTA's other threads only initialise the per-cell state.
 // ---------------------------------------------------------------------------------------------
+// Environment of the incremental planners: plain (volatile) loads of the bitmask instead of the
+// read-only path of cell_blocked(), because DStarLite.OnPress edits the obstacle set in the middle of
+// its walk (d_star_lite.py:82-90) -- toggle() flips the bit from inside the kernel.
+struct IncrEnvDev {
+    const GridDev &G;
+    const Motions &M;
+    __device__ bool inbox(int x, int y, int z) const {
+        return x >= 0 && y >= 0 && z >= 0 && x < G.X && y < G.Y && z < G.Z;
+    }
+    __device__ bool blocked(int x, int y, int z) const {
+        if (x < 0 || y < 0 || z < 0 || x >= G.PX || y >= G.PY || z >= G.PZ) return true;
+        const volatile u32 *w = G.bits + ((size_t)z * G.PY + y) * G.wpr + (x >> 5);
+        return (*w >> (x & 31)) & 1u;
+    }
+    __device__ bool obst(int x, int y, int z) const { return inbox(x, y, z) && blocked(x, y, z); }
+    __device__ bool legal_dir(int dx, int dy, int dz, int x, int y, int z) const {
+        if (blocked(x, y, z) || blocked(x + dx, y + dy, z + dz)) return false;
+        if ((dx != 0) + (dy != 0) + (dz != 0) >= 2) {
+            if (dx && blocked(x + dx, y, z)) return false;
+            if (dy && blocked(x, y + dy, z)) return false;
+            if (dz && blocked(x, y, z + dz)) return false;
+        }
+        return true;
+    }
+    __device__ bool toggle(int x, int y, int z) const { // true: an obstacle was removed
+        u32 *w = const_cast<u32 *>(G.bits) + ((size_t)z * G.PY + y) * G.wpr + (x >> 5);
+        const u32 old = atomicXor(w, 1u << (x & 31));
+        __threadfence();
+        return (old >> (x & 31)) & 1u;
+    }
+    __device__ int k() const { return M.k; }
+    __device__ void offset(int m, int &dx, int &dy, int &dz) const { dx = M.dx[m]; dy = M.dy[m]; dz = M.dz[m]; }
+    __device__ double len(int m) const { return M.len[m]; }
+};
+
 __device__ static void incr_geometry(BfState &S, const GridDev &G, int heuristic, const int32_t *sg) {
     S.heap = nullptr; S.hn = 0; S.heap_cap = 0;
     S.cg = S.ch = nullptr; S.cpar = nullptr; S.order = nullptr; S.n_order = 0; S.order_cap = 0;
@@ -199,7 +234,7 @@ __device__ static bool incr_query_ok(const GridDev &G, const int32_t *sg) {
            sg[3] >= 0 && sg[4] >= 0 && gz >= 0 && sg[3] < G.X && sg[4] < G.Y && gz < G.Z;
 }
 
-__global__ void k_lpa_star(const GridDev G, const __grid_constant__ Motions M, int op, int heuristic,
+__global__ void k_lpa_star(const GridDev G, const __grid_constant__ Motions M, int variant, int op, int heuristic,
                            const int32_t *sg, const int32_t *change, double *g, double *rhs, double *key,
                            u32 *list, int64_t list_cap, int64_t *ctl, u32 *expand, int64_t expand_cap,
                            u32 *path, int64_t cap, int32_t *plen, double *cost, int32_t *n_expand) {
@@ -216,16 +251,29 @@ __global__ void k_lpa_star(const GridDev G, const __grid_constant__ Motions M, i
     L.expand = expand; L.expand_cap = expand_cap; L.n_expand = 0;
     L.family = G.ndim;
     L.status = BF_RUNNING;
+    L.dlite = variant == 1;
+    L.km = op == 0 ? 0.0 : __longlong_as_double(ctl[2]);
     incr_geometry(L.S, G, heuristic, sg);
-    const BfEnvDev env = {G, M};
-    if (op == 0) lpa_init(L);
-    else lpa_apply_change(L, env, change[0], change[1], G.ndim == 3 ? change[2] : 0, change[3] != 0);
-    lpa_compute(L, env);
+    IncrEnvDev env = {G, M};
+    if (L.dlite) {
+        if (op == 0) {
+            lpa_init(L);
+            lpa_compute(L, env);
+            if (L.status != BF_OVERFLOW) dlite_extract(L, env, path, cap, plen, cost);
+        } else {
+            dlite_press(L, env, change[0], change[1], G.ndim == 3 ? change[2] : 0, path, cap, plen, cost);
+        }
+    } else {
+        if (op == 0) lpa_init(L);
+        else lpa_apply_change(L, env, change[0], change[1], G.ndim == 3 ? change[2] : 0, change[3] != 0);
+        lpa_compute(L, env);
+        if (L.status != BF_OVERFLOW) lpa_extract(L, env, path, cap, plen, cost);
+    }
     ctl[0] = L.un;
     ctl[1] = L.status;
+    ctl[2] = __double_as_longlong(L.km);
     *n_expand = (int32_t)L.n_expand;
-    if (L.status == BF_OVERFLOW) { *plen = -2; *cost = INF_D; return; }
-    lpa_extract(L, env, path, cap, plen, cost);
+    if (L.status == BF_OVERFLOW) { *plen = -2; *cost = INF_D; }
 }
 
 __global__ void k_d_star(const GridDev G, const __grid_constant__ Motions M, int op, const int32_t *sg,
@@ -248,7 +296,7 @@ __global__ void k_d_star(const GridDev G, const __grid_constant__ Motions M, int
     D.family = G.ndim;
     D.status = BF_RUNNING;
     incr_geometry(D.S, G, PMP_H_EUCLIDEAN, sg);
-    const BfEnvDev env = {G, M};
+    const IncrEnvDev env = {G, M};
     if (op == 0) {
         ds_init(D);
         ds_plan(D, env);
@@ -262,19 +310,20 @@ __global__ void k_d_star(const GridDev G, const __grid_constant__ Motions M, int
     if (D.status == BF_OVERFLOW) { *plen = -2; *cost = INF_D; }
 }
 
-extern "C" int pmp_lpa_star(const pmp_grid *g, int op, int heuristic, const int32_t *start_goal_dev,
+extern "C" int pmp_lpa_star(const pmp_grid *g, int variant, int op, int heuristic, const int32_t *start_goal_dev,
                             const int32_t *change_dev, double *g_dev, double *rhs_dev, double *key_dev,
                             uint32_t *list_dev, int64_t list_cap, int64_t *ctl_dev, uint32_t *expand_dev,
                             int64_t expand_cap, uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
                             double *cost_dev, int32_t *n_expand_dev, void *stream) {
-    if (!g || (op != 0 && op != 1) || !start_goal_dev || (op == 1 && !change_dev) || !g_dev || !rhs_dev ||
+    if (!g || (variant != 0 && variant != 1) || (op != 0 && op != 1) || !start_goal_dev || (op == 1 && !change_dev) || !g_dev || !rhs_dev ||
         !key_dev || !list_dev || list_cap < 1 || !ctl_dev || !expand_dev || expand_cap < 1 || !path_dev ||
         path_cap < 1 || !path_len_dev || !cost_dev || !n_expand_dev) {
         pmp_set_error("pmp_lpa_star: bad arguments");
         return -1;
     }
     if (g->d.pcells >= 0xFFFFFFFFull) { pmp_set_error("pmp_lpa_star: grid too large for 32-bit cell indices"); return -1; }
-    k_lpa_star<<<1, 256, 0, (cudaStream_t)stream>>>(g->d, g->mot, op, heuristic, start_goal_dev, change_dev, g_dev,
+    if (variant == 1 && g->d.ndim != 2) { pmp_set_error("pmp_lpa_star: D* Lite is a 2D planner (d_star_lite.py)"); return -1; }
+    k_lpa_star<<<1, 256, 0, (cudaStream_t)stream>>>(g->d, g->mot, variant, op, heuristic, start_goal_dev, change_dev, g_dev,
                                                     rhs_dev, key_dev, list_dev, list_cap, ctl_dev, expand_dev,
                                                     expand_cap, path_dev, path_cap, path_len_dev, cost_dev,
                                                     n_expand_dev);

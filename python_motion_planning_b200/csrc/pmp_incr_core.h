@@ -3,6 +3,7 @@
 //
 //   LPA*   LPAStar      global_planner/graph_search/lpa_star.py:62-230
 //          LPAStar3D    lpa_star3d.py:57-225
+//   D* Lite DStarLite   d_star_lite.py:34-187 (LPA* searched from the goal, keys shifted by km)
 //   D*     DStar        d_star.py:60-291
 //          DStar3D      d_star3d.py:68-280
 //
@@ -33,18 +34,26 @@ struct LpaState {
     BfState S;                 // geometry, heuristic, start / goal (heap / CLOSED members unused)
     int family;                // 2: LPAStar, 3: LPAStar3D
     int status;                // BF_RUNNING while searching; BF_REACHED / BF_EXHAUSTED / BF_OVERFLOW
+    int dlite;                 // 1: DStarLite -- rhs = 0 at the goal, keys measured to the start, + km
+    double km;
 };
+
+// the node whose rhs is pinned to 0 / the node the search runs towards
+BF_HD static inline uint32_t lpa_anchor(const LpaState &L) { return L.dlite ? L.S.goal_cell : L.S.start_cell; }
+BF_HD static inline uint32_t lpa_target(const LpaState &L) { return L.dlite ? L.S.start_cell : L.S.goal_cell; }
 
 BF_HD static inline bool lpa_key_lt(double a1, double a2, double b1, double b2) { // list < list
     return a1 < b1 || (a1 == b1 && a2 < b2);
 }
 
-// calculateKey, lpa_star.py:181-192 / lpa_star3d.py:172-175
+// calculateKey, lpa_star.py:181-192 / lpa_star3d.py:172-175 / d_star_lite.py:155-166
 BF_HD static inline void lpa_calc_key(const LpaState &L, uint32_t c, double &k1, double &k2) {
-    int x, y, z;
+    int x, y, z, tx, ty, tz;
     bf_coords(L.S, c, x, y, z);
+    bf_coords(L.S, lpa_target(L), tx, ty, tz);
     const double m = L.g[c] < L.rhs[c] ? L.g[c] : L.rhs[c]; // min(node.g, node.rhs)
-    k1 = m + bf_h(L.S.heuristic, L.S.gx - x, L.S.gy - y, L.S.gz - z);
+    k1 = m + bf_h(L.S.heuristic, tx - x, ty - y, tz - z);
+    if (L.dlite) k1 = k1 + L.km;
     k2 = m;
 }
 
@@ -76,7 +85,7 @@ BF_HD static inline void lpa_heappush(LpaState &L, uint32_t c) {
 // updateVertex, lpa_star.py:159-179 / lpa_star3d.py:156-170
 template <class ENV>
 BF_HD static inline void lpa_update_vertex(LpaState &L, const ENV &env, uint32_t c) {
-    if (c != L.S.start_cell) {
+    if (c != lpa_anchor(L)) {
         int x, y, z;
         bf_coords(L.S, c, x, y, z);
         double best = INFINITY; // the 2D class raises on an empty neighbour list; 3D: inf
@@ -105,9 +114,11 @@ BF_HD static inline void lpa_init(LpaState &L) {
     L.un = 0;
     L.n_expand = 0;
     L.status = BF_RUNNING;
-    L.rhs[L.S.start_cell] = 0.0;
-    lpa_calc_key(L, L.S.start_cell, L.k1[L.S.start_cell], L.k2[L.S.start_cell]);
-    lpa_heappush(L, L.S.start_cell);
+    L.km = 0.0;
+    const uint32_t a = lpa_anchor(L);                       // d_star_lite.py:34-52: the goal
+    L.rhs[a] = 0.0;
+    lpa_calc_key(L, a, L.k1[a], L.k2[a]);
+    lpa_heappush(L, a);
 }
 
 // the part of apply_change / OnPress after the obstacle set was edited (lpa_star3d.py:104-130,
@@ -127,10 +138,10 @@ BF_HD static inline void lpa_apply_change(LpaState &L, const ENV &env, int x, in
     }
 }
 
-// computeShortestPath, lpa_star.py:135-157 / lpa_star3d.py:137-154
+// computeShortestPath, lpa_star.py:135-157 / lpa_star3d.py:137-154 / d_star_lite.py:104-131
 template <class ENV>
 BF_HD static inline void lpa_compute(LpaState &L, const ENV &env) {
-    const uint32_t goal = L.S.goal_cell;
+    const uint32_t goal = lpa_target(L);
     while (L.status == BF_RUNNING) {
         if (L.un == 0) { L.status = BF_EXHAUSTED; return; } // 3D: loop ends; 2D: min([]) raises
         int64_t bi = 0; // min(self.U, key=...): the first minimum in list order
@@ -145,6 +156,15 @@ BF_HD static inline void lpa_compute(LpaState &L, const ENV &env) {
         lpa_remove_at(L, bi);
         if (L.n_expand >= L.expand_cap) { L.status = BF_OVERFLOW; return; }
         L.expand[L.n_expand++] = c;
+        if (L.dlite) { // "affected by obstacles": the stored key is out of date (d_star_lite.py:116-118)
+            double n1, n2;
+            lpa_calc_key(L, c, n1, n2);
+            if (lpa_key_lt(L.k1[c], L.k2[c], n1, n2)) {
+                L.k1[c] = n1; L.k2[c] = n2;
+                lpa_heappush(L, c);
+                continue;
+            }
+        }
         if (L.g[c] > L.rhs[c]) L.g[c] = L.rhs[c];
         else { L.g[c] = INFINITY; lpa_update_vertex(L, env, c); }
         int x, y, z;
@@ -195,6 +215,87 @@ BF_HD static inline void lpa_extract(const LpaState &L, const ENV &env, uint32_t
             if (n < cap) path[n] = c;
             ++n;
             if (++count >= 100000) { *plen = 0; *cost = total; return; }
+        }
+    }
+    *plen = n <= cap ? (int32_t)n : -1;
+    *cost = total;
+}
+
+// one greedy step of the extraction walks: the free, collision-free neighbour with the smallest g
+// (first in motion order on ties); false when there is none
+template <class ENV>
+BF_HD static inline bool lpa_greedy_step(const LpaState &L, const ENV &env, uint32_t c, uint32_t &next, double &w) {
+    int x, y, z;
+    bf_coords(L.S, c, x, y, z);
+    bool any = false;
+    double bg = 0.0;
+    for (int m = 0; m < env.k(); ++m) {
+        int dx, dy, dz;
+        env.offset(m, dx, dy, dz);
+        const int nx = x + dx, ny = y + dy, nz = z + dz;
+        if (!env.inbox(nx, ny, nz) || env.obst(nx, ny, nz)) continue;
+        if (!env.legal_dir(dx, dy, dz, x, y, z)) continue;
+        const uint32_t nc = bf_cell(L.S, nx, ny, nz);
+        if (!any || L.g[nc] < bg) { any = true; bg = L.g[nc]; next = nc; w = env.len(m); }
+    }
+    return any;
+}
+
+// DStarLite.extractPath, d_star_lite.py:168-187: greedy descent from the start; cells start first
+template <class ENV>
+BF_HD static inline void dlite_extract(const LpaState &L, const ENV &env, uint32_t *path, int64_t cap,
+                                       int32_t *plen, double *cost) {
+    uint32_t c = L.S.start_cell, nc = 0;
+    int64_t n = 0, count = 0;
+    double total = 0.0, w = 0.0;
+    if (n < cap) path[n] = c;
+    ++n;
+    while (c != L.S.goal_cell) {
+        if (!lpa_greedy_step(L, env, c, nc, w)) { *plen = 0; *cost = total; return; }
+        if (n < cap) path[n] = nc;
+        ++n;
+        total += w;
+        c = nc;
+        if (++count == 1000) { *plen = 0; *cost = total; return; }
+    }
+    *plen = n <= cap ? (int32_t)n : -1;
+    *cost = total;
+}
+
+// DStarLite.OnPress, d_star_lite.py:55-102: walk greedily from the start; after the first step the
+// clicked cell is toggled (env.toggle returns true when an obstacle was removed), km takes the
+// heuristic between the new and the old position, the vertices around the change are updated and
+// the field repaired; the walk then continues on the repaired field.  Cells start first.
+template <class ENV>
+BF_HD static inline void dlite_press(LpaState &L, ENV &env, int px, int py, int pz, uint32_t *path, int64_t cap,
+                                     int32_t *plen, double *cost) {
+    L.n_expand = 0;
+    L.status = BF_RUNNING;
+    uint32_t c = L.S.start_cell, nc = 0;
+    int64_t n = 0, count = 0;
+    double total = 0.0, w = 0.0;
+    bool update_start = true;
+    if (n < cap) path[n] = c;
+    ++n;
+    while (c != L.S.goal_cell) {
+        if (!lpa_greedy_step(L, env, c, nc, w)) { *plen = 0; *cost = total; return; } // min([]) raises in the reference
+        if (n < cap) path[n] = nc;
+        ++n;
+        total += w;
+        c = nc;
+        if (++count >= 100000) { *plen = 0; *cost = total; return; }                  // the reference has no guard
+        if (update_start) {
+            update_start = false;
+            int x, y, z, sx, sy, sz;
+            bf_coords(L.S, c, x, y, z);
+            bf_coords(L.S, L.S.start_cell, sx, sy, sz);
+            L.km = bf_h(L.S.heuristic, sx - x, sy - y, sz - z);
+            const bool freed = env.toggle(px, py, pz);
+            const int ne = (int)L.n_expand;
+            lpa_apply_change(L, env, px, py, pz, freed);
+            L.n_expand = ne;                               // EXPAND was cleared once, at the top
+            lpa_compute(L, env);
+            if (L.status != BF_RUNNING) { *plen = 0; *cost = total; return; }
         }
     }
     *plen = n <= cap ? (int32_t)n : -1;

@@ -95,10 +95,11 @@ class ReferenceIncrSession:
     apply_change / apply_dynamic_obstacles continue where plan() stopped, as the reference's planner
     objects do (csrc/pmp_incr_core.h)."""
 
-    def __init__(self, dg, kind, heuristic, start, goal):
+    def __init__(self, dg, kind, heuristic, start, goal, variant=0):
         t = dg.torch
         n = dg.pcells
-        self.dg, self.kind, self.heuristic = dg, kind, heuristic      # kind 0: LPA*, 1: D*
+        self.dg, self.kind, self.heuristic = dg, kind, heuristic      # kind 0: LPA* (variant 1: D* Lite), 1: D*
+        self.variant = variant
         dev = dg.device
         self.a = t.empty(n, dtype=t.float64, device=dev)               # g   | h
         self.b = t.empty(n, dtype=t.float64, device=dev)               # rhs | k
@@ -131,7 +132,7 @@ class ReferenceIncrSession:
             c[3] = 1 if change[1] else 0
             self.change.copy_(t.from_numpy(c))
         if self.kind == 0:
-            rc = dg.L.pmp_lpa_star(dg.handle, op, self.heuristic, self.sg.data_ptr(), self.change.data_ptr(),
+            rc = dg.L.pmp_lpa_star(dg.handle, self.variant, op, self.heuristic, self.sg.data_ptr(), self.change.data_ptr(),
                                    self.a.data_ptr(), self.b.data_ptr(), self.key.data_ptr(), self.list.data_ptr(),
                                    self.list_cap, self.ctl.data_ptr(), self.expand.data_ptr(), self.expand_cap,
                                    self.path.data_ptr(), self.path_cap, self.out_i.data_ptr(),
@@ -173,6 +174,7 @@ class _ReplanMixin:
     _scratch_cells = 1 << 20
 
     _ref_kind = 0          # reference-order mode: 0 = the LPA* containers, 1 = D*'s
+    _ref_variant = 0       # 1: D* Lite (LPA* from the goal)
 
     def _init_replan(self):
         self._session = None
@@ -185,7 +187,7 @@ class _ReplanMixin:
     def _ref_result(self, cost, cells, exp):
         dg = self._ref.dg
         pts = engine.cells_to_points(cells, dg)
-        if self._ref_kind == 0:
+        if self._ref_kind == 0 and self._ref_variant == 0:
             pts.reverse()                                  # start -> goal (lpa_star.py:229, lpa_star3d.py:224)
         coords = engine.cells_to_coords(exp, dg)
         t = dg.torch
@@ -198,13 +200,19 @@ class _ReplanMixin:
         if self._ref is None:
             dg = self._prepare()
             self._ref = ReferenceIncrSession(dg, self._ref_kind, self._heuristic_id(), self.start.current,
-                                             self.goal.current)
+                                             self.goal.current, self._ref_variant)
             self._result = self._ref_result(*self._ref.step(0))
         return self._result
 
     def _ref_changes(self, coords, flags):
         self._ref_plan()
-        if self._ref_kind == 0:                            # LPA*: one updateVertex round + plan() per cell
+        if self._ref_variant == 1:                         # D* Lite: OnPress walks and toggles the cell itself
+            for c, b in zip(coords, flags):
+                if b != (c not in self.obstacles):
+                    raise _lib.PmpError("reference-order D* Lite toggles the cell (d_star_lite.py:82-86)")
+                self._result = self._ref_result(*self._ref.step(1, (c, False)))
+                self._edit_host_map([c], [b])              # the kernel has flipped the device bit already
+        elif self._ref_kind == 0:                          # LPA*: one updateVertex round + plan() per cell
             for c, b in zip(coords, flags):
                 was = c in self.obstacles
                 self._edit_host_map([c], [b])
@@ -353,10 +361,11 @@ class LPAStar3D(_ReplanMixin, GraphSearcher3D):
 
 class DStarLite(LPAStar):
     """d_star_lite.py:14-187: same (g, rhs) repair as LPA*, searched from the goal; plan() and
-    the toggling OnPress have the LPA* signatures, the path is start -> goal"""
+    the toggling OnPress have the LPA* signatures, the path is start -> goal.  With
+    reference_order=True apply_change(coord) is the walk of the reference's OnPress: it returns the
+    cells walked from the start (one step on the old field, then on the repaired one) and their cost."""
 
-    def __init__(self, start: tuple, goal: tuple, env, heuristic_type: str = "euclidean") -> None:
-        super().__init__(start, goal, env, heuristic_type, reference_order=False)   # no reference-order kernel for D* Lite
+    _ref_variant = 1
 
     def __str__(self) -> str:
         return "D* Lite"

@@ -46,6 +46,12 @@ struct HostEnv {
     bool inbox(int x, int y, int z) const {
         return x >= 0 && y >= 0 && z >= 0 && x < dims[0] && y < dims[1] && z < dims[2];
     }
+    bool toggle(int x, int y, int z) const { // DStarLite.OnPress edits the obstacle set mid-walk; true = freed
+        uint8_t *p = const_cast<uint8_t *>(occ) + ((int64_t)z * dims[1] + y) * dims[0] + x;
+        const bool was = *p != 0;
+        *p = was ? 0 : 1;
+        return was;
+    }
     bool obst(int x, int y, int z) const { return inbox(x, y, z) && blocked(x, y, z); }
     bool legal_dir(int dx, int dy, int dz, int x, int y, int z) const {
         if (blocked(x, y, z) || blocked(x + dx, y + dy, z + dz)) return false;
@@ -151,7 +157,7 @@ extern "C" int bf_host_plan(int ndim, const int32_t *dims, const uint8_t *occ, i
 
 struct IncrHost {
     HostEnv env;
-    int kind; // 0 LPA*, 1 D*
+    int kind; // 0 LPA*, 1 D*, 2 D* Lite
     std::vector<double> a, b, key;
     std::vector<uint32_t> parent, list, expand;
     std::vector<uint8_t> tag;
@@ -181,8 +187,9 @@ extern "C" void *incr_host_create(int kind, int ndim, const int32_t *dims, const
     H->a.assign(cells, INFINITY); H->b.assign(cells, INFINITY); H->key.assign(2 * cells, 0.0);
     H->parent.assign(cells, BF_NONE); H->tag.assign(cells, DS_NEW);
     H->list.assign(8 * cells + 64, 0); H->expand.assign(64 * cells + 64, 0);
-    if (kind == 0) {
+    if (kind == 0 || kind == 2) {
         LpaState &L = H->L;
+        L.dlite = kind == 2; L.km = 0.0;
         L.g = H->a.data(); L.rhs = H->b.data(); L.k1 = H->key.data(); L.k2 = H->key.data() + cells;
         L.U = H->list.data(); L.ucap = (int64_t)H->list.size(); L.un = 0;
         L.expand = H->expand.data(); L.expand_cap = (int64_t)H->expand.size(); L.n_expand = 0;
@@ -211,7 +218,20 @@ extern "C" int incr_host_step(void *h, int op, const int32_t *change, double *co
     int32_t n = 0;
     const BfState *S;
     int status;
-    if (H->kind == 0) {
+    if (H->kind == 2) {
+        LpaState &L = H->L;
+        if (op == 0) {
+            lpa_init(L);
+            lpa_compute(L, H->env);
+            if (L.status != BF_OVERFLOW) dlite_extract(L, H->env, cellsv.data(), path_cap, &n, cost_out);
+        } else {
+            dlite_press(L, H->env, change[0], change[1], 0, cellsv.data(), path_cap, &n, cost_out);
+        }
+        status = L.status;
+        *n_expand = L.n_expand;
+        for (int64_t i = 0; i < L.n_expand && i < expand_cap; ++i) expand_cell[i] = L.expand[i];
+        S = &L.S;
+    } else if (H->kind == 0) {
         LpaState &L = H->L;
         if (op == 0) lpa_init(L);
         else lpa_apply_change(L, H->env, change[0], change[1], H->env.ndim == 3 ? change[2] : 0, change[3] != 0);

@@ -55,6 +55,39 @@ def dstar_press_2d(planner, xy):
     return cost, path
 
 
+def dlite_press_2d(planner, xy):
+    """d_star_lite.py:64-96 without the plot calls"""
+    x, y = xy
+    cur_start, new_start = planner.start, planner.start
+    update_start = True
+    cost, count = 0, 0
+    path = [planner.start.current]
+    planner.EXPAND = []
+    while cur_start != planner.goal:
+        neighbors = [node_n for node_n in planner.getNeighbor(cur_start)
+                     if not planner.isCollision(cur_start, node_n)]
+        next_node = min(neighbors, key=lambda n: n.g)
+        path.append(next_node.current)
+        cost += planner.cost(cur_start, next_node)
+        count += 1
+        cur_start = next_node
+        if update_start:
+            update_start = False
+            planner.km = planner.h(cur_start, new_start)
+            new_start = cur_start
+            node_change = planner.map[(x, y)]
+            if (x, y) not in planner.obstacles:
+                planner.obstacles.add((x, y))
+            else:
+                planner.obstacles.remove((x, y))
+                planner.updateVertex(node_change)
+            planner.env.update(planner.obstacles)
+            for node_n in planner.getNeighbor(node_change):
+                planner.updateVertex(node_n)
+            planner.computeShortestPath()
+    return cost, path
+
+
 def record(steps, shape, cost, path, expand):
     steps["cost"].append(float(cost))
     steps["path"].add(np.array(path, dtype=np.int32).reshape(-1, len(shape)))
@@ -80,7 +113,8 @@ def main_incr(pmp):
     out = {}
     specs = [("lpa", (31, 21), 0.12, 12), ("lpa", (36, 28), 0.2, 12), ("lpa", (14, 12, 10), 0.1, 10),
              ("lpa", (18, 10, 9), 0.18, 10), ("dstar", (31, 21), 0.12, 8), ("dstar", (36, 28), 0.18, 8),
-             ("dstar", (14, 12, 10), 0.1, 8), ("dstar", (18, 10, 9), 0.16, 8)]
+             ("dstar", (14, 12, 10), 0.1, 8), ("dstar", (18, 10, 9), 0.16, 8),
+             ("dlite", (31, 21), 0.12, 10), ("dlite", (36, 28), 0.2, 10)]
     k = 0
     for kind, dims, density, n_changes in specs:
         ndim = len(dims)
@@ -90,6 +124,8 @@ def main_incr(pmp):
         occ0 = occupancy(env, dims)
         if kind == "lpa":
             planner = (pmp.LPAStar if ndim == 2 else pmp.LPAStar3D)(start=start, goal=goal, env=env)
+        elif kind == "dlite":
+            planner = pmp.DStarLite(start=start, goal=goal, env=env)
         else:
             planner = (pmp.DStar if ndim == 2 else pmp.DStar3D)(start=start, goal=goal, env=env)
         steps = dict(cost=[], path=mg.Ragged(), expand=mg.Ragged())
@@ -113,7 +149,10 @@ def main_incr(pmp):
                 continue
             signal.alarm(20)
             try:
-                if kind == "lpa":
+                if kind == "dlite":
+                    now_blocked = c not in planner.obstacles
+                    cost, path = dlite_press_2d(planner, c)
+                elif kind == "lpa":
                     now_blocked = c not in planner.obstacles
                     if ndim == 2:
                         cost, path, _ = toggle_2d(planner, c)
@@ -136,7 +175,7 @@ def main_incr(pmp):
             changes.append(c)
             flags.append(now_blocked)
             record(steps, dims, cost, path, planner.EXPAND)
-        out[f"c{k}_kind"] = np.array(0 if kind == "lpa" else 1)
+        out[f"c{k}_kind"] = np.array({"lpa": 0, "dstar": 1, "dlite": 2}[kind])
         out[f"c{k}_shape"] = np.array(dims, dtype=np.int32)
         out[f"c{k}_bits"] = pack(occ0)
         out[f"c{k}_start"] = np.array(start, dtype=np.int32)
