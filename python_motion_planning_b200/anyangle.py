@@ -9,7 +9,7 @@ allows it (Lazy Theta*: assumes it does and repairs the parent when the node is 
   (`pmp_bestfirst`, csrc/pmp_bestfirst.cu: one warp per query, the line-of-sight tests of a node's
   neighbours run in parallel lanes).  cost, path, len(expand) and every expand record equal the
   reference's, including the Distance / Visited Nodes columns of the theta_star and
-  lazy_theta_star rows of its 3d_pathfinding_results.csv.  Default for grids up to 2 Mi padded
+  lazy_theta_star rows of its 3d_pathfinding_results.csv.  Default for grids up to 128 Ki padded
   cells (the reference's own sizes and well beyond).
 * `mode="shortcut"` -- for large maps: the tiled wavefront A* (`pmp_sssp`) + path extraction, then
   `pmp_shortcut_paths` walks the extracted path and keeps a waypoint only where the line of sight
@@ -17,7 +17,7 @@ allows it (Lazy Theta*: assumes it does and repairs the parent when the node is 
   bit-exact against the reference's on committed vectors), applied after the search instead of
   inside it.  Result: a collision-free any-angle path with cost <= the grid A* cost; not the
   reference's Theta* path (Theta* may leave the grid-optimal corridor), documented divergence of
-  this mode.  Default above 2 Mi cells.
+  this mode.  Default above 128 Ki cells.
 """
 import numpy as np
 
@@ -25,7 +25,7 @@ from . import _lib, engine
 from .environment import Node, Node3D
 from .planner import GraphSearcher, GraphSearcher3D, _plan_bestfirst
 
-REFERENCE_MODE_MAX_CELLS = 1 << 21
+REFERENCE_MODE_MAX_CELLS = 1 << 17
 
 
 def line_of_sight(env, a, b):

@@ -325,15 +325,16 @@ struct DsState {
 
 // insert, d_star.py:228-242 / d_star3d.py:236-249
 BF_HD static inline void ds_insert(DsState &D, uint32_t c, double h_new) {
+    const bool was_open = D.t[c] == DS_OPEN;
     if (D.t[c] == DS_NEW) D.k[c] = h_new;
-    else if (D.t[c] == DS_OPEN) D.k[c] = D.k[c] < h_new ? D.k[c] : h_new;
+    else if (was_open) D.k[c] = D.k[c] < h_new ? D.k[c] : h_new;
     else D.k[c] = D.h[c] < h_new ? D.h[c] : h_new;
     D.h[c] = h_new;
     D.t[c] = DS_OPEN;
-    if (D.family == 3) { // "if node not in self.OPEN"
-        for (int64_t i = 0; i < D.on; ++i)
-            if (D.OPEN[i] == c) return;
-    }
+    // 3D: "if node not in self.OPEN" (d_star3d.py:248-249).  There a node is in the list exactly while
+    // its tag is OPEN (insert appends on the way in, delete removes on the way out), so the tag
+    // answers the membership test without scanning the list.
+    if (D.family == 3 && was_open) return;
     if (D.on >= D.ocap) { D.status = BF_OVERFLOW; return; }
     D.OPEN[D.on++] = c;
 }

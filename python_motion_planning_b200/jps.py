@@ -6,13 +6,13 @@
   jump-point path, len(expand) and every expand record equal the reference's -- including the
   places where the reference is not optimal: its 2D jump() never calls isCollision (diagonal moves
   cut corners) and its 3D forced-neighbour rules prune too much (longer than AStar3D in a third of
-  the seeded queries, tools/make_golden_jps.py).  Default up to 2 Mi padded cells.
+  the seeded queries, tools/make_golden_jps.py).  Default up to 128 Ki padded cells.
 * `mode="wavefront"` -- for large maps: jump point search is a pruning technique for sequential A*;
   the tiled wavefront of k_sssp is this package's accelerator for the same job.  `JPS` runs it with
   the edge rule of the reference's jump() (`pmp_grid_set_corner_cutting`), so the cost equals the
   reference's (the optimum of that graph; tests/golden/jps.npz) and the path holds the turning
   points of the grid path (the reference lists its jump points: same polyline, possibly more
-  vertices).  `JPS3D` returns the optimum: cost <= the reference's.  Default above 2 Mi cells.
+  vertices).  `JPS3D` returns the optimum: cost <= the reference's.  Default above 128 Ki cells.
 """
 from .environment import Node, Node3D
 from .planner import GraphSearcher, GraphSearcher3D, _plan_bestfirst
@@ -31,7 +31,7 @@ def turning_points(path):
     return out
 
 
-REFERENCE_MODE_MAX_CELLS = 1 << 21
+REFERENCE_MODE_MAX_CELLS = 1 << 17
 
 
 class _JpsMixin:
