@@ -11,7 +11,7 @@ from .environment import Env, Env3D, Grid, Grid3D, Node, Node3D
 from .planner import (AStar, AStar3D, Dijkstra, Dijkstra3D, GBFS, GBFS3D, GraphSearcher,
                       GraphSearcher3D, Planner, Planner3D, SearchFactory, ExpandView,
                       set_reference_order)
-from .batch import plan_batch, plan_batch_sharded, cost_field, shard_range
+from .batch import plan_batch, plan_batch_reference, plan_batch_sharded, cost_field, shard_range
 from .replan import LPAStar, LPAStar3D, DStar, DStar3D, DStarLite, DynamicField, ReplanSession
 from .jps import JPS, JPS3D
 from .anyangle import ThetaStar, ThetaStar3D, LazyThetaStar, LazyThetaStar3D, line_of_sight
@@ -19,6 +19,6 @@ from ._lib import PmpError
 
 __all__ = ["Env", "Env3D", "Grid", "Grid3D", "Node", "Node3D", "AStar", "AStar3D", "Dijkstra",
            "Dijkstra3D", "GBFS", "GBFS3D", "GraphSearcher", "GraphSearcher3D", "Planner",
-           "Planner3D", "SearchFactory", "ExpandView", "plan_batch", "plan_batch_sharded", "shard_range", "cost_field", "PmpError",
+           "Planner3D", "SearchFactory", "ExpandView", "plan_batch", "plan_batch_reference", "plan_batch_sharded", "shard_range", "cost_field", "PmpError",
            "LPAStar", "LPAStar3D", "DStar", "DStar3D", "DStarLite", "DynamicField", "ReplanSession",
            "set_reference_order", "JPS", "JPS3D", "ThetaStar", "ThetaStar3D", "LazyThetaStar", "LazyThetaStar3D", "line_of_sight"]

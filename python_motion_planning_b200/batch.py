@@ -167,3 +167,75 @@ def plan_batch_sharded(env, starts, goals, dist=None, gather=True, _plan=None, *
         res.costs, res.gcosts = c[0], c[1]
         res.status, res.path_len = s[0].astype(np.int32), s[1].astype(np.int32)
     return res
+
+
+_REF_ALGO = {"a_star": _lib.ASTAR, "astar": _lib.ASTAR, "dijkstra": _lib.DIJKSTRA, "gbfs": _lib.GBFS,
+             "theta_star": _lib.THETA_STAR, "lazy_theta_star": _lib.LAZY_THETA_STAR, "jps": _lib.JPS}
+
+
+def plan_batch_reference(env, starts, goals, algo="a_star", heuristic_type="euclidean", want_paths=True,
+                         max_bytes=8 << 30):
+    """nq independent queries on one environment in the REFERENCE'S pop order (pmp_bestfirst, one warp
+    per query, all queries of a wave concurrently): costs, paths and `n_expand` (len(CLOSED), the
+    benchmark's "Visited Nodes") equal what the reference's planner returns for each query.
+    algo: a_star | dijkstra | gbfs | theta_star | lazy_theta_star | jps.  Paths are goal -> start
+    coordinate arrays as in plan_batch.  Usable as `_plan` of plan_batch_sharded."""
+    ndim = env._ndim
+    starts = np.asarray(starts, dtype=np.int32).reshape(-1, ndim)
+    goals = np.asarray(goals, dtype=np.int32).reshape(-1, ndim)
+    nq = len(starts)
+    dg = env.device_grid()
+    offsets, costs = motion_table(env, ndim)
+    dg.set_motions(offsets, costs)
+    t = dg.torch
+    n = dg.pcells
+    heap_cap = int(min(len(offsets) * n + 1, 1 << 23))
+    per_q = heap_cap * _lib.BESTFIRST_HEAP_REC_BYTES + 32 * n
+    wave = int(max(1, min(nq, max_bytes // per_q)))
+    hid = _lib.H_MANHATTAN if heuristic_type == "manhattan" else _lib.H_EUCLIDEAN
+    res = BatchResult()
+    res.costs = np.full(nq, np.inf)
+    res.gcosts = res.costs
+    res.status = np.zeros(nq, dtype=np.int32)
+    res.path_len = np.zeros(nq, dtype=np.int32)
+    res.n_expand = np.zeros(nq, dtype=np.int64)
+    if want_paths:
+        res.paths = [None] * nq
+    dev = dg.device
+    heap = t.empty(wave * heap_cap * _lib.BESTFIRST_HEAP_REC_BYTES, dtype=t.uint8, device=dev)
+    cg = t.empty((wave, n), dtype=t.float64, device=dev)
+    ch = t.empty((wave, n), dtype=t.float64, device=dev)
+    cpar = t.empty((wave, n), dtype=t.int32, device=dev)
+    order = t.empty((wave, n), dtype=t.int32, device=dev)
+    path = t.empty((wave, n), dtype=t.int32, device=dev)
+    plen_d = t.empty(wave, dtype=t.int32, device=dev)
+    cost_d = t.empty(wave, dtype=t.float64, device=dev)
+    nexp_d = t.empty(wave, dtype=t.int32, device=dev)
+    for q0 in range(0, nq, wave):
+        m = min(wave, nq - q0)
+        sg = np.zeros((2, m, 3), dtype=np.int32)
+        sg[0, :, :ndim] = starts[q0:q0 + m]
+        sg[1, :, :ndim] = goals[q0:q0 + m]
+        sg_d = t.from_numpy(sg).to(dev)
+        res.h2d_bytes += sg.nbytes
+        _lib.check(dg.L.pmp_bestfirst(dg.handle, _REF_ALGO[algo], hid, m, sg_d[0].data_ptr(), sg_d[1].data_ptr(),
+                                      heap.data_ptr(), heap_cap, cg.data_ptr(), ch.data_ptr(), cpar.data_ptr(),
+                                      order.data_ptr(), n, path.data_ptr(), n, plen_d.data_ptr(),
+                                      cost_d.data_ptr(), nexp_d.data_ptr(), dg.stream()), "pmp_bestfirst")
+        plen = plen_d[:m].cpu().numpy()
+        if (plen < 0).any():
+            raise _lib.PmpError("pmp_bestfirst: OPEN / CLOSED capacity exceeded for a query of the batch")
+        res.costs[q0:q0 + m] = cost_d[:m].cpu().numpy()
+        res.path_len[q0:q0 + m] = plen
+        res.n_expand[q0:q0 + m] = nexp_d[:m].cpu().numpy()
+        res.status[q0:q0 + m] = np.where(plen > 0, _lib.ST_REACHED, _lib.ST_EXHAUSTED)
+        res.d2h_bytes += m * (8 + 4 + 4)
+        if want_paths:
+            mask = t.arange(n, device=dev)[None, :] < plen_d[:m, None]
+            flat = path[:m][mask].cpu().numpy()
+            res.d2h_bytes += flat.nbytes
+            coords = engine.cells_to_coords(flat, dg)
+            off = np.concatenate([[0], np.cumsum(plen)])
+            for i in range(m):
+                res.paths[q0 + i] = coords[off[i]:off[i + 1]]
+    return res

@@ -107,3 +107,32 @@ def test_reference_order_switches():
         pmp.set_reference_order(False)
     wave_cost = pmp.AStar(c["start"], c["goal"], env).plan()[0]
     assert wave_cost == pytest.approx(cost, rel=1e-9)
+
+
+def test_reference_order_batch_equals_single_queries():
+    """plan_batch_reference: all queries of a (grid, algorithm) group in one launch, one warp each"""
+    checked = 0
+    for fname, ndim in (("cases2d.npz", 2), ("cases3d.npz", 3), ("anyangle2d.npz", 2), ("jpscases3d.npz", 3)):
+        cases = gio.Cases(fname, ndim)
+        groups = {}
+        for i in range(len(cases)):
+            c = cases.case(i)
+            groups.setdefault((c["gi"], c["algo"], c["heur"], c["mset"]), []).append(c)
+        names = {0: "a_star", 1: "dijkstra", 2: "gbfs", 3: "theta_star", 4: "lazy_theta_star", 5: "jps"}
+        for (gi, algo, heur, mset), cs in groups.items():
+            if len(cs) < 2:
+                continue
+            env = make_env(cs[0]["occ"], mset)
+            res = pmp.plan_batch_reference(env, [c["start"] for c in cs], [c["goal"] for c in cs], algo=names[algo],
+                                           heuristic_type="manhattan" if heur == 1 else "euclidean")
+            for q, c in enumerate(cs):
+                tag = (fname, gi, algo, q)
+                assert int(res.n_expand[q]) == len(c["e_cell"]) or (ndim == 2 and not c["found"]), tag
+                if c["found"]:
+                    assert res.costs[q] == c["cost"], tag
+                    want = c["path"] if ndim == 2 else c["path"][::-1]      # batch paths are goal -> start
+                    assert [tuple(int(v) for v in p) for p in res.paths[q]] == want, tag
+                else:
+                    assert np.isinf(res.costs[q]) and res.path_len[q] == 0, tag
+                checked += 1
+    assert checked >= 100
