@@ -106,3 +106,48 @@ def test_core_csv_known_answers(host, name, algo, fname):
         assert len(r["e_cell"]) == int(a[f"{name}_csv_vis"][k]), (name, k)
         assert r["cost"] == pytest.approx(float(a[f"{name}_csv_dist"][k]), rel=4e-16, abs=0), (name, k)
         assert r["cost"] == float(a[f"{name}_ref_cost"][k]), (name, k)
+
+
+def random_cases(seed, n_grids, ndim):
+    """seeded random walled maps with a motion subset, a heuristic and a few free start / goal pairs"""
+    rng = np.random.default_rng(seed)
+    for _ in range(n_grids):
+        shape = tuple(int(v) for v in (rng.integers(9, 28, size=2) if ndim == 2 else rng.integers(6, 13, size=3)))
+        occ = rng.random(shape) < rng.choice([0.1, 0.2, 0.3])
+        for ax in range(ndim):
+            idx = [slice(None)] * ndim
+            idx[ax] = 0
+            occ[tuple(idx)] = True
+            idx[ax] = -1
+            occ[tuple(idx)] = True
+        free = np.argwhere(~occ)
+        if len(free) < 4:
+            continue
+        mset = int(rng.choice([4, 8]) if ndim == 2 else rng.choice([6, 18, 26]))
+        heur = int(rng.integers(0, 2))
+        pairs = [(tuple(int(v) for v in free[i]), tuple(int(v) for v in free[j]))
+                 for i, j in rng.integers(0, len(free), size=(4, 2))]
+        yield occ, mset, heur, pairs
+
+
+@pytest.mark.parametrize("ndim", [2, 3])
+def test_core_equals_oracle_on_random_maps(host, ndim):
+    """two independent restatements of the reference (the oracle's C, pinned to the reference, and the
+    kernel's core) agree exactly on seeded random cases: 4/8- and 6/18/26-connected, both heuristics,
+    unreachable goals included"""
+    n = 0
+    for occ, mset, heur, pairs in random_cases(11 + ndim, 60, ndim):
+        motions, mg = gio.motions_for(ndim, mset)
+        for algo in (0, 1, 2):
+            for s, g in pairs:
+                want = oracle.plan(occ, s, g, algo=algo, heuristic=heur, motions=motions, motion_g=mg)
+                got = plan(host, occ, s, g, algo, heur, motions, mg)
+                tag = (occ.shape, mset, heur, algo, s, g)
+                assert got["reached"] == want.reached, tag
+                if want.reached:
+                    assert got["cost"] == want.cost and got["path"] == want.path, tag
+                assert np.array_equal(got["e_cell"], want.expand_cell), tag
+                assert np.array_equal(got["e_g"], want.expand_g) and np.array_equal(got["e_h"], want.expand_h), tag
+                assert np.array_equal(got["e_parent"], want.expand_parent), tag
+                n += 1
+    assert n >= 600

@@ -136,3 +136,31 @@ def test_reference_order_batch_equals_single_queries():
                     assert np.isinf(res.costs[q]) and res.path_len[q] == 0, tag
                 checked += 1
     assert checked >= 100
+
+
+@pytest.mark.parametrize("ndim", [2, 3])
+def test_reference_order_equals_oracle_on_random_maps(ndim):
+    """the kernel against the pinned oracle on seeded random maps (4/8- and 6/18/26-connected, both
+    heuristics, unreachable goals): cost, path and len(CLOSED) of every query, batched per map"""
+    from oracle import oracle
+    from tests.test_bestfirst_core import random_cases
+    names = {0: "a_star", 1: "dijkstra", 2: "gbfs"}
+    n = 0
+    for occ, mset, heur, pairs in random_cases(11 + ndim, 60, ndim):
+        motions, mg = gio.motions_for(ndim, mset)
+        env = make_env(occ, mset)
+        for algo in (0, 1, 2):
+            res = pmp.plan_batch_reference(env, [s for s, _ in pairs], [g for _, g in pairs], algo=names[algo],
+                                           heuristic_type="manhattan" if heur == 1 else "euclidean")
+            for q, (s, g) in enumerate(pairs):
+                want = oracle.plan(occ, s, g, algo=algo, heuristic=heur, motions=motions, motion_g=mg)
+                tag = (occ.shape, mset, heur, algo, s, g)
+                assert int(res.n_expand[q]) == want.n_expand, tag
+                if want.reached:
+                    assert res.costs[q] == want.cost, tag
+                    path = [tuple(int(v) for v in p) for p in res.paths[q]]           # goal -> start
+                    assert path == (want.path if ndim == 2 else want.path[::-1]), tag
+                else:
+                    assert np.isinf(res.costs[q]) and res.path_len[q] == 0, tag
+                n += 1
+    assert n >= 600
