@@ -348,20 +348,19 @@ BF_HD static inline int64_t ds_min_index(const DsState &D) {
     return bi;
 }
 
-// processState, d_star.py:150-211 / d_star3d.py:167-220.  Returns the new minimum k, -1: OPEN empty.
+// processState, d_star.py:150-211 / d_star3d.py:167-220.  Returns the new minimum k, -1: OPEN empty
+// (want_min = false: only the sign is wanted -- plan() -- and the second scan of the list is skipped).
 template <class ENV>
-BF_HD static inline double ds_process_state(DsState &D, const ENV &env) {
+BF_HD static inline double ds_process_state(DsState &D, const ENV &env, bool want_min = true) {
     const int64_t bi = ds_min_index(D);
     if (bi < 0) return -1.0;
     const uint32_t c = D.OPEN[bi];
     if (D.n_expand >= D.expand_cap) { D.status = BF_OVERFLOW; return -1.0; }
     D.expand[D.n_expand++] = c;
     const double k_old = D.k[c];
-    if (D.t[c] == DS_OPEN) D.t[c] = DS_CLOSED;          // delete(): the first occurrence leaves the list
-    {
-        int64_t i = 0;
-        while (D.OPEN[i] != c) ++i;
-        for (int64_t j = i; j + 1 < D.on; ++j) D.OPEN[j] = D.OPEN[j + 1];
+    if (D.t[c] == DS_OPEN) D.t[c] = DS_CLOSED;          // delete(): the first occurrence leaves the list --
+    {                                                     // that is bi: duplicates of a node share its k, and
+        for (int64_t j = bi; j + 1 < D.on; ++j) D.OPEN[j] = D.OPEN[j + 1]; // min() returned the first of them
         --D.on;
     }
     int x, y, z;
@@ -407,6 +406,7 @@ BF_HD static inline double ds_process_state(DsState &D, const ENV &env) {
             }
         }
     }
+    if (!want_min) return D.on == 0 ? -1.0 : 0.0;
     const int64_t mi = ds_min_index(D);
     return mi < 0 ? -1.0 : D.k[D.OPEN[mi]];
 }
@@ -425,7 +425,7 @@ BF_HD static inline void ds_init(DsState &D) {
 template <class ENV>
 BF_HD static inline void ds_plan(DsState &D, const ENV &env) {
     for (int64_t it = 0; it < DS_GUARD && D.status == BF_RUNNING; ++it) {
-        const double kmin = ds_process_state(D, env);
+        const double kmin = ds_process_state(D, env, false);
         if (D.family == 3 && kmin < 0) break;
         if (D.t[D.S.start_cell] == DS_CLOSED) break;
         if (D.family == 2 && D.on == 0) { D.status = BF_EXHAUSTED; break; } // the reference would spin here
