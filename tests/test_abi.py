@@ -97,3 +97,16 @@ def test_dense_update_and_lazy_obstacles():
     env.update(occ)
     assert (5, 4) in env.obstacles and len(env.obstacles) == int(occ.sum())
     assert np.array_equal(env.occupancy(), occ)
+
+
+def test_reference_import_paths():
+    """the reference's import paths for this path's names (utils/__init__.py, global_planner/graph_search/__init__.py)"""
+    from python_motion_planning_b200.utils import Grid, Grid3D, Node, SearchFactory, Planner
+    from python_motion_planning_b200.global_planner.graph_search import (AStar, AStar3D, Dijkstra3D, GBFS3D, JPS3D,
+                                                                         LazyThetaStar3D, ThetaStar3D, LPAStar3D,
+                                                                         DStar3D, DStarLite)
+    from python_motion_planning_b200.global_planner import Dijkstra
+    assert Grid is pmp.Grid and Grid3D is pmp.Grid3D and Node is pmp.Node and SearchFactory is pmp.SearchFactory
+    assert AStar is pmp.AStar and AStar3D is pmp.AStar3D and Dijkstra is pmp.Dijkstra and Planner is pmp.Planner
+    assert DStarLite is pmp.DStarLite and ThetaStar3D is pmp.ThetaStar3D and LPAStar3D is pmp.LPAStar3D
+    assert all(c is not None for c in (Dijkstra3D, GBFS3D, JPS3D, LazyThetaStar3D, DStar3D))

@@ -45,3 +45,22 @@ def test_benchmark_writer_schema_and_known_answers(tmp_path):
         if a in ("theta_star", "lazy_theta_star"):
             assert abs(d - float(az[f"{a}_csv_dist"][k])) <= 4e-16 * max(d, 1.0)
             assert int(r["Visited Nodes"]) == int(az[f"{a}_csv_vis"][k])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("flag", [[], ["--reference-order"]])
+def test_global_examples_script(flag):
+    """examples/global_examples.py (the reference's script with the package swapped): every 2D planner name of
+    SearchFactory plans and 'animates' headlessly; README costs as measured on the reference"""
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "global_examples.py")] + flag, check=True,
+                         capture_output=True, text=True, timeout=300).stdout
+    rows = {line.split()[0]: line for line in out.strip().splitlines()}
+    assert set(rows) == {"a_star", "dijkstra", "gbfs", "theta_star", "lazy_theta_star", "jps", "d_star", "lpa_star",
+                         "d_star_lite"}
+    assert "cost 54.041631" in rows["a_star"] and "cost 54.041631" in rows["dijkstra"]
+    assert "cost 73.254834" in rows["gbfs"]
+    if flag:                                   # reference order: the reference's own expansion counts
+        assert rows["a_star"].rstrip().endswith("visited 579") and rows["dijkstra"].rstrip().endswith("visited 1219")
+        assert rows["gbfs"].rstrip().endswith("visited 197")
+        assert "cost 51.707233" in rows["theta_star"] and "cost 51.978792" in rows["lazy_theta_star"]
+        assert "cost 53.455844" in rows["jps"]
