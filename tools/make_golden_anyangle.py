@@ -59,6 +59,16 @@ def make_2d(pmp):
             for a, cls in classes.items():
                 res = mg.run(cls(start=s, goal=g, env=env), occ.shape)
                 cw.add(gi, a, 0, 8, s, g, res)
+    # 4-connected: env.motions filtered before the planner aliases it (graph_search.py:26)
+    occ = c2.grids[2]
+    env = env2d_from(pmp, occ)
+    env.motions = [m for m in env.motions if m.g == 1]
+    gi = cw.add_grid(c2.grid_names[2] + "_4conn", occ)
+    pts = mg.free_cells(occ, np.random.default_rng(950), 8)
+    for qi in range(4):
+        s, g = pts[2 * qi], pts[2 * qi + 1]
+        for a, cls in classes.items():
+            cw.add(gi, a, 0, 4, s, g, mg.run(cls(start=s, goal=g, env=env), occ.shape))
     cw.save("anyangle2d.npz")
     print("anyangle2d:", len(cw.meta), "cases;", sum(cw.found), "with a path")
 
@@ -67,10 +77,13 @@ def make_3d(pmp):
     ref_harness.fast_grid_map(pmp)
     cw = mg.CaseWriter(3)
     classes = {THETA: pmp.ThetaStar3D, LAZY: pmp.LazyThetaStar3D}
-    for mset, dims, seed in ((26, (18, 14, 10), 31), (26, (16, 16, 12), 32), (18, (16, 13, 10), 33)):
+    for mset, dims, seed in ((26, (18, 14, 10), 31), (26, (16, 16, 12), 32), (18, (16, 13, 10), 33),
+                             (6, (14, 12, 10), 34)):
         env = mg.boxes_env3d(pmp, dims, 14, 4, seed)
         if mset == 18:
             env.motions = [m for m in env.motions if m.g < 1.5]
+        elif mset == 6:
+            env.motions = [m for m in env.motions if m.g == 1]
         occ = mg.dense(env, 3)
         gi = cw.add_grid(f"boxes_{mset}conn_{seed}", occ)
         pts = mg.free_cells(occ, np.random.default_rng(400 + seed), 8)
@@ -106,6 +119,14 @@ def make_jps(pmp):
         for qi in range(8):
             s, g = pts[2 * qi], pts[2 * qi + 1]
             cw.add(gi, JPS, 0, 8, s, g, mg.run(pmp.JPS(start=s, goal=g, env=env), occ.shape))
+    occ = c2.grids[2]
+    env = env2d_from(pmp, occ)
+    env.motions = [m for m in env.motions if m.g == 1]
+    gi = cw.add_grid(c2.grid_names[2] + "_4conn", occ)
+    pts = mg.free_cells(occ, np.random.default_rng(750), 8)
+    for qi in range(4):
+        s, g = pts[2 * qi], pts[2 * qi + 1]
+        cw.add(gi, JPS, 0, 4, s, g, mg.run(pmp.JPS(start=s, goal=g, env=env), occ.shape))
     cw.save("jpscases2d.npz")
     print("jpscases2d:", len(cw.meta), "cases;", sum(cw.found), "with a path")
     cw = mg.CaseWriter(3)
