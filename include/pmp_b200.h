@@ -34,7 +34,8 @@
 extern "C" {
 #endif
 
-#define PMP_B200_ABI_VERSION 1
+/* 2: + pmp_bestfirst, pmp_lpa_star, pmp_d_star (additive; every version-1 entry point is unchanged) */
+#define PMP_B200_ABI_VERSION 2
 
 typedef struct pmp_grid pmp_grid; /* opaque: occupancy bitmask + motion table on one device */
 

@@ -12,6 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PMP_B200_LIB") or os.path.join(_HERE, "libpmp_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
 
+ABI_VERSION = 2                              # PMP_B200_ABI_VERSION this binding was written against
 ASTAR, DIJKSTRA, GBFS = 0, 1, 2
 THETA_STAR, LAZY_THETA_STAR, JPS = 3, 4, 5    # pmp_bestfirst only
 BESTFIRST_HEAP_REC_BYTES = 40
@@ -74,6 +75,9 @@ def lib():
     L.pmp_last_error.restype = ctypes.c_char_p
     L.pmp_last_error.argtypes = []
     L.pmp_abi_version.restype = i32
+    if L.pmp_abi_version() != ABI_VERSION:
+        raise PmpError(f"{LIB_PATH} has ABI version {L.pmp_abi_version()}, this package needs {ABI_VERSION}: "
+                       "rebuild it (python -c 'import __graft_entry__ as g; g.build()')")
     L.pmp_device_count.restype = i32
     sig = {
         "pmp_grid_create": [i32, vp, ctypes.POINTER(vp)],
