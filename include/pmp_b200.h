@@ -52,7 +52,8 @@ enum pmp_status {
     PMP_ST_EXHAUSTED = 1, /* every reachable cell settled; goal (if any) not reached */
     PMP_ST_REACHED = 2,   /* g[goal] is final */
     PMP_ST_BAD_QUERY = 3, /* start or goal outside the box or on an obstacle */
-    PMP_ST_REPLAN_OVERFLOW = 4 /* pmp_replan_update: scratch too small for the invalidated region */
+    PMP_ST_REPLAN_OVERFLOW = 4, /* pmp_replan_update: scratch too small for the invalidated region */
+    PMP_ST_ERROR = 5      /* the search did not finish (a queue wait timed out): the result is invalid */
 };
 
 const char *pmp_last_error(void);

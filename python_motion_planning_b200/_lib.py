@@ -18,7 +18,15 @@ THETA_STAR, LAZY_THETA_STAR, JPS = 3, 4, 5    # pmp_bestfirst only
 BESTFIRST_HEAP_REC_BYTES = 40
 H_EUCLIDEAN, H_MANHATTAN = 0, 1
 W_F64, W_U32 = 0, 1
-ST_RUNNING, ST_EXHAUSTED, ST_REACHED, ST_BAD_QUERY, ST_REPLAN_OVERFLOW = 0, 1, 2, 3, 4
+ST_RUNNING, ST_EXHAUSTED, ST_REACHED, ST_BAD_QUERY, ST_REPLAN_OVERFLOW, ST_ERROR = 0, 1, 2, 3, 4, 5
+
+
+def check_status(status, what="search"):
+    """raise PmpError when a status word (or array of them) reports an aborted search -- a queue
+    wait timed out inside the kernel, so whatever the field holds must not be used"""
+    import numpy as np
+    if np.any(np.asarray(status) == ST_ERROR):
+        raise PmpError(f"{what}: the search kernel aborted (queue wait timed out); no result")
 
 # every symbol include/pmp_b200.h declares (tests/test_abi.py checks the header against this)
 SYMBOLS = (

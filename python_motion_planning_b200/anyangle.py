@@ -96,6 +96,7 @@ class _AnyAngleMixin:
         gcost, cost, plen, status = float(res[0]), float(res[1]), int(res[2]), int(res[3])
         self.grid_cost = float(res[4])                       # cost of the grid path that was shortcut
         expand = self._expand_view(ws, gcost if np.isfinite(gcost) else None)
+        _lib.check_status(status, str(self))
         if status == _lib.ST_BAD_QUERY or plen <= 0:
             return self._no_path(expand)
         pts = engine.cells_to_points(wp[0, :plen].cpu().numpy(), dg)

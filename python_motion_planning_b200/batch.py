@@ -80,6 +80,7 @@ def plan_batch(env, starts, goals, algo="dijkstra", heuristic_type="euclidean", 
         res.costs[q0:q0 + n] = ws.cost.cpu().numpy()
         res.gcosts[q0:q0 + n] = ws.gcost.cpu().numpy()
         res.status[q0:q0 + n] = ws.status.cpu().numpy()
+        _lib.check_status(res.status[q0:q0 + n], "plan_batch")
         res.path_len[q0:q0 + n] = plen
         res.stats += ws.stats.cpu().numpy()
         res.d2h_bytes += n * (8 + 8 + 4 + 4) + 64
@@ -112,7 +113,8 @@ def cost_field(env, source, weight="f64", window=0.0, to_host=True):
     engine.upload_queries(ws, [tuple(source)], None, ndim)
     engine.sssp(ws, _lib.DIJKSTRA, 0, full_field=True, window=window, have_goals=False)
     if not to_host:
-        return ws, ws.stats
+        return ws, ws.stats        # asynchronous: the caller checks ws.status (engine.check_field_status)
+    _lib.check_status(ws.status.cpu().numpy(), "cost_field")
     return engine.field_to_numpy(ws, 0)
 
 

@@ -1,0 +1,710 @@
+// pmp_bfs_core.cuh -- unit-weight cost-to-go fields on 6-connected voxel grids: one WARP per tile,
+// the whole tile solve in registers (no shared memory, no CTA barrier).
+//
+// Replaces, for the integer-weight 6-connected case (BASELINE.json config 5), the expansion loop of
+// Dijkstra3D.plan / getNeighbor (global_planner/graph_search/dijkstra3d.py:39-126) run to
+// exhaustion with `env.motions` filtered to the six unit moves: with unit weights the cost of a
+// cell is its BFS level, so the same field is produced bit for bit.
+//
+// Scheme
+//   * tile = 32(x) x 8(y) x 8(z) cells.  Lane l of the warp owns the column x = x0 + l: 64 cells
+//     as two 32-bit words, bit (z & 3) * 8 + y of word z >> 2.  A BFS level step is then a handful
+//     of shifts inside the lane (y, z neighbours) plus four warp shuffles (x neighbours); the
+//     level of every cell is recorded in bit-sliced form (7 planes x 2 words) and turned back into
+//     integers by 8x8 bit-matrix transposes -- row stores of the field are naturally coalesced
+//     (one 128-byte line per (y, z) row per instruction).
+//   * PULL model: field words are final values in the library's (value << 1 | 1) format, written
+//     only by the warp that owns the tile.  A tile that lowered boundary cells sets a dirty-face
+//     bit in the neighbour tile's state word and queues the tile; the neighbour reads the face
+//     straight out of the owner's field rows.  Because min-plus relaxation is linear, an
+//     activation only sweeps from the NEW seeds (halo + 1 that beat the own boundary value) and
+//     min-merges the result -- a tile that was never touched is not even read (lazy
+//     initialisation: no field fill before the search; untouched tiles are filled afterwards).
+//   * scheduling: persistent warps pop tile ids from one FIFO ring (near-BFS order, so a tile is
+//     activated about once); per tile a state word {dirty faces, queued, touched} gives mutual
+//     exclusion; an in-flight counter ends the search.
+//   * multi-GPU (z-slabs): the tiles of the lowest / highest z-row read their z halo from the PEER
+//     GPU's field over NVLink and arm / queue the peer's tile with remote atomics -- the same
+//     protocol as between two tiles of one GPU; a counter of active ranks detects termination.
+//
+// The file is compiled by nvcc for sm_100a (pmp_bfs.cu) and, unchanged, by g++ against
+// tests/simt_host.h (a fiber-based SIMT emulator) for the CPU tests.
+#pragma once
+
+#define BFS_FULL 0xFFFFFFFFu
+#define BFS_SRC 0x40u    // state: the source cell lies in this tile and has not been injected yet
+#define BFS_Q 0x80u      // state: the tile is in the ring or being processed
+#define BFS_T 0x100u     // state: the tile's field words are initialised
+#define BFS_DIRTY 0x3Fu  // state bits 0..5: face f has new values on the neighbour's side
+#define BFS_INF 0x7FFFFFFFu
+#define BFS_RAWINF 0xFFFFFFFFu
+#define BFS_CINV 0xFFFFFFFFu
+#define BFS_NREC 7
+#define BFS_LIM 128      // levels one pass can record (2^BFS_NREC)
+#define BFS_SEEDMAX 63u  // largest seed level relative to the pass base (6 seed planes)
+
+// control block (u32 words; hot counters on separate 128-byte lines)
+#define BFS_C_HEAD 0
+#define BFS_C_TAIL 32
+#define BFS_C_INFLIGHT 64
+#define BFS_C_DONE 96
+#define BFS_C_ERR 97
+#define BFS_C_ACTIVE 128 // ranks with work in flight (only rank 0's word is used)
+#define BFS_C_SRC 160    // local source cell x, y, z and a valid flag
+#define BFS_C_WORDS 192
+
+#define BFS_ERR_TIMEOUT 1u
+
+struct BfsPeer {
+    u32 *g;      // peer field (nullptr: no neighbour slab on this side)
+    u32 *state;
+    u32 *ring;
+    u32 *ctr;
+    u32 ring_cap;
+    int nbz;     // z tile rows of the peer
+    int zadj;    // the peer's plane adjacent to this slab (its local z)
+    int bzadj;   // the peer's tile row adjacent to this slab
+};
+
+struct BfsArgs {
+    GridDev G;   // the LOCAL box (a whole grid, or one z-slab of it)
+    int nbx, nby, nbz;
+    u32 ntiles;
+    u32 *g;
+    u32 *state;
+    u32 *ring;
+    u32 ring_cap;
+    u32 *ctr;
+    u64 *stats;
+    int rank, world;
+    BfsPeer lo, hi;      // slabs below (z - 1) / above (z + 1)
+    u32 *peer_ctr[8];    // control blocks of all ranks (termination broadcast); [rank] = own
+    u32 *active;         // rank 0's BFS_C_ACTIVE word
+    u64 timeout_ns;      // spin-loop safety net (0: none)
+};
+
+struct BfsCount {
+    u32 act, idle, lowered, levels, passes, redo, remote;
+};
+
+#ifdef __CUDACC__
+__device__ static inline u64 bfs_now_ns() {
+    u64 t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ static inline void bfs_store(u32 *p, u32 v) { *p = v; }
+__device__ static inline void bfs_store_volatile(u32 *p, u32 v) { *(volatile u32 *)p = v; }
+#else
+static inline u64 bfs_now_ns() { return 0; }
+static inline void bfs_store(u32 *p, u32 v) { *p = v; }
+static inline void bfs_store_volatile(u32 *p, u32 v) { *(volatile u32 *)p = v; }
+#endif
+
+__device__ __forceinline__ u32 bfs_spread4(u32 n) { return ((n & 0xFu) * 0x00204081u) & 0x01010101u; }
+__device__ __forceinline__ u32 bfs_compress4(u32 x) { return (((x & 0x01010101u) * 0x01020408u) >> 24) & 0xFu; }
+
+// 32 x 32 bit-matrix transpose across the warp: afterwards lane x holds the word whose bit l is
+// bit x of the word lane l passed in.
+__device__ __forceinline__ u32 bfs_transpose32(u32 v, const int lane) {
+#pragma unroll
+    for (int j = 16; j >= 1; j >>= 1) {
+        const u32 m = j == 16 ? 0x0000FFFFu : (j == 8 ? 0x00FF00FFu : (j == 4 ? 0x0F0F0F0Fu : (j == 2 ? 0x33333333u : 0x55555555u)));
+        const u32 o = __shfl_xor_sync(BFS_FULL, v, j);
+        if (lane & j) v = (v & ~m) | ((o >> j) & m);
+        else v = (v & m) | ((o << j) & ~m);
+    }
+    return v;
+}
+
+// 8 x 8 bit-matrix transpose of the 64-bit value hi:lo (row k = byte k)
+__device__ __forceinline__ void bfs_transpose8(u32 &lo, u32 &hi) {
+    u64 x = (u64)lo | ((u64)hi << 32), t;
+    t = (x ^ (x >> 7)) & 0x00AA00AA00AA00AAull; x = x ^ t ^ (t << 7);
+    t = (x ^ (x >> 14)) & 0x0000CCCC0000CCCCull; x = x ^ t ^ (t << 14);
+    t = (x ^ (x >> 28)) & 0x00000000F0F0F0F0ull; x = x ^ t ^ (t << 28);
+    lo = (u32)x;
+    hi = (u32)(x >> 32);
+}
+
+// ---- ring ------------------------------------------------------------------------------------
+__device__ static inline void bfs_push(u32 *ring, u32 cap, u32 *ctr, u32 tile) {
+    const u32 ticket = atomicAdd(&ctr[BFS_C_TAIL], 1u);
+    bfs_store_volatile(&ring[ticket % cap], tile + 1u);
+}
+
+__device__ static inline void bfs_fail(const BfsArgs &A, u32 code) {
+    atomicOr(&A.ctr[BFS_C_ERR], code);
+    for (int r = 0; r < A.world; ++r) bfs_store_volatile(&A.peer_ctr[r][BFS_C_DONE], 1u);
+}
+
+// lane 0: next tile id + 1, or 0 when the search is over
+__device__ static inline u32 bfs_pop(const BfsArgs &A) {
+    const u32 ticket = atomicAdd(&A.ctr[BFS_C_HEAD], 1u);
+    u32 *slot = &A.ring[ticket % A.ring_cap];
+    unsigned ns = 32, spins = 0;
+    u64 t0 = 0;
+    for (;;) {
+        const u32 v = __ldcg(slot);
+        if (v) {
+            bfs_store_volatile(slot, 0u); // recycle; the ring has more slots than tiles + waiting warps
+            __threadfence();
+            return v;
+        }
+        if (__ldcg(&A.ctr[BFS_C_DONE])) return 0u;
+        __nanosleep(ns);
+        if (ns < 1024) ns *= 2;
+        if (A.timeout_ns && (++spins & 1023u) == 0) {
+            const u64 now = bfs_now_ns();
+            if (!t0) t0 = now;
+            else if (now - t0 > A.timeout_ns) { bfs_fail(A, BFS_ERR_TIMEOUT); return 0u; }
+        }
+    }
+}
+
+// this rank has nothing in flight any more: leave the set of active ranks; the last one ends
+// the search everywhere
+__device__ static inline void bfs_rank_idle(const BfsArgs &A) {
+    __threadfence_system();
+    if (atomicSub(A.active, 1u) == 1u) {
+        for (int r = 0; r < A.world; ++r) bfs_store_volatile(&A.peer_ctr[r][BFS_C_DONE], 1u);
+    }
+}
+
+// ---- the sweep ---------------------------------------------------------------------------------
+// Multi-source BFS on the tile's bit lanes.  Seeds are given bit-sliced (6 planes: level relative
+// to the pass base, valid mask sv) in two sets: A (y / z faces, every lane) and B (x faces, lanes
+// 0 and 31); `init` cells start at level 0; `R` enters as the cells that must not be entered
+// (blocked by an earlier pass) and returns with the cells reached added.  Levels are recorded
+// bit-sliced in rec[7][2].  Returns in `carry` the cells that would get level BFS_LIM (0 if the
+// wave died out), and the number of levels swept.
+struct BfsSeeds {
+    u32 sp[6][2];
+    u32 sv[2];
+    int last; // largest seed level (uniform), -1: none
+};
+
+__device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const BfsSeeds &SA, const BfsSeeds &SB,
+                                         const u32 init0, const u32 init1, u32 &R0, u32 &R1, u32 (&rec)[BFS_NREC][2],
+                                         u32 &carry0, u32 &carry1, const int lane) {
+    const u32 mUp = lane > 0 ? BFS_FULL : 0u, mDn = lane < 31 ? BFS_FULL : 0u;
+#pragma unroll
+    for (int b = 0; b < BFS_NREC; ++b) rec[b][0] = rec[b][1] = 0u;
+    u32 c0 = init0, c1 = init1;
+    const int last = SA.last > SB.last ? SA.last : SB.last;
+    u32 nlev = 0;
+    bool fin = false;
+    for (int rb = 0; rb < BFS_LIM && !fin; rb += 8) {
+        // seeds of this block of 8 levels: the three high bits of their level equal rb >> 3
+        u32 ha0 = 0, ha1 = 0, hb0 = 0, hb1 = 0;
+        const bool useA = rb <= SA.last, useB = rb <= SB.last;
+        if (useA) {
+            ha0 = SA.sv[0]; ha1 = SA.sv[1];
+#pragma unroll
+            for (int b = 3; b < 6; ++b) {
+                const u32 flip = ((rb >> b) & 1) ? 0u : BFS_FULL;
+                ha0 &= SA.sp[b][0] ^ flip;
+                ha1 &= SA.sp[b][1] ^ flip;
+            }
+        }
+        if (useB) {
+            hb0 = SB.sv[0]; hb1 = SB.sv[1];
+#pragma unroll
+            for (int b = 3; b < 6; ++b) {
+                const u32 flip = ((rb >> b) & 1) ? 0u : BFS_FULL;
+                hb0 &= SB.sp[b][0] ^ flip;
+                hb1 &= SB.sp[b][1] ^ flip;
+            }
+        }
+        u32 bf0 = 0, bf1 = 0; // cells that got a level inside this block
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            u32 f0 = c0, f1 = c1;
+            if (useA) {
+                u32 m0 = ha0, m1 = ha1;
+#pragma unroll
+                for (int b = 0; b < 3; ++b) {
+                    m0 &= ((k >> b) & 1) ? SA.sp[b][0] : ~SA.sp[b][0];
+                    m1 &= ((k >> b) & 1) ? SA.sp[b][1] : ~SA.sp[b][1];
+                }
+                f0 |= m0 & ~R0;
+                f1 |= m1 & ~R1;
+            }
+            if (useB) {
+                u32 m0 = hb0, m1 = hb1;
+#pragma unroll
+                for (int b = 0; b < 3; ++b) {
+                    m0 &= ((k >> b) & 1) ? SB.sp[b][0] : ~SB.sp[b][0];
+                    m1 &= ((k >> b) & 1) ? SB.sp[b][1] : ~SB.sp[b][1];
+                }
+                f0 |= m0 & ~R0;
+                f1 |= m1 & ~R1;
+            }
+            R0 |= f0; R1 |= f1;
+            bf0 |= f0; bf1 |= f1;
+#pragma unroll
+            for (int b = 0; b < 3; ++b)
+                if ((k >> b) & 1) { rec[b][0] |= f0; rec[b][1] |= f1; }
+            // neighbours of the frontier: y +- 1 inside a byte, z +- 1 = byte shifts across the two
+            // words, x +- 1 = the adjacent lanes
+            u32 n0 = ((f0 << 1) & 0xFEFEFEFEu) | ((f0 >> 1) & 0x7F7F7F7Fu) | (f0 << 8) | (f0 >> 8) | (f1 << 24);
+            u32 n1 = ((f1 << 1) & 0xFEFEFEFEu) | ((f1 >> 1) & 0x7F7F7F7Fu) | (f1 << 8) | (f1 >> 8) | (f0 >> 24);
+            const u32 u0 = __shfl_up_sync(BFS_FULL, f0, 1), u1 = __shfl_up_sync(BFS_FULL, f1, 1);
+            const u32 d0 = __shfl_down_sync(BFS_FULL, f0, 1), d1 = __shfl_down_sync(BFS_FULL, f1, 1);
+            n0 |= (u0 & mUp) | (d0 & mDn);
+            n1 |= (u1 & mUp) | (d1 & mDn);
+            c0 = n0 & free0 & ~R0;
+            c1 = n1 & free1 & ~R1;
+            ++nlev;
+            if (rb + k >= last && !__any_sync(BFS_FULL, (c0 | c1) != 0u)) { fin = true; break; }
+        }
+#pragma unroll
+        for (int b = 3; b < BFS_NREC; ++b)
+            if ((rb >> b) & 1) { rec[b][0] |= bf0; rec[b][1] |= bf1; }
+    }
+    carry0 = fin ? 0u : c0;
+    carry1 = fin ? 0u : c1;
+    return nlev;
+}
+
+// ---- levels -> field words -----------------------------------------------------------------------
+// For the cells in N (reached in this pass) the value is base + recorded level.  TOUCHED: the
+// tile already holds values -> min-merge, store only lowered cells; otherwise every word of the
+// tile is written (unreached / blocked cells = all-ones).  Returns the lowered cells in low[].
+template <bool TOUCHED>
+__device__ __forceinline__ void bfs_extract(const u32 (&rec)[BFS_NREC][2], const u32 N0, const u32 N1, const u32 base,
+                                            u32 *cell0, const bool inx, const size_t strideY, const size_t strideZ,
+                                            u32 &low0, u32 &low1) {
+    const u32 base2 = (base << 1) | 1u; // stored word of level 0
+    u32 *pz = cell0;
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+        const u32 Nw = w ? N1 : N0;
+        u32 loww = 0;
+#pragma unroll
+        for (int zb = 0; zb < 4; ++zb) {
+            // byte zb of the 7 planes + the "not reached" plane -> 8 x 8 bit matrix -> one byte per cell
+            const u32 sel = (u32)zb | ((u32)(4 + zb) << 4);
+            const u32 t01 = __byte_perm(rec[0][w], rec[1][w], sel);
+            const u32 t23 = __byte_perm(rec[2][w], rec[3][w], sel);
+            const u32 t45 = __byte_perm(rec[4][w], rec[5][w], sel);
+            const u32 t67 = __byte_perm(rec[6][w], ~Nw, sel);
+            u32 lo = __byte_perm(t01, t23, 0x5410u), hi = __byte_perm(t45, t67, 0x5410u);
+            bfs_transpose8(lo, hi);
+            u32 own[8];
+            if (TOUCHED) {
+                u32 *q = pz;
+#pragma unroll
+                for (int y = 0; y < 8; ++y) {
+                    own[y] = BFS_RAWINF;
+                    if ((Nw >> (zb * 8 + y)) & 1u) own[y] = __ldcg(q); // reached cells are free cells: inside the row
+                    q += strideY;
+                }
+            }
+            u32 *p = pz;
+#pragma unroll
+            for (int y = 0; y < 8; ++y) {
+                const u32 src = y < 4 ? lo : hi;
+                const u32 lv = __byte_perm(src, 0u, 0x4440u | (u32)(y & 3));
+                // a cell that was not reached has bit 7 of its byte set: the sign-replicating byte
+                // select turns that into an all-ones word ("unreached" in the stored format)
+                const u32 unr = __byte_perm(src, 0u, 0x1111u * (u32)(8 | (y & 3)));
+                const u32 word = unr | (base2 + (lv << 1));
+                if (TOUCHED) {
+                    const bool lower = word < own[y]; // stored words order like their values
+                    if (lower) bfs_store(p, word);
+                    loww |= (lower ? 1u : 0u) << (zb * 8 + y);
+                } else {
+                    if (inx) bfs_store(p, word);
+                }
+                p += strideY;
+            }
+            pz += strideZ;
+        }
+        if (TOUCHED) { if (w) low1 |= loww; else low0 |= loww; }
+    }
+    if (!TOUCHED) { low0 |= N0; low1 |= N1; }
+}
+
+// candidate value read across a face: halo + 1, or BFS_CINV if the halo cell is unreached
+__device__ __forceinline__ u32 bfs_cand(u32 raw) { return raw == BFS_RAWINF ? BFS_CINV : (raw >> 1) + 1u; }
+
+// level of a candidate relative to the pass base as a byte (0x80: no seed in this pass); seeds
+// beyond the six seed planes are left for a later activation (`far`)
+__device__ __forceinline__ u32 bfs_rel(const u32 c, const u32 base, u32 &far, u32 &any, u32 &last) {
+    if (c == BFS_CINV) return 0x80u;
+    const u32 r = c - base;
+    if (r > BFS_SEEDMAX) { far = 1u; return 0x80u; }
+    any = 1u;
+    last = r > last ? r : last;
+    return r;
+}
+
+// ---- one tile activation -----------------------------------------------------------------------
+__device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, const int lane, BfsCount &cnt) {
+    const GridDev &Gd = A.G;
+    const int bx = (int)(t % (u32)A.nbx), by = (int)((t / (u32)A.nbx) % (u32)A.nby), bz = (int)(t / ((u32)A.nbx * (u32)A.nby));
+    const int x0 = bx * 32, y0 = by * 8, z0 = bz * 8;
+    const size_t sY = (size_t)Gd.PX, sZ = (size_t)Gd.PX * Gd.PY;
+    const bool inx = x0 + lane < Gd.PX;
+    u32 *cell0 = A.g + (size_t)z0 * sZ + (size_t)y0 * sY + (size_t)(x0 + lane);
+    const bool peer_lo = bz == 0 && A.lo.g != nullptr, peer_hi = bz == A.nbz - 1 && A.hi.g != nullptr;
+
+    // ---- claim: take the dirty faces, keep Q (nobody else may process or queue the tile) ----
+    u32 old = 0;
+    if (lane == 0) old = atomicAnd(&A.state[t], BFS_Q | BFS_T);
+    old = __shfl_sync(BFS_FULL, old, 0);
+    __threadfence(); // acquire: the neighbours' rows written before they set our dirty bits
+    const u32 dirty = old & BFS_DIRTY;
+    bool touched = (old & BFS_T) != 0u;
+    ++cnt.act;
+
+    // ---- occupancy: rows -> this lane's column bits ----
+    const int ly = lane & 7, lzq = lane >> 3; // the (y, z & 3) this lane handles in row-distributed steps
+    u32 free0, free1;
+    {
+        const u32 *brow = Gd.bits + ((size_t)(z0 + lzq) * Gd.PY + (size_t)(y0 + ly)) * Gd.wpr + bx;
+        const u32 o0 = __ldg(brow), o1 = __ldg(brow + (size_t)4 * Gd.PY * Gd.wpr);
+        free0 = ~bfs_transpose32(o0, lane);
+        free1 = ~bfs_transpose32(o1, lane);
+    }
+    // free cells on the far side of each face (a neighbour tile is only armed through them)
+    u32 ymf0, ymf1, ypf0, ypf1, zmf, zpf, xmf0, xmf1, xpf0, xpf1;
+    {
+        u32 o = BFS_FULL; // outside the box: blocked
+        const int i = lane & 7;
+        if (lane < 8) { if (by > 0) o = __ldg(Gd.bits + ((size_t)(z0 + i) * Gd.PY + (size_t)(y0 - 1)) * Gd.wpr + bx); }
+        else if (lane < 16) { if (by < A.nby - 1) o = __ldg(Gd.bits + ((size_t)(z0 + i) * Gd.PY + (size_t)(y0 + 8)) * Gd.wpr + bx); }
+        else if (lane < 24) {
+            if (bz > 0) o = __ldg(Gd.bits + ((size_t)(z0 - 1) * Gd.PY + (size_t)(y0 + i)) * Gd.wpr + bx);
+            else if (peer_lo) o = 0u; // the peer's occupancy is not mapped here: assume free (conservative)
+        } else {
+            if (bz < A.nbz - 1) o = __ldg(Gd.bits + ((size_t)(z0 + 8) * Gd.PY + (size_t)(y0 + i)) * Gd.wpr + bx);
+            else if (peer_hi) o = 0u;
+        }
+        const u32 nf = ~bfs_transpose32(o, lane);
+        ymf0 = bfs_spread4(nf); ymf1 = bfs_spread4(nf >> 4);
+        ypf0 = bfs_spread4(nf >> 8) << 7; ypf1 = bfs_spread4(nf >> 12) << 7;
+        zmf = (nf >> 16) & 0xFFu;
+        zpf = nf & 0xFF000000u;
+        const u32 *brow = Gd.bits + ((size_t)(z0 + lzq) * Gd.PY + (size_t)(y0 + ly)) * Gd.wpr + bx;
+        const size_t w1 = (size_t)4 * Gd.PY * Gd.wpr;
+        u32 a0 = BFS_FULL, a1 = BFS_FULL, b0 = BFS_FULL, b1 = BFS_FULL;
+        if (bx > 0) { a0 = __ldg(brow - 1); a1 = __ldg(brow - 1 + w1); }
+        if (bx < A.nbx - 1) { b0 = __ldg(brow + 1); b1 = __ldg(brow + 1 + w1); }
+        xmf0 = __ballot_sync(BFS_FULL, !(a0 >> 31)); xmf1 = __ballot_sync(BFS_FULL, !(a1 >> 31));
+        xpf0 = __ballot_sync(BFS_FULL, !(b0 & 1u)); xpf1 = __ballot_sync(BFS_FULL, !(b1 & 1u));
+    }
+
+    // ---- candidates across the dirty faces: halo + 1 where it beats the own boundary value ----
+    u32 cYm[8], cYp[8], cZm[8], cZp[8], cXm[2], cXp[2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) cYm[i] = cYp[i] = cZm[i] = cZp[i] = BFS_CINV;
+    cXm[0] = cXm[1] = cXp[0] = cXp[1] = BFS_CINV;
+    if (dirty & 4u) { // y-: halo rows (y0 - 1, z), own cells (y = 0, z)
+        u32 h[8], o[8];
+#pragma unroll
+        for (int z = 0; z < 8; ++z) {
+            h[z] = inx ? __ldcg(cell0 + (size_t)z * sZ - sY) : BFS_RAWINF;
+            o[z] = (touched && inx) ? __ldcg(cell0 + (size_t)z * sZ) : BFS_RAWINF;
+        }
+#pragma unroll
+        for (int z = 0; z < 8; ++z) {
+            const u32 c = bfs_cand(h[z]);
+            const u32 fr = ((z < 4 ? free0 : free1) >> ((z & 3) * 8)) & 1u;
+            cYm[z] = (fr && c != BFS_CINV && c < (o[z] >> 1)) ? c : BFS_CINV;
+        }
+    }
+    if (dirty & 8u) { // y+
+        u32 h[8], o[8];
+#pragma unroll
+        for (int z = 0; z < 8; ++z) {
+            h[z] = inx ? __ldcg(cell0 + (size_t)z * sZ + 8 * sY) : BFS_RAWINF;
+            o[z] = (touched && inx) ? __ldcg(cell0 + (size_t)z * sZ + 7 * sY) : BFS_RAWINF;
+        }
+#pragma unroll
+        for (int z = 0; z < 8; ++z) {
+            const u32 c = bfs_cand(h[z]);
+            const u32 fr = ((z < 4 ? free0 : free1) >> ((z & 3) * 8 + 7)) & 1u;
+            cYp[z] = (fr && c != BFS_CINV && c < (o[z] >> 1)) ? c : BFS_CINV;
+        }
+    }
+    if (dirty & 16u) { // z-: halo rows (y, z0 - 1) -- on the lowest tile row of a slab they are the peer's
+        const u32 *hrow = peer_lo ? A.lo.g + (size_t)A.lo.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 - sZ;
+        u32 h[8], o[8];
+#pragma unroll
+        for (int y = 0; y < 8; ++y) {
+            h[y] = inx ? __ldcg(hrow + (size_t)y * sY) : BFS_RAWINF;
+            o[y] = (touched && inx) ? __ldcg(cell0 + (size_t)y * sY) : BFS_RAWINF;
+        }
+#pragma unroll
+        for (int y = 0; y < 8; ++y) {
+            const u32 c = bfs_cand(h[y]);
+            const u32 fr = (free0 >> y) & 1u;
+            cZm[y] = (fr && c != BFS_CINV && c < (o[y] >> 1)) ? c : BFS_CINV;
+        }
+    }
+    if (dirty & 32u) { // z+
+        const u32 *hrow = peer_hi ? A.hi.g + (size_t)A.hi.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 + 8 * sZ;
+        u32 h[8], o[8];
+#pragma unroll
+        for (int y = 0; y < 8; ++y) {
+            h[y] = inx ? __ldcg(hrow + (size_t)y * sY) : BFS_RAWINF;
+            o[y] = (touched && inx) ? __ldcg(cell0 + 7 * sZ + (size_t)y * sY) : BFS_RAWINF;
+        }
+#pragma unroll
+        for (int y = 0; y < 8; ++y) {
+            const u32 c = bfs_cand(h[y]);
+            const u32 fr = (free1 >> (24 + y)) & 1u;
+            cZp[y] = (fr && c != BFS_CINV && c < (o[y] >> 1)) ? c : BFS_CINV;
+        }
+    }
+    // x faces, row-distributed: this lane looks at the cells (y = ly, z = lzq + 4w)
+    u32 *colrow = A.g + (size_t)(z0 + lzq) * sZ + (size_t)(y0 + ly) * sY + (size_t)x0;
+    if (dirty & 1u) { // x-: halo column x0 - 1, own column x0 (lane 0's cells)
+        const u32 fw0 = __shfl_sync(BFS_FULL, free0, 0), fw1 = __shfl_sync(BFS_FULL, free1, 0);
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+            const u32 c = bfs_cand(__ldcg(colrow + (size_t)(4 * w) * sZ - 1));
+            const u32 o = touched ? __ldcg(colrow + (size_t)(4 * w) * sZ) : BFS_RAWINF;
+            const u32 fr = ((w ? fw1 : fw0) >> lane) & 1u;
+            cXm[w] = (fr && c != BFS_CINV && c < (o >> 1)) ? c : BFS_CINV;
+        }
+    }
+    if (dirty & 2u) { // x+: halo column x0 + 32, own column x0 + 31 (lane 31's cells)
+        const u32 fw0 = __shfl_sync(BFS_FULL, free0, 31), fw1 = __shfl_sync(BFS_FULL, free1, 31);
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+            const u32 c = bfs_cand(__ldcg(colrow + (size_t)(4 * w) * sZ + 32));
+            const u32 o = touched ? __ldcg(colrow + (size_t)(4 * w) * sZ + 31) : BFS_RAWINF;
+            const u32 fr = ((w ? fw1 : fw0) >> lane) & 1u;
+            cXp[w] = (fr && c != BFS_CINV && c < (o >> 1)) ? c : BFS_CINV;
+        }
+    }
+    // corner cells of the y / z faces have two candidates: keep the smaller one in the y array
+    {
+        u32 m;
+        m = cYm[0] < cZm[0] ? cYm[0] : cZm[0]; cYm[0] = m; cZm[0] = BFS_CINV;
+        m = cYp[0] < cZm[7] ? cYp[0] : cZm[7]; cYp[0] = m; cZm[7] = BFS_CINV;
+        m = cYm[7] < cZp[0] ? cYm[7] : cZp[0]; cYm[7] = m; cZp[0] = BFS_CINV;
+        m = cYp[7] < cZp[7] ? cYp[7] : cZp[7]; cYp[7] = m; cZp[7] = BFS_CINV;
+    }
+    // the source cell
+    u32 init0 = 0, init1 = 0;
+    bool src = false;
+    if (old & BFS_SRC) {
+        const int sx = (int)__ldcg(&A.ctr[BFS_C_SRC]) - x0, sy = (int)__ldcg(&A.ctr[BFS_C_SRC + 1]) - y0,
+                  sz = (int)__ldcg(&A.ctr[BFS_C_SRC + 2]) - z0;
+        src = true;
+        if (lane == sx) { if (sz < 4) init0 = 1u << (sz * 8 + sy); else init1 = 1u << ((sz - 4) * 8 + sy); }
+    }
+
+    // ---- pass base = smallest candidate ----
+    u32 base;
+    {
+        u32 m = BFS_CINV;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            m = cYm[i] < m ? cYm[i] : m; m = cYp[i] < m ? cYp[i] : m;
+            m = cZm[i] < m ? cZm[i] : m; m = cZp[i] < m ? cZp[i] : m;
+        }
+        m = cXm[0] < m ? cXm[0] : m; m = cXm[1] < m ? cXm[1] : m;
+        m = cXp[0] < m ? cXp[0] : m; m = cXp[1] < m ? cXp[1] : m;
+        base = __reduce_min_sync(BFS_FULL, m);
+        if (src) base = 0u;
+    }
+
+    u32 low0 = 0, low1 = 0; // cells lowered by this activation
+    u32 redo = 0;           // dirty faces to look at again (seeds beyond the range of one pass)
+    if (base != BFS_CINV) {
+        // ---- bit-sliced seed levels ----
+        BfsSeeds SA, SB;
+        u32 far = 0, lastA = 0, lastB = 0, anyA = 0, anyB = 0;
+#pragma unroll
+        for (int b = 0; b < 6; ++b) SA.sp[b][0] = SA.sp[b][1] = SB.sp[b][0] = SB.sp[b][1] = 0u;
+        SA.sv[0] = SA.sv[1] = SB.sv[0] = SB.sv[1] = 0u;
+        {
+            // relative levels, packed one byte per cell; bit 7 of a byte marks "no seed"
+            u32 pYm[2] = {0, 0}, pYp[2] = {0, 0}, pZm[2] = {0, 0}, pZp[2] = {0, 0};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                pYm[i >> 2] |= bfs_rel(cYm[i], base, far, anyA, lastA) << ((i & 3) * 8);
+                pYp[i >> 2] |= bfs_rel(cYp[i], base, far, anyA, lastA) << ((i & 3) * 8);
+                pZm[i >> 2] |= bfs_rel(cZm[i], base, far, anyA, lastA) << ((i & 3) * 8);
+                pZp[i >> 2] |= bfs_rel(cZp[i], base, far, anyA, lastA) << ((i & 3) * 8);
+            }
+            // y faces: cell (y, z) of word z >> 2 sits at bit (z & 3) * 8 + y: the packed bytes line up
+#pragma unroll
+            for (int w = 0; w < 2; ++w) {
+                const u32 vm = (~pYm[w] >> 7) & 0x01010101u, vp = (~pYp[w] >> 7) & 0x01010101u;
+                SA.sv[w] |= vm | (vp << 7);
+#pragma unroll
+                for (int b = 0; b < 6; ++b)
+                    SA.sp[b][w] |= ((pYm[w] >> b) & vm) | (((pYp[w] >> b) & vp) << 7);
+            }
+            // z faces: cell (y, z = 0) at bit y of word 0, (y, z = 7) at bit 24 + y of word 1
+            {
+                const u32 vm = bfs_compress4(~pZm[0] >> 7) | (bfs_compress4(~pZm[1] >> 7) << 4);
+                const u32 vp = bfs_compress4(~pZp[0] >> 7) | (bfs_compress4(~pZp[1] >> 7) << 4);
+                SA.sv[0] |= vm;
+                SA.sv[1] |= vp << 24;
+#pragma unroll
+                for (int b = 0; b < 6; ++b) {
+                    const u32 nm = bfs_compress4(pZm[0] >> b) | (bfs_compress4(pZm[1] >> b) << 4);
+                    const u32 np = bfs_compress4(pZp[0] >> b) | (bfs_compress4(pZp[1] >> b) << 4);
+                    SA.sp[b][0] |= nm & vm;
+                    SA.sp[b][1] |= (np & vp) << 24;
+                }
+            }
+        }
+        // x faces: the ballots assemble lane 0's (x-) and lane 31's (x+) words
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+            const u32 rm = bfs_rel(cXm[w], base, far, anyB, lastB), rp = bfs_rel(cXp[w], base, far, anyB, lastB);
+            const bool any_x = __any_sync(BFS_FULL, (rm & rp & 0x80u) == 0u);
+            if (any_x) {
+                const u32 vm = __ballot_sync(BFS_FULL, !(rm & 0x80u)), vp = __ballot_sync(BFS_FULL, !(rp & 0x80u));
+                SB.sv[w] = lane == 0 ? vm : (lane == 31 ? vp : 0u);
+#pragma unroll
+                for (int b = 0; b < 6; ++b) {
+                    const u32 bm = __ballot_sync(BFS_FULL, (rm >> b) & 1u & ~(rm >> 7)), bp = __ballot_sync(BFS_FULL, (rp >> b) & 1u & ~(rp >> 7));
+                    SB.sp[b][w] = lane == 0 ? bm : (lane == 31 ? bp : 0u);
+                }
+            }
+        }
+        {
+            const u32 la = __reduce_max_sync(BFS_FULL, lastA), lb = __reduce_max_sync(BFS_FULL, lastB);
+            SA.last = __any_sync(BFS_FULL, anyA != 0u) ? (int)la : -1;
+            SB.last = __any_sync(BFS_FULL, anyB != 0u) ? (int)lb : -1;
+            if (__any_sync(BFS_FULL, far != 0u)) redo = dirty;
+        }
+
+        // ---- sweep, extract, store; continuation passes if a wave outlives the recordable range ----
+        u32 R0 = 0, R1 = 0, pbase = base;
+        for (;;) {
+            u32 rec[BFS_NREC][2];
+            u32 carry0, carry1;
+            const u32 P0 = R0, P1 = R1;
+            cnt.levels += bfs_sweep(free0, free1, SA, SB, init0, init1, R0, R1, rec, carry0, carry1, lane);
+            ++cnt.passes;
+            if (touched) bfs_extract<true>(rec, R0 & ~P0, R1 & ~P1, pbase, cell0, inx, sY, sZ, low0, low1);
+            else bfs_extract<false>(rec, R0 & ~P0, R1 & ~P1, pbase, cell0, inx, sY, sZ, low0, low1);
+            touched = true;
+            if (!__any_sync(BFS_FULL, (carry0 | carry1) != 0u)) break;
+            init0 = carry0; init1 = carry1;
+            pbase += BFS_LIM;
+            SA.last = -1; SB.last = -1;
+        }
+        cnt.lowered += (u32)(__popc(low0) + __popc(low1));
+    } else {
+        ++cnt.idle;
+    }
+
+    // ---- publish: every store above is visible before a neighbour is armed ----
+    __threadfence();
+    __syncwarp();
+    u32 arms = 0;
+    arms |= (__any_sync(BFS_FULL, lane == 0 && ((low0 & xmf0) | (low1 & xmf1)) != 0u) ? 1u : 0u) << 0;
+    arms |= (__any_sync(BFS_FULL, lane == 31 && ((low0 & xpf0) | (low1 & xpf1)) != 0u) ? 1u : 0u) << 1;
+    arms |= (__any_sync(BFS_FULL, ((low0 & ymf0) | (low1 & ymf1)) != 0u) ? 1u : 0u) << 2;
+    arms |= (__any_sync(BFS_FULL, ((low0 & ypf0) | (low1 & ypf1)) != 0u) ? 1u : 0u) << 3;
+    arms |= (__any_sync(BFS_FULL, (low0 & zmf) != 0u) ? 1u : 0u) << 4;
+    arms |= (__any_sync(BFS_FULL, (low1 & zpf) != 0u) ? 1u : 0u) << 5;
+
+    // lanes 1..6 arm the six neighbours, lane 0 releases the tile -- all in parallel
+    bool need_push = false, requeue = false;
+    u32 ntile = 0;
+    bool remote = false;
+    if (lane >= 1 && lane <= 6 && ((arms >> (lane - 1)) & 1u)) {
+        const int f = lane - 1;
+        const int nx = bx + (f == 0 ? -1 : (f == 1 ? 1 : 0)), ny = by + (f == 2 ? -1 : (f == 3 ? 1 : 0));
+        const int nz = bz + (f == 4 ? -1 : (f == 5 ? 1 : 0));
+        const u32 bit = (1u << (f ^ 1)) | BFS_Q;
+        if (nz < 0 || nz >= A.nbz) { // the neighbour tile lives on the peer GPU
+            const BfsPeer &P = nz < 0 ? A.lo : A.hi;
+            ntile = (u32)((P.bzadj * A.nby + ny) * A.nbx + nx);
+            remote = true;
+            const u32 was = atomicOr(&P.state[ntile], bit);
+            if (!(was & BFS_Q)) {
+                // queue it over there: first make the peer (and, if it was idle, the set of active
+                // ranks) count the tile, then hand it over
+                if (atomicAdd(&P.ctr[BFS_C_INFLIGHT], 1u) == 0u)
+                    cnt.remote += atomicAdd(A.active, 1u) == 0xFFFFFFFFu; // the returned value: performed before we go on
+                __threadfence_system();
+                bfs_push(P.ring, P.ring_cap, P.ctr, ntile);
+                ++cnt.remote;
+            }
+        } else {
+            ntile = (u32)((nz * A.nby + ny) * A.nbx + nx);
+            const u32 was = atomicOr(&A.state[ntile], bit);
+            need_push = !(was & BFS_Q);
+        }
+    }
+    if (lane == 0) {
+        const u32 tbit = touched ? BFS_T : 0u; // the tile's words are initialised from now on
+        if (redo) {
+            atomicOr(&A.state[t], redo | tbit);
+            requeue = true;
+        } else {
+            const u32 expect = BFS_Q | (old & BFS_T);
+            const u32 was = atomicCAS(&A.state[t], expect, tbit);
+            if (was != expect) { // new dirty faces arrived meanwhile: stay queued
+                if (tbit) atomicOr(&A.state[t], tbit);
+                requeue = true;
+            }
+        }
+    }
+    (void)remote;
+    const u32 pushes = __ballot_sync(BFS_FULL, need_push || requeue);
+    const int np = __popc(pushes);
+    if (np >= 2) {
+        if (lane == 0) { atomicAdd(&A.ctr[BFS_C_INFLIGHT], (u32)(np - 1)); __threadfence(); }
+        __syncwarp();
+    }
+    if (need_push) bfs_push(A.ring, A.ring_cap, A.ctr, ntile);
+    if (requeue) { bfs_push(A.ring, A.ring_cap, A.ctr, t); ++cnt.redo; }
+    if (np == 0 && lane == 0) {
+        if (atomicSub(&A.ctr[BFS_C_INFLIGHT], 1u) == 1u) bfs_rank_idle(A);
+    }
+    __syncwarp();
+}
+
+// ---- persistent warp loop --------------------------------------------------------------------------
+__device__ static inline void bfs_warp_main(const BfsArgs &A, const int lane) {
+    BfsCount cnt;
+    cnt.act = cnt.idle = cnt.lowered = cnt.levels = cnt.passes = cnt.redo = cnt.remote = 0;
+    for (;;) {
+        u32 item = 0;
+        if (lane == 0) item = bfs_pop(A);
+        item = __shfl_sync(BFS_FULL, item, 0);
+        if (item == 0u) break;
+        bfs_process_tile(A, item - 1u, lane, cnt);
+    }
+    cnt.lowered = __reduce_add_sync(BFS_FULL, cnt.lowered); // per-lane counters
+    cnt.remote = __reduce_add_sync(BFS_FULL, cnt.remote);
+    if (lane == 0 && A.stats) {
+        if (cnt.act) {
+            atomicAdd((unsigned long long *)&A.stats[1], (unsigned long long)cnt.act);
+            atomicAdd((unsigned long long *)&A.stats[2], (unsigned long long)cnt.lowered);
+            atomicAdd((unsigned long long *)&A.stats[3], (unsigned long long)cnt.lowered * 6ull);
+            atomicAdd((unsigned long long *)&A.stats[12], (unsigned long long)cnt.levels);
+            atomicAdd((unsigned long long *)&A.stats[13], (unsigned long long)cnt.idle);
+            atomicAdd((unsigned long long *)&A.stats[14], (unsigned long long)cnt.passes);
+            atomicAdd((unsigned long long *)&A.stats[5], (unsigned long long)cnt.redo);
+            atomicAdd((unsigned long long *)&A.stats[7], (unsigned long long)cnt.remote);
+        }
+    }
+}
+
+// after the search: tiles that were never touched hold no values yet -> all-ones (unreached)
+__device__ static inline void bfs_fill_tile(const BfsArgs &A, const u32 t, const int lane) {
+    const GridDev &Gd = A.G;
+    const int bx = (int)(t % (u32)A.nbx), by = (int)((t / (u32)A.nbx) % (u32)A.nby), bz = (int)(t / ((u32)A.nbx * (u32)A.nby));
+    const size_t sY = (size_t)Gd.PX, sZ = (size_t)Gd.PX * Gd.PY;
+    if (bx * 32 + lane >= Gd.PX) return;
+    u32 *cell0 = A.g + (size_t)(bz * 8) * sZ + (size_t)(by * 8) * sY + (size_t)(bx * 32 + lane);
+#pragma unroll
+    for (int z = 0; z < 8; ++z)
+#pragma unroll
+        for (int y = 0; y < 8; ++y) bfs_store(cell0 + (size_t)z * sZ + (size_t)y * sY, BFS_RAWINF);
+}

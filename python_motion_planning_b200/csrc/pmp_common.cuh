@@ -5,11 +5,10 @@
 #include <stdint.h>
 
 #include "../../include/pmp_b200.h"
+#include "pmp_griddev.h"
 
 #define PMP_MAXM 26
 
-typedef unsigned long long u64;
-typedef uint32_t u32;
 
 #define KEY_INF (~0ull)
 
@@ -27,18 +26,6 @@ struct Motions {
     u32 wi[PMP_MAXM];     // integer cost (u32 fields)
     double w[PMP_MAXM];   // cost accumulated along a path
     double len[PMP_MAXM]; // Euclidean length of the offset (Planner.dist, planner.py:22-23)
-};
-
-struct GridDev {
-    int ndim;
-    int X, Y, Z;       // box
-    int PX, PY, PZ;    // padded to whole tiles
-    int TX, TY, TZ;    // tile
-    int ntx, nty, ntz; // tiles per axis
-    int wpr;           // 32-bit words per bitmask row
-    u32 ntiles;
-    u64 pcells;
-    const u32 *bits; // occupancy, 1 = blocked; row (y,z) at ((z*PY)+y)*wpr
 };
 
 struct pmp_grid {

@@ -133,7 +133,8 @@ struct SsspArgs {
     u64 *T[2];
     int *done;
     u32 *goalcell; // padded cell index of each goal (0xFFFFFFFF = none)
-    u32 *ctr;      // per round parity p: [p] ring tail, [2+p] ring head, [4+p] live tiles, [6+p] tiles in flight
+    u32 *ctr;      // per round parity p: [p] ring tail, [2+p] ring head, [4+p] live tiles, [6+p] tiles in flight;
+                   // [8] abort flag (a ring wait timed out: the result is invalid), [9] the search ran out of live tiles
     u64 *stats;    // 16 counters, see include/pmp_b200.h (pmp_sssp)
     double window, sub, he, hm;
     int nbands;   // > 1: the ring is split into key bands served lowest first (single A-star queries)
@@ -797,19 +798,19 @@ __device__ void banded_pop(const SsspArgs &A, const int cur, TileSmem<C> &S) {
             if (lane == 0) {
                 u32 *slot = &A.wl[0][(size_t)b * A.ring_cap + ticket % A.ring_cap];
                 unsigned w = 0;
-                while ((v = ld_cg(slot)) == 0 && ++w < (1u << 24)) { } // the push of this ticket is in flight
+                while ((v = ld_cg(slot)) == 0 && ++w < (1u << 24) && !ld_cg(&A.ctr[8])) { } // the push of this ticket is in flight
                 if (v) { fence_gpu(); *(volatile u32 *)slot = 0; }
-                else A.stats[15] = 0xDEADu;
+                else atomicOr(&A.ctr[8], 1u); // timed out: abort the search (k_sssp_finish reports PMP_ST_ERROR)
             }
             bsel = b;
             break;
         }
         int fl = 0;
-        if (lane == 0) fl = ld_cg(&A.ctr[6 + cur]) == 0;
-        if (__shfl_sync(0xFFFFFFFFu, fl, 0)) break; // nothing queued or being processed: nobody can append
+        if (lane == 0) fl = ld_cg(&A.ctr[6 + cur]) == 0 || ld_cg(&A.ctr[8]) != 0;
+        if (__shfl_sync(0xFFFFFFFFu, fl, 0)) break; // nothing queued or being processed (or aborted): nobody can append
         __nanosleep(ns);
         if (ns < 160) ns *= 2;
-        if (++spins > (1u << 22)) { if (lane == 0) A.stats[15] = 0xDEADu; break; } // safety net (seconds)
+        if (++spins > (1u << 22)) { if (lane == 0) atomicOr(&A.ctr[8], 1u); break; } // safety net (seconds): abort
     }
     if (lane == 0) {
         S.item = v;
@@ -888,7 +889,13 @@ __global__ void __launch_bounds__(NT, MINB) k_sssp(const __grid_constant__ SsspA
 
         const u32 live = ld_cg(&A.ctr[4 + cur]);
         if (timer) { const u64 tb = globaltimer_ns(); S.tm[1] += tb - S.tm[4]; S.tm[4] = tb; }
-        if (live == 0) break;
+        if (ld_cg(&A.ctr[8])) break; // a ring wait timed out in the last round (uniform: read after the grid barrier)
+        if (live == 0) {
+            // nothing pending below the key cap.  Without a cap that means every query still
+            // running has settled all it can reach (k_sssp_finish turns it into EXHAUSTED / REACHED).
+            if (blockIdx.x == 0 && tid == 0 && A.key_cap == KEY_INF) A.ctr[9] = 1u;
+            break;
+        }
         if (A.max_rounds > 0 && r >= A.max_rounds) break;
 
         // ---- per-query bookkeeping: termination, next window ----
@@ -937,10 +944,10 @@ __global__ void __launch_bounds__(NT, MINB) k_sssp(const __grid_constant__ SsspA
                 for (;;) {
                     v = ld_cg(slot);
                     if (v) break;
-                    if (ld_cg(&A.ctr[6 + cur]) == 0) break; // nothing in flight: nobody can append
+                    if (ld_cg(&A.ctr[6 + cur]) == 0 || ld_cg(&A.ctr[8])) break; // nothing in flight (or aborted): nobody can append
                     __nanosleep(ns);
                     if (ns < 160) ns *= 2;
-                    if (++spins > (1u << 22)) { A.stats[15] = 0xDEADu; break; } // safety net (seconds)
+                    if (++spins > (1u << 22)) { atomicOr(&A.ctr[8], 1u); break; } // safety net (seconds): abort
                 }
 #ifdef PMP_POPSTAT
                 if (v) { S.stat[13] += (u64)(clock64() - pt0); S.stat[14] += spins == 0; S.stat[15] += 1; }
@@ -964,7 +971,7 @@ __global__ void __launch_bounds__(NT, MINB) k_sssp(const __grid_constant__ SsspA
         }
     }
     __syncthreads();
-    if (tid < 16 && tid != 0 && tid != 4 && (tid < 8 || tid >= 12) && S.stat[tid]) atomicAdd(&A.stats[tid], S.stat[tid]);
+    if (tid < 15 && tid != 0 && tid != 4 && (tid < 8 || tid >= 12) && S.stat[tid]) atomicAdd(&A.stats[tid], S.stat[tid]); // [15] = error flag
     if (timer) {
         A.stats[8] = globaltimer_ns() - S.tm[0];
         A.stats[9] = S.tm[1]; A.stats[10] = S.tm[2]; A.stats[11] = S.tm[3];
@@ -1013,6 +1020,7 @@ __global__ void k_sssp_finish(SsspArgs A, double *gcost, int32_t *status) {
     typedef typename W::G G;
     for (u32 q = blockIdx.x * blockDim.x + threadIdx.x; q < A.nq; q += gridDim.x * blockDim.x) {
         int st = A.done[q];
+        if (st == PMP_ST_RUNNING && A.ctr[9]) st = PMP_ST_EXHAUSTED; // ran out of pending keys (REACHED below if the goal has a value)
         double c = __longlong_as_double(0x7ff0000000000000LL);
         const u32 gc = A.goalcell[q];
         if (st != PMP_ST_BAD_QUERY && gc != 0xFFFFFFFFu) {
@@ -1024,9 +1032,14 @@ __global__ void k_sssp_finish(SsspArgs A, double *gcost, int32_t *status) {
                 st = PMP_ST_EXHAUSTED;
             }
         }
+        if (A.ctr[8] && st != PMP_ST_BAD_QUERY) { // aborted: whatever g[goal] holds is not trustworthy
+            st = PMP_ST_ERROR;
+            c = __longlong_as_double(0x7ff0000000000000LL);
+        }
         if (gcost) gcost[q] = c;
         if (status) status[q] = st;
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) A.stats[15] = A.ctr[8];
 }
 
 __global__ void k_field_finalize(u64 *g, size_t n) {
@@ -1265,6 +1278,11 @@ static void fill_args(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const i
 
 }
 
+// pmp_bfs.cu: warp-per-tile solver for full fields on 6-connected unit-weight 3D grids
+bool pmp_bfs_applicable(const pmp_grid *g);
+int pmp_bfs_field(pmp_grid *g, const int32_t *start_dev, void *g_dev, void *ws_dev, int64_t ws_bytes,
+                  double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream);
+
 static int sssp_from_scratch(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, const int32_t *starts_dev,
                              const int32_t *goals_dev, void *g_dev, void *ws_dev, int64_t ws_bytes,
                              double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream,
@@ -1293,6 +1311,11 @@ static int sssp_from_scratch(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, 
         return -1;
     }
     cudaStream_t s = (cudaStream_t)stream;
+    // One full field, integer words, exactly the six unit moves: the warp-per-tile level solver
+    // (pmp_bfs.cu) -- no field fill, no key windows.  PMP_B200_OLD_BFS=1 keeps the tiled kernel.
+    if (nq == 1 && P->full_field && P->weight == PMP_W_U32 && !no_prune && pmp_bfs_applicable(g) &&
+        !getenv("PMP_B200_OLD_BFS"))
+        return pmp_bfs_field(g, starts_dev, g_dev, ws_dev, ws_bytes, gcost_dev, status_dev, stats_dev, stream);
     SsspArgs A;
     fill_args(g, P, nq, starts_dev, goals_dev, g_dev, ws_dev, L, A, no_prune);
     const size_t gsz = (size_t)nq * g->d.pcells * (P->weight == PMP_W_F64 ? 8 : 4);
@@ -1360,6 +1383,7 @@ __global__ void k_slab_arm(SsspArgs A, u64 cap) {
     A.done[0] = 0;
     A.goalcell[0] = 0xFFFFFFFFu;
     for (int i = 0; i < 16; ++i) A.ctr[i] = 0;
+    A.stats[0] = 0; // k_slab_export picks the qmin parity from the rounds of THIS run
 }
 
 __global__ void k_slab_export(SsspArgs A, u64 *out) {
@@ -1368,6 +1392,7 @@ __global__ void k_slab_export(SsspArgs A, u64 *out) {
     out[1] = A.stats[0];
     out[2] = A.stats[1];
     out[3] = A.stats[2];
+    out[5] = A.ctr[8]; // non-zero: a ring wait timed out, the slab state is invalid
 }
 
 template <class C>

@@ -109,6 +109,12 @@ def sssp(ws, algo, heuristic=0, full_field=False, window=0.0, max_rounds=0, have
                              ws.status.data_ptr(), ws.stats.data_ptr(), dg.stream()), "pmp_sssp")
 
 
+def check_field_status(ws):
+    """synchronising check of the status words of the last search in ws: raises PmpError when the
+    kernel aborted (PMP_ST_ERROR) -- for callers that keep the field on the device"""
+    _lib.check_status(ws.status.cpu().numpy(), "search")
+
+
 def extract_paths(ws, path_cap):
     dg = ws.dg
     ws.ensure_path(path_cap)

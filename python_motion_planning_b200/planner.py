@@ -198,10 +198,16 @@ class _SearchMixin:
     def _heuristic_id(self):
         return _lib.H_MANHATTAN if self.heuristic_type == "manhattan" else _lib.H_EUCLIDEAN
 
-    def _prepare(self):
-        dg = self.env.device_grid()
+    def _install_motions(self, dg):
+        """this planner's motion table and edge rule on the (shared) device grid; returns the
+        installed (motion key, corner-cutting flag)"""
         offsets, costs = motion_table(self.env if self.motions is self.env.motions else self, self._ndim)
         dg.set_motions(offsets, costs, cut=getattr(self, "_cut", False))
+        return dg._motion_key, getattr(dg, "_cut", False)
+
+    def _prepare(self):
+        dg = self.env.device_grid()
+        self._install_motions(dg)
         return dg
 
     def _no_path(self, expand):
@@ -228,6 +234,7 @@ class _SearchMixin:
         self.last_field = ws
         res = ws.host_res
         gcost, cost, plen, status = float(res[0]), float(res[1]), int(res[2]), int(res[3])
+        _lib.check_status(status, str(self))
         if status == _lib.ST_BAD_QUERY:
             return self._no_path(self._expand_view(ws, None))
         if plen == -1:                         # path longer than the first guess: retry full size

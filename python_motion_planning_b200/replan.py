@@ -232,14 +232,24 @@ class _ReplanMixin:
         """lpa_star.py:78-89 / lpa_star3d.py:88-92: (cost, path start -> goal, expand)."""
         if self.reference_order:
             return self._ref_plan()
+        if self._session is not None and self._reinstall() != self._session_key:
+            self._session = None       # the motion table changed under the resident field: search again
         if self._session is None:
             dg = self._prepare()
+            self._session_key = (dg._motion_key, getattr(dg, "_cut", False))
             self._session = ReplanSession(dg, self._algo, self._heuristic_id(), scratch_cells=self._scratch_cells)
             self._session.begin(self.start.current, self.goal.current)
             self._result = None
         if self._result is None:
             self._result = self._collect()
         return self._result
+
+    def _reinstall(self):
+        """The pmp_grid handle is shared by every planner of the environment, and the repair and
+        the path walk read its motion table: put this planner's table and edge rule back before
+        any of them runs (another planner -- JPS with corner cutting, a filtered motion set --
+        may have planned on the same env in between)."""
+        return self._install_motions(self._session.ws.dg)
 
     def apply_change(self, coord: tuple, blocked=None) -> tuple:
         """lpa_star3d.py:98-133 (2D: the body of OnPress, lpa_star.py:112-127).  blocked = None
@@ -255,7 +265,8 @@ class _ReplanMixin:
         flags = [bool(b) for b in (blocked if hasattr(blocked, "__len__") else [blocked] * len(coords))]
         if self.reference_order:
             return self._ref_changes(coords, flags)
-        if self._session is None:
+        if self._session is None or self._reinstall() != self._session_key:
+            self._session = None
             self.plan()
         self._edit_host_map(coords, flags)
         self.info = self._session.update(np.array(coords, dtype=np.int32).reshape(-1, self._ndim), flags)
@@ -301,6 +312,7 @@ class _ReplanMixin:
         ws = self._session.ws
         dg = ws.dg
         t = dg.torch
+        self._reinstall()
         engine.extract_paths(ws, self._path_cap(dg))
         res = t.stack([ws.gcost[0], ws.cost[0], ws.path_len[0].to(t.float64),
                        ws.status[0].to(t.float64)]).cpu()
@@ -315,6 +327,7 @@ class _ReplanMixin:
         if self._ndim == 3:                                # the 2D planner returns None (lpa_star.py:89)
             expand = self._expand_view(ws, gcost if math.isfinite(gcost) else None)
             self.EXPAND = expand
+        _lib.check_status(status, str(self))
         if status == _lib.ST_BAD_QUERY or plen <= 0:
             return float("inf"), [], expand
         cells = ws.path[0, :plen].cpu().numpy()

@@ -104,6 +104,8 @@ class CudaSlabEngine:
     def pending(self):
         """(smallest pending key incl. merged cells, cells improved by merges) -- one D2H"""
         o = self.out.cpu()
+        if int(o[5].item()):
+            raise _lib.PmpError("pmp_slab_run: the search kernel aborted (queue wait timed out)")
         return self._key(o[0].item()), int(o[4].item())
 
     def stats(self):
