@@ -35,7 +35,7 @@ extern "C" {
 #endif
 
 /* 2: + pmp_bestfirst, pmp_lpa_star, pmp_d_star (additive; every version-1 entry point is unchanged) */
-#define PMP_B200_ABI_VERSION 2
+#define PMP_B200_ABI_VERSION 3
 
 typedef struct pmp_grid pmp_grid; /* opaque: occupancy bitmask + motion table on one device */
 
@@ -83,6 +83,11 @@ int pmp_grid_set_dense(pmp_grid *g, const uint8_t *occ_dev, void *stream);
  * the memory layout of a C-ordered array indexed [x, y(, z)] like the reference's coordinate
  * tuples; transposed on the fly, no host-side or extra device pass. */
 int pmp_grid_set_dense_xyz(pmp_grid *g, const uint8_t *occ_dev, void *stream);
+/* Occupancy already packed by the caller: rows_dev = [Z][Y][ceil(X/32)] 32-bit words, bit i of
+ * word w <-> x = 32 w + i, 1 = obstacle (numpy: np.packbits(occ.transpose(2, 1, 0), axis=-1,
+ * bitorder="little") viewed as uint32 when X is a multiple of 32).  1/8 of the bytes of the dense
+ * forms; 2D grids: Z = 1. */
+int pmp_grid_set_packed(pmp_grid *g, const uint32_t *rows_dev, void *stream);
 /* Toggle single cells without rebuilding (obstacle edits between plans). value: 1 block, 0 free */
 int pmp_grid_edit_cells(pmp_grid *g, const int32_t *coords_dev, int64_t n, int value, void *stream);
 /* Copy the device bitmask to host: words_per_row * PY * PZ uint32 (bit x%32 of word x/32). Synchronous. */
@@ -262,6 +267,40 @@ int pmp_slab_run(pmp_grid *g, const pmp_sssp_params *params, void *g_dev, void *
  * to out_dev[4]); mark = 0: values only (refreshing a ghost plane). */
 int pmp_slab_merge(pmp_grid *g, int weight, void *g_dev, void *ws_dev, int64_t ws_bytes,
                    int z_local, int mark, const void *plane_dev, uint64_t *out_dev, void *stream);
+
+/* ---- z-slabs with device-side halo exchange (round 2): the unit-weight field of BASELINE.json
+ *      config 5 (6-connected, cost 1: the field Dijkstra3D.plan computes with env.motions filtered
+ *      to the unit moves, dijkstra3d.py:39-126) split over up to 8 GPUs of one node.  Rank p owns
+ *      planes [z0, z1) as its LOCAL grid (no ghost planes; every slab but the last a multiple of
+ *      8 planes).  Field + workspace live in one arena per rank that the other ranks map through
+ *      CUDA IPC; the search kernel (csrc/pmp_bfs_core.cuh) reads the z halo of a boundary tile
+ *      straight from the neighbour GPU's field over NVLink and arms / queues the neighbour's
+ *      tiles with remote atomics.  No host round trip and no NCCL call inside a search: the host
+ *      brackets one kernel launch per rank with two barriers.
+ *      Protocol (python_motion_planning_b200/slab.py, BfsSlabSolver): create; export; all-gather
+ *      the (handle, info) pairs (torch.distributed); connect; then per search: begin, barrier,
+ *      run, barrier.  SURVEY.md 8(b) sketched "pmp_slab_* taking an ncclComm_t": the exchange
+ *      itself needs no communicator, only the peers' mapped arenas. ---- */
+typedef struct pmp_bfs_slab pmp_bfs_slab;
+int pmp_bfs_slab_create(pmp_grid *g_local, int rank, int world, pmp_bfs_slab **out);
+int pmp_bfs_slab_destroy(pmp_bfs_slab *s);
+/* handle64: 64 bytes (cudaIpcMemHandle_t of the arena); info8: 8 x int64 layout words */
+int pmp_bfs_slab_export(pmp_bfs_slab *s, void *handle64, int64_t *info8);
+/* handles: world x 64 bytes, infos: world x 8 int64, both ordered by rank (own entry ignored) */
+int pmp_bfs_slab_connect(pmp_bfs_slab *s, const void *handles, const int64_t *infos);
+/* several slabs held by ONE process on one device (tests, or a grid cut for other reasons) */
+int pmp_bfs_slab_connect_local(pmp_bfs_slab **slabs, int n);
+/* reset + queue the source tile; start_local_dev = the source in local coordinates if it lies in
+ * this slab, else NULL.  All ranks must complete this (stream sync + barrier) before any runs. */
+int pmp_bfs_slab_begin(pmp_bfs_slab *s, const int32_t *start_local_dev, int32_t *status_dev, void *stream);
+/* one launch: search to global termination, fill never-touched tiles, counters -> stats_dev (16 x
+ * uint64, layout of pmp_sssp's stats) and PMP_ST_EXHAUSTED / PMP_ST_ERROR -> status_dev */
+int pmp_bfs_slab_run(pmp_bfs_slab *s, int32_t *status_dev, uint64_t *stats_dev, void *stream);
+/* connect_local'ed slabs: ONE launch serves all of them (synchronous) */
+int pmp_bfs_slab_run_group(pmp_bfs_slab **slabs, int n, void *stream);
+/* device pointers into the arena: the field (padded local box, (value << 1 | 1) words, all-ones =
+ * unreached), its size, the 16 counters and the control block */
+int pmp_bfs_slab_buffers(pmp_bfs_slab *s, void **field_dev, int64_t *field_bytes, void **stats_dev, void **ctr_dev);
 
 /* ---- incremental replanning on a resident field.  Replaces the repair loop
  *      of the reference's incremental planners: LPAStar.OnPress / LPAStar3D.apply_change +

@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PMP_B200_LIB") or os.path.join(_HERE, "libpmp_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
 
-ABI_VERSION = 2                              # PMP_B200_ABI_VERSION this binding was written against
+ABI_VERSION = 3                              # PMP_B200_ABI_VERSION this binding was written against
 ASTAR, DIJKSTRA, GBFS = 0, 1, 2
 THETA_STAR, LAZY_THETA_STAR, JPS = 3, 4, 5    # pmp_bestfirst only
 BESTFIRST_HEAP_REC_BYTES = 40
@@ -32,12 +32,15 @@ def check_status(status, what="search"):
 SYMBOLS = (
     "pmp_last_error", "pmp_abi_version", "pmp_device_count",
     "pmp_grid_create", "pmp_grid_destroy", "pmp_grid_layout", "pmp_grid_set_cells",
-    "pmp_grid_set_dense", "pmp_grid_set_dense_xyz", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
+    "pmp_grid_set_dense", "pmp_grid_set_dense_xyz", "pmp_grid_set_packed", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
     "pmp_grid_set_motions", "pmp_grid_set_corner_cutting", "pmp_sssp_sizes", "pmp_sssp", "pmp_field_finalize",
     "pmp_count_settled", "pmp_extract_paths", "pmp_verify_field", "pmp_gbfs", "pmp_bestfirst",
     "pmp_lpa_star", "pmp_d_star",
     "pmp_slab_begin", "pmp_slab_run", "pmp_slab_merge", "pmp_replan_begin", "pmp_replan_update",
     "pmp_line_of_sight", "pmp_shortcut_paths",
+    "pmp_bfs_slab_create", "pmp_bfs_slab_destroy", "pmp_bfs_slab_export", "pmp_bfs_slab_connect",
+    "pmp_bfs_slab_connect_local", "pmp_bfs_slab_begin", "pmp_bfs_slab_run", "pmp_bfs_slab_run_group",
+    "pmp_bfs_slab_buffers",
 )
 
 
@@ -94,6 +97,7 @@ def lib():
         "pmp_grid_set_cells": [vp, vp, i64, vp],
         "pmp_grid_set_dense": [vp, vp, vp],
         "pmp_grid_set_dense_xyz": [vp, vp, vp],
+        "pmp_grid_set_packed": [vp, vp, vp],
         "pmp_grid_edit_cells": [vp, vp, i64, i32, vp],
         "pmp_grid_read_bits": [vp, vp, i64],
         "pmp_grid_count_free": [vp, vp],
@@ -112,6 +116,15 @@ def lib():
         "pmp_slab_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, i64, vp],
         "pmp_slab_run": [vp, ctypes.POINTER(SsspParams), vp, vp, i64, dbl, vp, vp],
         "pmp_slab_merge": [vp, i32, vp, vp, i64, i32, i32, vp, vp, vp],
+        "pmp_bfs_slab_create": [vp, i32, i32, ctypes.POINTER(vp)],
+        "pmp_bfs_slab_destroy": [vp],
+        "pmp_bfs_slab_export": [vp, vp, vp],
+        "pmp_bfs_slab_connect": [vp, vp, vp],
+        "pmp_bfs_slab_connect_local": [vp, i32],
+        "pmp_bfs_slab_begin": [vp, vp, vp, vp],
+        "pmp_bfs_slab_run": [vp, vp, vp, vp],
+        "pmp_bfs_slab_run_group": [vp, i32, vp],
+        "pmp_bfs_slab_buffers": [vp, vp, vp, vp, vp],
         "pmp_line_of_sight": [vp, i64, vp, vp, vp, vp],
         "pmp_shortcut_paths": [vp, i64, vp, i64, vp, vp, vp, vp, vp],
         "pmp_replan_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, vp, i64, vp, vp, vp, vp],

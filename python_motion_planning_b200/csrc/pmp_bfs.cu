@@ -19,7 +19,7 @@
 #define BFS_RING_SLACK 8192
 
 __global__ void __launch_bounds__(BFS_NT, BFS_MINB) k_bfs(const __grid_constant__ BfsArgs A) {
-    bfs_warp_main(A, (int)(threadIdx.x & 31));
+    bfs_warp_main(A, (int)(threadIdx.x & 31), blockIdx.x == 0 && threadIdx.x < 32);
     if ((threadIdx.x & 31) == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[10], (unsigned long long)bfs_now_ns());
 }
 
@@ -43,7 +43,7 @@ __global__ void k_bfs_init(BfsArgs A, const int32_t *start, int32_t *status) {
             A.ctr[BFS_C_SRC] = (u32)sx; A.ctr[BFS_C_SRC + 1] = (u32)sy; A.ctr[BFS_C_SRC + 2] = (u32)sz;
         } else {
             st = PMP_ST_BAD_QUERY;
-            for (int r = 0; r < A.world; ++r) A.peer_ctr[r][BFS_C_DONE] = 1u; // nothing to search
+            A.ctr[BFS_C_SRC + 3] = 1u; // nothing to search: the first warp of k_bfs ends the search on every rank
         }
     }
     if (status) *status = st;
@@ -122,6 +122,9 @@ static void bfs_fill_args(const pmp_grid *g, void *g_dev, void *ws_dev, const Bf
     A.active = A.ctr + BFS_C_ACTIVE;
     const char *e = getenv("PMP_B200_BFS_TIMEOUT_MS");
     A.timeout_ns = (u64)(e ? atoll(e) : 20000) * 1000000ull;
+    // a tile is activated a few times; a search that pops 64x its tiles is stuck (abort with PMP_ST_ERROR)
+    const u64 budget = 64ull * L.ntiles + (1ull << 20);
+    A.max_pops = budget > 0xFFFFFFF0ull ? 0u : (u32)budget;
 }
 
 static int bfs_grid_blocks(int *out) {
@@ -182,5 +185,230 @@ int pmp_bfs_field(pmp_grid *g, const int32_t *start_dev, void *g_dev, void *ws_d
     if (bfs_launch_fill(A, s)) return -2;
     k_bfs_finish<<<1, 1, 0, s>>>(A, gcost_dev, status_dev, (u64 *)stats_dev);
     PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// z-slabs over several GPUs (BASELINE.json config 5).
+//
+// Rank p owns the planes [z0, z1) of the grid (z0, z1 multiples of 8 except the last z1) as its
+// LOCAL box -- no ghost planes.  Field and workspace live in one cudaMalloc'ed arena per rank,
+// exported with cudaIpcGetMemHandle and mapped by the other ranks: the tiles of the lowest /
+// highest tile row read their z halo straight out of the neighbour GPU's field (NVLink loads)
+// and arm / queue the neighbour's tiles with remote atomics (pmp_bfs_core.cuh).  One kernel
+// launch per rank per search; the host only brackets it with two barriers (every rank has
+// reset its workspace before any rank searches; every rank has finished before any resets).
+// Several slabs can also be held by ONE process on one GPU (pmp_bfs_slab_connect_local +
+// pmp_bfs_slab_run_group): one launch serves all of them, so no kernel ever waits for another
+// launch -- the single-GPU test of the same protocol.
+// ---------------------------------------------------------------------------------------------
+#define BFS_INFO_WORDS 8
+#define BFS_MAX_RANKS 8
+
+struct pmp_bfs_slab {
+    pmp_grid *grid;
+    int rank, world;
+    char *arena;
+    size_t arena_bytes, field_bytes;
+    BfsLayout L;
+    BfsArgs A;
+    void *peer_base[BFS_MAX_RANKS];
+    bool connected;
+};
+
+static BfsLayout bfs_layout_tiles(int nbx, int nby, int nbz) {
+    BfsLayout L;
+    L.nbx = nbx; L.nby = nby; L.nbz = nbz;
+    L.ntiles = (u32)((size_t)nbx * nby * nbz);
+    L.ring_cap = L.ntiles + BFS_RING_SLACK;
+    size_t o = 0;
+    L.state = o; o = bfs_align(o + (size_t)L.ntiles * 4);
+    L.ring = o; o = bfs_align(o + (size_t)L.ring_cap * 4);
+    L.ctr = o; o = bfs_align(o + BFS_C_WORDS * 4);
+    L.stats = o; o = bfs_align(o + 16 * 8);
+    L.total = o;
+    return L;
+}
+
+extern "C" int pmp_bfs_slab_create(pmp_grid *g, int rank, int world, pmp_bfs_slab **out) {
+    if (!g || !out || world < 1 || world > BFS_MAX_RANKS || rank < 0 || rank >= world) {
+        pmp_set_error("pmp_bfs_slab_create: bad arguments (1 <= world <= %d)", BFS_MAX_RANKS);
+        return -1;
+    }
+    if (!pmp_bfs_applicable(g)) {
+        pmp_set_error("pmp_bfs_slab_create: needs a 3D grid whose motion table is the six unit moves");
+        return -1;
+    }
+    if (rank < world - 1 && g->d.Z % 8) {
+        pmp_set_error("pmp_bfs_slab_create: every slab but the last must hold a multiple of 8 planes (got %d)", g->d.Z);
+        return -1;
+    }
+    pmp_bfs_slab *s = new pmp_bfs_slab();
+    memset(s, 0, sizeof *s);
+    s->grid = g; s->rank = rank; s->world = world;
+    s->L = bfs_layout(g);
+    s->field_bytes = bfs_align((size_t)g->d.pcells * 4);
+    s->arena_bytes = s->field_bytes + s->L.total;
+    cudaError_t e = cudaMalloc(&s->arena, s->arena_bytes);
+    if (e != cudaSuccess) {
+        pmp_set_error("pmp_bfs_slab_create: cudaMalloc(%zu B): %s", s->arena_bytes, cudaGetErrorString(e));
+        delete s;
+        return -2;
+    }
+    bfs_fill_args(g, s->arena, s->arena + s->field_bytes, s->L, s->A);
+    s->A.rank = rank; s->A.world = world;
+    s->A.peer_ctr[rank] = s->A.ctr;
+    if (world == 1) s->connected = true;
+    *out = s;
+    return 0;
+}
+
+extern "C" int pmp_bfs_slab_destroy(pmp_bfs_slab *s) {
+    if (!s) return 0;
+    for (int r = 0; r < BFS_MAX_RANKS; ++r)
+        if (s->peer_base[r]) cudaIpcCloseMemHandle(s->peer_base[r]);
+    cudaFree(s->arena);
+    delete s;
+    return 0;
+}
+
+// 64-byte IPC handle of the arena + 8 int64 describing its layout, for the other ranks
+extern "C" int pmp_bfs_slab_export(pmp_bfs_slab *s, void *handle64, int64_t *info8) {
+    if (!s || !handle64 || !info8) { pmp_set_error("pmp_bfs_slab_export: bad arguments"); return -1; }
+    cudaIpcMemHandle_t h;
+    PMP_CHECK_CUDA(cudaIpcGetMemHandle(&h, s->arena));
+    static_assert(sizeof h == 64, "IPC handle size");
+    memcpy(handle64, &h, 64);
+    info8[0] = s->L.nbx; info8[1] = s->L.nby; info8[2] = s->L.nbz;
+    info8[3] = s->grid->d.Z; info8[4] = (int64_t)s->field_bytes; info8[5] = (int64_t)s->arena_bytes;
+    info8[6] = s->grid->d.PX; info8[7] = s->grid->d.PY;
+    return 0;
+}
+
+static int bfs_set_peer(pmp_bfs_slab *s, int r, char *base, const int64_t *info) {
+    if (info[0] != s->L.nbx || info[1] != s->L.nby || info[6] != s->grid->d.PX || info[7] != s->grid->d.PY) {
+        pmp_set_error("pmp_bfs_slab_connect: rank %d has a different x / y extent", r);
+        return -1;
+    }
+    const BfsLayout PL = bfs_layout_tiles((int)info[0], (int)info[1], (int)info[2]);
+    char *ws = base + info[4];
+    s->A.peer_ctr[r] = (u32 *)(ws + PL.ctr);
+    if (r == 0) s->A.active = (u32 *)(ws + PL.ctr) + BFS_C_ACTIVE;
+    if (r == s->rank - 1 || r == s->rank + 1) {
+        BfsPeer &P = r < s->rank ? s->A.lo : s->A.hi;
+        P.g = (u32 *)base;
+        P.state = (u32 *)(ws + PL.state);
+        P.ring = (u32 *)(ws + PL.ring);
+        P.ctr = (u32 *)(ws + PL.ctr);
+        P.ring_cap = PL.ring_cap;
+        P.nbz = PL.nbz;
+        P.zadj = r < s->rank ? (int)info[3] - 1 : 0;
+        P.bzadj = r < s->rank ? PL.nbz - 1 : 0;
+    }
+    return 0;
+}
+
+// handles: world x 64 bytes, infos: world x 8 int64 (all ranks' pmp_bfs_slab_export outputs, by rank)
+extern "C" int pmp_bfs_slab_connect(pmp_bfs_slab *s, const void *handles, const int64_t *infos) {
+    if (!s || !handles || !infos) { pmp_set_error("pmp_bfs_slab_connect: bad arguments"); return -1; }
+    for (int r = 0; r < s->world; ++r) {
+        if (r == s->rank) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char *)handles + 64 * r, 64);
+        void *base = nullptr;
+        PMP_CHECK_CUDA(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+        s->peer_base[r] = base;
+        if (bfs_set_peer(s, r, (char *)base, infos + BFS_INFO_WORDS * r)) return -1;
+    }
+    if (s->rank == 0) s->A.active = s->A.ctr + BFS_C_ACTIVE;
+    s->connected = true;
+    return 0;
+}
+
+// all slabs in this process, on this device: plain pointers instead of IPC mappings
+extern "C" int pmp_bfs_slab_connect_local(pmp_bfs_slab **slabs, int n) {
+    if (!slabs || n < 1 || n > BFS_MAX_RANKS) { pmp_set_error("pmp_bfs_slab_connect_local: bad arguments"); return -1; }
+    for (int i = 0; i < n; ++i)
+        if (!slabs[i] || slabs[i]->rank != i || slabs[i]->world != n) { pmp_set_error("pmp_bfs_slab_connect_local: slabs must be given by rank"); return -1; }
+    for (int i = 0; i < n; ++i) {
+        pmp_bfs_slab *s = slabs[i];
+        for (int r = 0; r < n; ++r) {
+            if (r == i) continue;
+            int64_t info[BFS_INFO_WORDS];
+            char dummy[64];
+            pmp_bfs_slab *p = slabs[r];
+            (void)dummy;
+            info[0] = p->L.nbx; info[1] = p->L.nby; info[2] = p->L.nbz; info[3] = p->grid->d.Z;
+            info[4] = (int64_t)p->field_bytes; info[5] = (int64_t)p->arena_bytes; info[6] = p->grid->d.PX; info[7] = p->grid->d.PY;
+            if (bfs_set_peer(s, r, p->arena, info)) return -1;
+        }
+        if (i == 0) s->A.active = s->A.ctr + BFS_C_ACTIVE;
+        s->connected = true;
+    }
+    return 0;
+}
+
+// reset the workspace and queue the source tile (start_local_dev: the source in LOCAL coordinates
+// if it lies in this slab, else NULL).  Every rank must have finished this call (stream
+// synchronised + a barrier across ranks) before any rank calls pmp_bfs_slab_run.
+extern "C" int pmp_bfs_slab_begin(pmp_bfs_slab *s, const int32_t *start_local_dev, int32_t *status_dev, void *stream) {
+    if (!s || !s->connected) { pmp_set_error("pmp_bfs_slab_begin: slab not connected"); return -1; }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (bfs_reset_ws(s->A, s->L, st)) return -2;
+    k_bfs_init<<<1, 1, 0, st>>>(s->A, start_local_dev, status_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pmp_bfs_slab_run(pmp_bfs_slab *s, int32_t *status_dev, uint64_t *stats_dev, void *stream) {
+    if (!s || !s->connected) { pmp_set_error("pmp_bfs_slab_run: slab not connected"); return -1; }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (bfs_launch_search(s->A, st)) return -2;
+    if (bfs_launch_fill(s->A, st)) return -2;
+    k_bfs_finish<<<1, 1, 0, st>>>(s->A, nullptr, status_dev, (u64 *)stats_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---- several slabs, one launch (single-GPU form of the multi-GPU protocol) ----
+__global__ void __launch_bounds__(BFS_NT, BFS_MINB) k_bfs_group(const BfsArgs *args, int n) {
+    const u32 gwarp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const BfsArgs &A = args[gwarp % (u32)n];
+    bfs_warp_main(A, (int)(threadIdx.x & 31), gwarp < (u32)n);
+    if ((threadIdx.x & 31) == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[10], (unsigned long long)bfs_now_ns());
+}
+
+extern "C" int pmp_bfs_slab_run_group(pmp_bfs_slab **slabs, int n, void *stream) {
+    if (!slabs || n < 1 || n > BFS_MAX_RANKS) { pmp_set_error("pmp_bfs_slab_run_group: bad arguments"); return -1; }
+    cudaStream_t st = (cudaStream_t)stream;
+    BfsArgs *dargs = nullptr;
+    PMP_CHECK_CUDA(cudaMalloc(&dargs, sizeof(BfsArgs) * n));
+    for (int i = 0; i < n; ++i) {
+        if (!slabs[i] || !slabs[i]->connected) { cudaFree(dargs); pmp_set_error("pmp_bfs_slab_run_group: slab %d not connected", i); return -1; }
+        PMP_CHECK_CUDA(cudaMemcpyAsync(dargs + i, &slabs[i]->A, sizeof(BfsArgs), cudaMemcpyHostToDevice, st));
+    }
+    int blocks = 0;
+    if (bfs_grid_blocks(&blocks)) { cudaFree(dargs); return -2; }
+    k_bfs_group<<<blocks, BFS_NT, 0, st>>>(dargs, n);
+    cudaError_t e = cudaGetLastError();
+    for (int i = 0; i < n && e == cudaSuccess; ++i) {
+        if (bfs_launch_fill(slabs[i]->A, st)) { e = cudaErrorUnknown; break; }
+        k_bfs_finish<<<1, 1, 0, st>>>(slabs[i]->A, nullptr, nullptr, nullptr);
+    }
+    cudaStreamSynchronize(st);
+    cudaFree(dargs);
+    if (e != cudaSuccess) { pmp_set_error("pmp_bfs_slab_run_group: %s", cudaGetErrorString(e)); return -2; }
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// field pointer (padded local box, the library's (value << 1 | 1) words), its size in bytes, and
+// the 16 counters of the last run (device pointers into the arena)
+extern "C" int pmp_bfs_slab_buffers(pmp_bfs_slab *s, void **field_dev, int64_t *field_bytes, void **stats_dev, void **ctr_dev) {
+    if (!s) { pmp_set_error("pmp_bfs_slab_buffers: null"); return -1; }
+    if (field_dev) *field_dev = s->arena;
+    if (field_bytes) *field_bytes = (int64_t)s->grid->d.pcells * 4;
+    if (stats_dev) *stats_dev = s->A.stats;
+    if (ctr_dev) *ctr_dev = s->A.ctr;
     return 0;
 }

@@ -54,6 +54,7 @@
 #define BFS_C_WORDS 192
 
 #define BFS_ERR_TIMEOUT 1u
+#define BFS_ERR_BUDGET 2u
 
 struct BfsPeer {
     u32 *g;      // peer field (nullptr: no neighbour slab on this side)
@@ -81,6 +82,7 @@ struct BfsArgs {
     u32 *peer_ctr[8];    // control blocks of all ranks (termination broadcast); [rank] = own
     u32 *active;         // rank 0's BFS_C_ACTIVE word
     u64 timeout_ns;      // spin-loop safety net (0: none)
+    u32 max_pops;        // activation budget of this rank (0: none): a search that needs more is aborted
 };
 
 struct BfsCount {
@@ -95,10 +97,18 @@ __device__ static inline u64 bfs_now_ns() {
 }
 __device__ static inline void bfs_store(u32 *p, u32 v) { *p = v; }
 __device__ static inline void bfs_store_volatile(u32 *p, u32 v) { *(volatile u32 *)p = v; }
+// all-ones if bit 7 of byte k of v is set, else 0: PRMT in its sign-replicating form (selector
+// nibble 8 | k) -- __byte_perm() masks the selector to 3 bits, so it takes inline PTX
+__device__ __forceinline__ u32 bfs_byte_sign(u32 v, int k) {
+    u32 d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(v), "r"(0u), "r"(0x1111u * (u32)(8 | k)));
+    return d;
+}
 #else
 static inline u64 bfs_now_ns() { return 0; }
 static inline void bfs_store(u32 *p, u32 v) { *p = v; }
 static inline void bfs_store_volatile(u32 *p, u32 v) { *(volatile u32 *)p = v; }
+static inline u32 bfs_byte_sign(u32 v, int k) { return ((v >> (8 * k)) & 0x80u) ? 0xFFFFFFFFu : 0u; }
 #endif
 
 __device__ __forceinline__ u32 bfs_spread4(u32 n) { return ((n & 0xFu) * 0x00204081u) & 0x01010101u; }
@@ -141,6 +151,7 @@ __device__ static inline void bfs_fail(const BfsArgs &A, u32 code) {
 // lane 0: next tile id + 1, or 0 when the search is over
 __device__ static inline u32 bfs_pop(const BfsArgs &A) {
     const u32 ticket = atomicAdd(&A.ctr[BFS_C_HEAD], 1u);
+    if (A.max_pops && ticket > A.max_pops) { bfs_fail(A, BFS_ERR_BUDGET); return 0u; }
     u32 *slot = &A.ring[ticket % A.ring_cap];
     unsigned ns = 32, spins = 0;
     u64 t0 = 0;
@@ -308,7 +319,7 @@ __device__ __forceinline__ void bfs_extract(const u32 (&rec)[BFS_NREC][2], const
                 const u32 lv = __byte_perm(src, 0u, 0x4440u | (u32)(y & 3));
                 // a cell that was not reached has bit 7 of its byte set: the sign-replicating byte
                 // select turns that into an all-ones word ("unreached" in the stored format)
-                const u32 unr = __byte_perm(src, 0u, 0x1111u * (u32)(8 | (y & 3)));
+                const u32 unr = bfs_byte_sign(src, y & 3);
                 const u32 word = unr | (base2 + (lv << 1));
                 if (TOUCHED) {
                     const bool lower = word < own[y]; // stored words order like their values
@@ -603,18 +614,99 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
     // ---- publish: every store above is visible before a neighbour is armed ----
     __threadfence();
     __syncwarp();
+    // Which neighbours can use what this activation lowered?  Across a face that was NOT read in
+    // this activation: any lowered boundary cell with a free cell behind it.  Across a face that
+    // WAS read (the wave came from there -- the common case): only if a lowered cell actually beats
+    // the neighbour's current value by more than the step, checked against the neighbour's
+    // boundary cells (re-read: they can only have become smaller, so "no" stays "no").  Without
+    // this every tile would re-activate its upstream neighbours for nothing.
     u32 arms = 0;
-    arms |= (__any_sync(BFS_FULL, lane == 0 && ((low0 & xmf0) | (low1 & xmf1)) != 0u) ? 1u : 0u) << 0;
-    arms |= (__any_sync(BFS_FULL, lane == 31 && ((low0 & xpf0) | (low1 & xpf1)) != 0u) ? 1u : 0u) << 1;
-    arms |= (__any_sync(BFS_FULL, ((low0 & ymf0) | (low1 & ymf1)) != 0u) ? 1u : 0u) << 2;
-    arms |= (__any_sync(BFS_FULL, ((low0 & ypf0) | (low1 & ypf1)) != 0u) ? 1u : 0u) << 3;
-    arms |= (__any_sync(BFS_FULL, (low0 & zmf) != 0u) ? 1u : 0u) << 4;
-    arms |= (__any_sync(BFS_FULL, (low1 & zpf) != 0u) ? 1u : 0u) << 5;
+    {
+        // x faces, row-distributed: this lane looks at the cells (y = ly, z = lzq + 4w) of lane 0 / 31
+        const u32 a0 = __shfl_sync(BFS_FULL, low0 & xmf0, 0), a1 = __shfl_sync(BFS_FULL, low1 & xmf1, 0);
+        const u32 b0 = __shfl_sync(BFS_FULL, low0 & xpf0, 31), b1 = __shfl_sync(BFS_FULL, low1 & xpf1, 31);
+        if ((a0 | a1) != 0u) {
+            bool imp = !(dirty & 1u);
+            if (!imp) {
+#pragma unroll
+                for (int w = 0; w < 2; ++w)
+                    if (((w ? a1 : a0) >> lane) & 1u) {
+                        const u32 own = __ldcg(colrow + (size_t)(4 * w) * sZ), h = __ldcg(colrow + (size_t)(4 * w) * sZ - 1);
+                        imp |= own + 2u < h;
+                    }
+            }
+            arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << 0;
+        }
+        if ((b0 | b1) != 0u) {
+            bool imp = !(dirty & 2u);
+            if (!imp) {
+#pragma unroll
+                for (int w = 0; w < 2; ++w)
+                    if (((w ? b1 : b0) >> lane) & 1u) {
+                        const u32 own = __ldcg(colrow + (size_t)(4 * w) * sZ + 31), h = __ldcg(colrow + (size_t)(4 * w) * sZ + 32);
+                        imp |= own + 2u < h;
+                    }
+            }
+            arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << 1;
+        }
+        // y / z faces: this lane's own column
+        const u32 cym0 = low0 & ymf0, cym1 = low1 & ymf1, cyp0 = low0 & ypf0, cyp1 = low1 & ypf1;
+        const u32 czm = low0 & zmf, czp = low1 & zpf;
+        if (__any_sync(BFS_FULL, (cym0 | cym1) != 0u)) {
+            bool imp = !(dirty & 4u) && (cym0 | cym1) != 0u;
+            if (dirty & 4u) {
+#pragma unroll
+                for (int z = 0; z < 8; ++z)
+                    if (((z < 4 ? cym0 : cym1) >> ((z & 3) * 8)) & 1u) {
+                        const u32 own = __ldcg(cell0 + (size_t)z * sZ), h = __ldcg(cell0 + (size_t)z * sZ - sY);
+                        imp |= own + 2u < h;
+                    }
+            }
+            arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << 2;
+        }
+        if (__any_sync(BFS_FULL, (cyp0 | cyp1) != 0u)) {
+            bool imp = !(dirty & 8u) && (cyp0 | cyp1) != 0u;
+            if (dirty & 8u) {
+#pragma unroll
+                for (int z = 0; z < 8; ++z)
+                    if (((z < 4 ? cyp0 : cyp1) >> ((z & 3) * 8 + 7)) & 1u) {
+                        const u32 own = __ldcg(cell0 + (size_t)z * sZ + 7 * sY), h = __ldcg(cell0 + (size_t)z * sZ + 8 * sY);
+                        imp |= own + 2u < h;
+                    }
+            }
+            arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << 3;
+        }
+        if (__any_sync(BFS_FULL, czm != 0u)) {
+            bool imp = !(dirty & 16u) && czm != 0u;
+            if (dirty & 16u) {
+                const u32 *hrow = peer_lo ? A.lo.g + (size_t)A.lo.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 - sZ;
+#pragma unroll
+                for (int y = 0; y < 8; ++y)
+                    if ((czm >> y) & 1u) {
+                        const u32 own = __ldcg(cell0 + (size_t)y * sY), h = __ldcg(hrow + (size_t)y * sY);
+                        imp |= own + 2u < h;
+                    }
+            }
+            arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << 4;
+        }
+        if (__any_sync(BFS_FULL, czp != 0u)) {
+            bool imp = !(dirty & 32u) && czp != 0u;
+            if (dirty & 32u) {
+                const u32 *hrow = peer_hi ? A.hi.g + (size_t)A.hi.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 + 8 * sZ;
+#pragma unroll
+                for (int y = 0; y < 8; ++y)
+                    if ((czp >> (24 + y)) & 1u) {
+                        const u32 own = __ldcg(cell0 + 7 * sZ + (size_t)y * sY), h = __ldcg(hrow + (size_t)y * sY);
+                        imp |= own + 2u < h;
+                    }
+            }
+            arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << 5;
+        }
+    }
 
     // lanes 1..6 arm the six neighbours, lane 0 releases the tile -- all in parallel
     bool need_push = false, requeue = false;
     u32 ntile = 0;
-    bool remote = false;
     if (lane >= 1 && lane <= 6 && ((arms >> (lane - 1)) & 1u)) {
         const int f = lane - 1;
         const int nx = bx + (f == 0 ? -1 : (f == 1 ? 1 : 0)), ny = by + (f == 2 ? -1 : (f == 3 ? 1 : 0));
@@ -623,7 +715,6 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
         if (nz < 0 || nz >= A.nbz) { // the neighbour tile lives on the peer GPU
             const BfsPeer &P = nz < 0 ? A.lo : A.hi;
             ntile = (u32)((P.bzadj * A.nby + ny) * A.nbx + nx);
-            remote = true;
             const u32 was = atomicOr(&P.state[ntile], bit);
             if (!(was & BFS_Q)) {
                 // queue it over there: first make the peer (and, if it was idle, the set of active
@@ -654,7 +745,6 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
             }
         }
     }
-    (void)remote;
     const u32 pushes = __ballot_sync(BFS_FULL, need_push || requeue);
     const int np = __popc(pushes);
     if (np >= 2) {
@@ -670,7 +760,11 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
 }
 
 // ---- persistent warp loop --------------------------------------------------------------------------
-__device__ static inline void bfs_warp_main(const BfsArgs &A, const int lane) {
+// `first`: this is the first warp of its rank -- it ends the search at once when the source was
+// rejected (blocked / outside the box: k_bfs_init left a flag and queued nothing)
+__device__ static inline void bfs_warp_main(const BfsArgs &A, const int lane, const bool first) {
+    if (first && lane == 0 && __ldcg(&A.ctr[BFS_C_SRC + 3]))
+        for (int r = 0; r < A.world; ++r) bfs_store_volatile(&A.peer_ctr[r][BFS_C_DONE], 1u);
     BfsCount cnt;
     cnt.act = cnt.idle = cnt.lowered = cnt.levels = cnt.passes = cnt.redo = cnt.remote = 0;
     for (;;) {

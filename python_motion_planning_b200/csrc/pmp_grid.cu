@@ -120,6 +120,25 @@ __global__ void k_bits_pack_xyz(GridDev G, u32 *bits, const uint8_t *occ, int ve
     }
 }
 
+// caller-packed occupancy rows [z][y][ceil(X / 32)] (bit i of word w <-> x = 32 w + i, 1 = blocked)
+// -> the grid's own rows; everything outside the box (tail bits, padding rows / planes) blocked
+__global__ void k_bits_from_packed(GridDev G, u32 *bits, const u32 *rows, int wpr_in) {
+    const size_t n_words = (size_t)G.wpr * G.PY * G.PZ;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_words;
+         i += (size_t)gridDim.x * blockDim.x) {
+        const int wx = (int)(i % G.wpr);
+        const size_t row = i / G.wpr;
+        const int y = (int)(row % G.PY), z = (int)(row / G.PY);
+        u32 w = 0xFFFFFFFFu;
+        if (y < G.Y && z < G.Z && wx < wpr_in) {
+            w = rows[((size_t)z * G.Y + y) * wpr_in + wx];
+            const int x0 = wx * 32;
+            if (x0 + 32 > G.X) w |= x0 >= G.X ? 0xFFFFFFFFu : 0xFFFFFFFFu << (G.X - x0);
+        }
+        bits[i] = w;
+    }
+}
+
 __global__ void k_count_free(GridDev G, const u32 *bits, u64 *out) {
     const size_t n_words = (size_t)G.wpr * G.PY * G.PZ;
     u64 local = 0;
@@ -329,6 +348,14 @@ extern "C" int pmp_grid_set_dense_xyz(pmp_grid *g, const uint8_t *occ_dev, void 
     dim3 grid((unsigned)((g->d.Z + 127) / 128), (unsigned)g->d.Y, (unsigned)g->d.wpr), block(32, 8);
     const int vec = (g->d.Z % 4 == 0) && (((uintptr_t)occ_dev & 3) == 0); // 4-byte loads stay aligned
     k_bits_pack_xyz<<<grid, block, 0, s>>>(g->d, g->bits, occ_dev, vec);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pmp_grid_set_packed(pmp_grid *g, const uint32_t *rows_dev, void *stream) {
+    if (!g || !rows_dev) { pmp_set_error("pmp_grid_set_packed: bad arguments"); return -1; }
+    const size_t n_words = (size_t)g->d.wpr * g->d.PY * g->d.PZ;
+    k_bits_from_packed<<<blocks_for(n_words, 256), 256, 0, (cudaStream_t)stream>>>(g->d, g->bits, rows_dev, (g->d.X + 31) / 32);
     PMP_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

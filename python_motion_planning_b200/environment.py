@@ -206,6 +206,28 @@ class DeviceGrid:
                    "pmp_grid_set_dense_xyz")
         self._keep = dev
 
+    def set_packed(self, rows):
+        """rows: uint32 array / tensor [Z][Y][ceil(X/32)] (2D: [Y][ceil(X/32)]), bit i of word w <->
+        x = 32 w + i, 1 = obstacle -- occupancy the caller already holds as bits: 1/8 of the upload
+        of the dense form.  Host arrays go pinned host memory -> device."""
+        t = self.torch
+        X, Y = self.dims[0], self.dims[1]
+        Z = self.dims[2] if self.ndim == 3 else 1
+        want = Z * Y * ((X + 31) // 32)
+        if isinstance(rows, t.Tensor):
+            if rows.numel() != want or rows.element_size() != 4:
+                raise ValueError(f"packed occupancy: expected {want} 32-bit words")
+            self.h2d_bytes = 0 if rows.is_cuda else rows.numel() * 4
+            dev = rows.contiguous().to(self.device, non_blocking=True)
+        else:
+            a = np.ascontiguousarray(rows)
+            if a.size != want or a.dtype.itemsize != 4:
+                raise ValueError(f"packed occupancy: expected {want} 32-bit words")
+            dev = t.from_numpy(a.view(np.int32)).pin_memory().to(self.device, non_blocking=True)
+            self.h2d_bytes = a.nbytes
+        _lib.check(self.L.pmp_grid_set_packed(self.handle, dev.data_ptr(), self.stream()), "pmp_grid_set_packed")
+        self._keep = dev
+
     def set_motions(self, offsets, costs, cut=False):
         """motion table + edge rule (cut = True: diagonal moves may cut corners, the JPS graph)"""
         key = (tuple(map(tuple, offsets)), tuple(costs))
@@ -257,14 +279,39 @@ class _EnvBase:
 
     def _init_state(self):
         self._obstacles = None
+        self._packed = None       # uint32 bit rows when update_packed() was used
         self._dense = None        # numpy / torch occupancy when update() got an array
         self._tree = None
         self._device = None
         self._device_version = -1
         self._version = 0
 
+    def update_packed(self, rows):
+        """Occupancy as bit rows [Z][Y][ceil(X/32)] of uint32 (bit i of word w <-> x = 32 w + i, 1 =
+        obstacle; DeviceGrid.set_packed) -- the 1-bit-per-cell form of update() for callers that
+        hold their map as bits already (a 1536^3 grid is 432 MiB instead of 3.4 GiB).  No
+        counterpart in the reference (env.py:78-80 takes a set of tuples)."""
+        self._packed = rows
+        self._dense = None
+        self._obstacles = None
+        self._tree = None
+        self._version += 1
+
+    def _unpack(self):
+        r = self._packed
+        if not isinstance(r, np.ndarray):
+            r = r.detach().cpu().numpy()
+        dims = self._dims()
+        X, Y = dims[0], dims[1]
+        Z = dims[2] if self._ndim == 3 else 1
+        bits = np.unpackbits(np.ascontiguousarray(r).view(np.uint8).reshape(Z, Y, -1), axis=-1, bitorder="little")[:, :, :X]
+        occ = bits.astype(bool).transpose(2, 1, 0)
+        return occ if self._ndim == 3 else occ[:, :, 0]
+
     @property
     def obstacles(self):
+        if self._obstacles is None and self._packed is not None:
+            self._obstacles = set(map(tuple, np.argwhere(self._unpack()).tolist()))
         if self._obstacles is None and self._dense is not None:
             d = self._dense
             if not isinstance(d, np.ndarray):
@@ -297,11 +344,14 @@ class _EnvBase:
                 raise ValueError(f"occupancy shape {tuple(obstacles.shape)} != {self._dims()}")
             self._dense = obstacles
             self._obstacles = None
+        self._packed = None
         self._tree = None
         self._version += 1
 
     def occupancy(self):
         """dense bool array [x, y(, z)] of the box (host)."""
+        if self._packed is not None:
+            return self._unpack().copy()
         if self._dense is not None:
             d = self._dense
             if not isinstance(d, np.ndarray):
@@ -320,9 +370,11 @@ class _EnvBase:
         if self._device is None:
             self._device = DeviceGrid(self._ndim, self._dims())
         dg = self._device
-        small_set = self._dense is None and len(self._obstacles) <= self._ALWAYS_SYNC_LIMIT
+        small_set = self._dense is None and self._packed is None and len(self._obstacles) <= self._ALWAYS_SYNC_LIMIT
         if force or small_set or self._device_version != self._version:
-            if self._dense is not None:
+            if self._packed is not None:
+                dg.set_packed(self._packed)
+            elif self._dense is not None:
                 dg.set_dense(self._dense)
             else:
                 n = len(self._obstacles)

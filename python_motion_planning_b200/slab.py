@@ -234,16 +234,20 @@ class SlabDriver:
         return bad, reached, pend
 
 
-def build_local_env(occ_local, motions="6"):
-    """Grid3D of the local box from a dense occupancy array [x, y, z_local]; `motions`: "6"
-    keeps the unit moves only (config 5), "26" the full table."""
+def build_local_env(occ_local, motions="6", packed_shape=None):
+    """Grid3D of the local box from a dense occupancy array [x, y, z_local] -- or, with
+    packed_shape = (X, Y, Z_local), from bit rows [z][y][X/32] (Grid3D.update_packed); `motions`:
+    "6" keeps the unit moves only (config 5), "26" the full table."""
     from .environment import Grid3D
-    env = Grid3D(*occ_local.shape, walls=False)
+    env = Grid3D(*(packed_shape or occ_local.shape), walls=False)
     if motions == "6":
         env.motions = [m for m in env.motions if m.g == 1]
     elif motions == "18":
         env.motions = [m for m in env.motions if m.g < 1.5]
-    env.update(occ_local)
+    if packed_shape:
+        env.update_packed(occ_local)
+    else:
+        env.update(occ_local)
     return env
 
 
@@ -276,3 +280,221 @@ def solve_in_process(engines, Z, source_global, outer_window=512.0, max_iteratio
         hi.e.merge(0, lo.e.plane(lo.nzl - 2).clone(), mark=False)
         lo.e.merge(lo.nzl - 1, hi.e.plane(1).clone(), mark=False)
     return it, drv
+
+
+# ------------------------------------------------------------------------------------------------
+# Round 2: z-slabs with DEVICE-SIDE halo exchange (pmp_bfs_slab_*, csrc/pmp_bfs.cu).
+#
+# For the unit-weight 6-connected field (config 5) the host-driven loop above is replaced by one
+# kernel launch per rank: boundary tiles read their z halo out of the neighbour GPU's field over
+# NVLink (CUDA IPC mapping of the peer's arena) and queue the neighbour's tiles with remote
+# atomics.  torch.distributed only carries the 128-byte (IPC handle, layout) records once and the
+# two barriers around a search.
+# ------------------------------------------------------------------------------------------------
+def slab_range8(Z, rank, world):
+    """owned planes [z0, z1) of `rank` when slab boundaries fall on tile rows (multiples of 8)"""
+    ntz = (Z + 7) // 8
+    t0, t1 = ntz * rank // world, ntz * (rank + 1) // world
+    return t0 * 8, min(Z, t1 * 8)
+
+
+class _DevMem:
+    """a device allocation of the library, viewed by torch without a copy"""
+
+    def __init__(self, ptr, n_words, owner):
+        self.__cuda_array_interface__ = {"shape": (int(n_words),), "typestr": "<i4", "data": (int(ptr), False),
+                                         "version": 2}
+        self._owner = owner
+
+
+class BfsSlab:
+    """One z-slab (owned planes only, no ghosts) of a 6-connected unit-weight grid on the current
+    CUDA device.  occ_local: dense occupancy [x, y, z_local]."""
+
+    def __init__(self, occ_local, rank=0, world=1, packed_shape=None):
+        self.env = build_local_env(occ_local, "6", packed_shape)
+        self.dg = self.env.device_grid()
+        self.dg.set_motions(*motion_table(self.env, 3))
+        self.rank, self.world = rank, world
+        t = self.torch = self.dg.torch
+        L = self.L = self.dg.L
+        h = ctypes.c_void_p()
+        _lib.check(L.pmp_bfs_slab_create(self.dg.handle, rank, world, ctypes.byref(h)), "pmp_bfs_slab_create")
+        self.handle = h
+        fp, sp, cp, nb = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_int64(0)
+        _lib.check(L.pmp_bfs_slab_buffers(h, ctypes.byref(fp), ctypes.byref(nb), ctypes.byref(sp), ctypes.byref(cp)),
+                   "pmp_bfs_slab_buffers")
+        self.field = t.as_tensor(_DevMem(fp.value, nb.value // 4, self), device=self.dg.device)   # raw words
+        self._stats_arena = t.as_tensor(_DevMem(sp.value, 32, self), device=self.dg.device).view(t.int64)
+        self.stats = t.zeros(16, dtype=t.int64, device=self.dg.device)
+        self.status = t.zeros(1, dtype=t.int32, device=self.dg.device)
+        self._start = t.zeros(3, dtype=t.int32, device=self.dg.device)
+        self.launches = 0
+
+    def close(self):
+        if self.handle is not None:
+            self.field = None
+            self._stats_arena = None
+            self.L.pmp_bfs_slab_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def export(self):
+        hb = (ctypes.c_uint8 * 64)()
+        info = (ctypes.c_int64 * 8)()
+        _lib.check(self.L.pmp_bfs_slab_export(self.handle, hb, info), "pmp_bfs_slab_export")
+        return bytes(hb), [int(v) for v in info]
+
+    def connect(self, handles, infos):
+        """handles: list of 64-byte strings by rank; infos: list of 8-int lists by rank"""
+        hb = (ctypes.c_uint8 * (64 * self.world)).from_buffer_copy(b"".join(handles))
+        ib = (ctypes.c_int64 * (8 * self.world))(*[v for inf in infos for v in inf])
+        _lib.check(self.L.pmp_bfs_slab_connect(self.handle, hb, ib), "pmp_bfs_slab_connect")
+
+    def begin(self, start_local):
+        sp = None
+        if start_local is not None:
+            self._start.copy_(self.torch.tensor(list(start_local), dtype=self.torch.int32))
+            sp = self._start.data_ptr()
+        self.status.zero_()
+        _lib.check(self.L.pmp_bfs_slab_begin(self.handle, sp, self.status.data_ptr(), self.dg.stream()),
+                   "pmp_bfs_slab_begin")
+        self.launches += 1
+
+    def run(self):
+        _lib.check(self.L.pmp_bfs_slab_run(self.handle, self.status.data_ptr(), self.stats.data_ptr(),
+                                           self.dg.stream()), "pmp_bfs_slab_run")
+        self.launches += 3
+
+    def check(self):
+        _lib.check_status(self.status.cpu().numpy(), "pmp_bfs_slab_run")
+
+    def stats_host(self):
+        """the 16 counters of the last search, read from the arena (layout of pmp_sssp's stats)"""
+        v = self._stats_arena.cpu().numpy()
+        if int(v[15]):
+            raise _lib.PmpError("pmp_bfs_slab: the search kernel aborted (queue wait timed out)")
+        return v
+
+    def plane(self, z_local):
+        n = self.dg.padded[0] * self.dg.padded[1]
+        return self.field[z_local * n:(z_local + 1) * n]
+
+    def field_numpy(self):
+        """float64 [x, y, z_local] (+inf = unreached)"""
+        t = self.torch
+        PX, PY, PZ = self.dg.padded
+        raw = self.field.clone()
+        f = (raw >> 1).to(t.float64)
+        f = t.where(raw == -1, t.full_like(f, float("inf")), f).view(PZ, PY, PX)
+        X, Y, Z = self.dg.dims
+        return f[:Z, :Y, :X].permute(2, 1, 0).contiguous().cpu().numpy()
+
+
+def solve_group(slabs, Z, source_global):
+    """several BfsSlab objects of ONE process / one GPU (slab p = rank p of len(slabs)): one kernel
+    launch serves all of them, with the peer protocol running between them."""
+    n = len(slabs)
+    L = slabs[0].L
+    arr = (ctypes.c_void_p * n)(*[s.handle for s in slabs])
+    _lib.check(L.pmp_bfs_slab_connect_local(arr, n), "pmp_bfs_slab_connect_local")
+    sx, sy, sz = source_global
+    for p, s in enumerate(slabs):
+        z0, z1 = slab_range8(Z, p, n)
+        s.begin((sx, sy, sz - z0) if z0 <= sz < z1 else None)
+    _lib.check(L.pmp_bfs_slab_run_group(arr, n, slabs[0].dg.stream()), "pmp_bfs_slab_run_group")
+
+
+class BfsSlabSolver:
+    """The unit-weight field of one large grid over `world` GPUs, one process per GPU.
+
+    occ_planes(z0, z1) -> dense occupancy [x, y, z0:z1] of the GLOBAL grid of `shape` (packed=True:
+    bit rows [z1 - z0][Y][X/32], Grid3D.update_packed);
+    dist: torch.distributed (initialised; NCCL on the GPU box) or None for world 1."""
+
+    def __init__(self, occ_planes, shape, rank=0, world=1, dist=None, packed=False):
+        self.shape, self.rank, self.world, self.dist = tuple(shape), rank, world, dist
+        self.occ_planes, self.packed = occ_planes, packed
+        self.z0, self.z1 = slab_range8(shape[2], rank, world)
+        self.slab = BfsSlab(occ_planes(self.z0, self.z1), rank, world,
+                            (shape[0], shape[1], self.z1 - self.z0) if packed else None)
+        self.torch = self.slab.torch
+        if world > 1:
+            t = self.torch
+            h, info = self.slab.export()
+            rec = np.zeros(128, dtype=np.uint8)
+            rec[:64] = np.frombuffer(h, dtype=np.uint8)
+            rec[64:] = np.array(info, dtype=np.int64).view(np.uint8)
+            dev = self.slab.dg.device if dist.get_backend() == "nccl" else "cpu"
+            mine = t.from_numpy(rec).to(dev)
+            allr = [t.empty_like(mine) for _ in range(world)]
+            dist.all_gather(allr, mine)
+            recs = [a.cpu().numpy() for a in allr]
+            self.slab.connect([r[:64].tobytes() for r in recs], [r[64:].view(np.int64).tolist() for r in recs])
+        self.bytes_halo = 0
+
+    def _barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+
+    def solve(self, source_global):
+        """one search to global termination; returns nothing (the field stays in self.slab.field)"""
+        sx, sy, sz = source_global
+        self.slab.begin((sx, sy, sz - self.z0) if self.z0 <= sz < self.z1 else None)
+        self._barrier()          # every rank has reset its workspace before any rank searches
+        self.slab.run()
+        self._barrier()          # ... and has finished before any rank resets again
+
+    def check(self):
+        self.slab.check()
+
+    def verify(self, source_global):
+        """global (violations, reached cells, pending flags): the local-optimality certificate
+        (pmp_verify_field) over the owned planes, evaluated on a copy with one ghost plane per
+        interior side fetched from the neighbour ranks (send / recv; test / accounting path only)."""
+        t, s = self.torch, self.slab
+        Z = self.shape[2]
+        h0, h1 = max(self.z0 - 1, 0), min(self.z1 + 1, Z)
+        env_g = build_local_env(self.occ_planes(h0, h1), "6", (self.shape[0], self.shape[1], h1 - h0) if self.packed else None)
+        dg = env_g.device_grid()
+        dg.set_motions(*motion_table(env_g, 3))
+        PX, PY, PZg = dg.padded
+        n = PX * PY
+        f = t.full((PZg * n,), -1, dtype=t.int32, device=dg.device)
+        off = self.z0 - h0
+        nz = self.z1 - self.z0
+        f[off * n:(off + nz) * n] = s.field[:nz * n]
+        if self.world > 1:
+            d = self.dist
+            ops = []
+            lo_rx = hi_rx = None
+            if self.rank > 0:
+                lo_rx = t.empty(n, dtype=t.int32, device=dg.device)
+                ops += [d.P2POp(d.isend, s.plane(0).contiguous(), self.rank - 1), d.P2POp(d.irecv, lo_rx, self.rank - 1)]
+            if self.rank < self.world - 1:
+                hi_rx = t.empty(n, dtype=t.int32, device=dg.device)
+                ops += [d.P2POp(d.isend, s.plane(nz - 1).contiguous(), self.rank + 1), d.P2POp(d.irecv, hi_rx, self.rank + 1)]
+            for w in d.batch_isend_irecv(ops):
+                w.wait()
+            if lo_rx is not None:
+                f[0:n] = lo_rx
+            if hi_rx is not None:
+                f[(off + nz) * n:(off + nz + 1) * n] = hi_rx
+        out = t.zeros(3, dtype=t.int64, device=dg.device)
+        sx, sy, sz = source_global
+        sp = None
+        if self.z0 <= sz < self.z1:
+            src = t.tensor([sx, sy, sz - h0], dtype=t.int32, device=dg.device)
+            sp = src.data_ptr()
+        _lib.check(dg.L.pmp_verify_field(dg.handle, _lib.W_U32, f.data_ptr(), sp, off, off + nz, out.data_ptr(),
+                                         dg.stream()), "pmp_verify_field")
+        if self.world > 1:
+            self.dist.all_reduce(out, op=self.dist.ReduceOp.SUM)
+        bad, reached, pend = (int(v) for v in out.cpu().tolist())
+        return bad, reached, pend

@@ -79,6 +79,34 @@ def replicated_slab(blk, shape, z0, z1):
     return plane
 
 
+def pack_rows(occ):
+    """dense occupancy [x, y, z] -> bit rows [z][y][ceil(X/32)] of uint32 (Grid3D.update_packed)"""
+    X = occ.shape[0]
+    b = np.packbits(np.ascontiguousarray(occ.transpose(2, 1, 0)), axis=-1, bitorder="little")
+    pad = (-b.shape[-1]) % 4
+    if pad:
+        b = np.concatenate([b, np.zeros(b.shape[:-1] + (pad,), dtype=np.uint8)], axis=-1)
+    return np.ascontiguousarray(b).view(np.uint32).reshape(occ.shape[2], occ.shape[1], (X + 31) // 32)
+
+
+def replicated_packed(blk, shape, z0, z1):
+    """replicated_slab(blk, shape, z0, z1) as bit rows [z1 - z0][Y][X / 32], built from the packed
+    block without materialising a byte per cell (base must be a multiple of 32)"""
+    base = blk.shape[0]
+    reps = shape[0] // base
+    assert base % 32 == 0 and shape[0] == shape[1] == base * reps
+    pb = pack_rows(blk)                                    # [base z][base y][base / 32]
+    zs = np.arange(z0, z1)
+    rows = np.tile(pb[zs % base], (1, reps, reps))         # [nz][Y][X / 32]
+    rows[:, :, 0] |= np.uint32(1)                          # x = 0 wall
+    rows[:, :, -1] |= np.uint32(0x80000000)                # x = X - 1 wall
+    rows[:, 0, :] = np.uint32(0xFFFFFFFF)
+    rows[:, -1, :] = np.uint32(0xFFFFFFFF)
+    rows[zs == 0] = np.uint32(0xFFFFFFFF)
+    rows[zs == shape[2] - 1] = np.uint32(0xFFFFFFFF)
+    return rows
+
+
 def door3d(dims=(26, 20, 16), door_size=2, start=(1, 1, 1), goal=None, bubble=1):
     """config 2: the default scene of examples/3d_example.py -- two rooms split by a wall at
     x = X//2 with a door_size^2 door at the centre (examples/scenarios.py:28-47), shell walls,

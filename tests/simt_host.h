@@ -243,8 +243,7 @@ static inline uint32_t __byte_perm(uint32_t a, uint32_t b, uint32_t sel) {
     uint32_t r = 0;
     for (int i = 0; i < 4; ++i) {
         const uint32_t n = (sel >> (4 * i)) & 0xF;
-        uint32_t byte = (uint32_t)(v >> (8 * (n & 7))) & 0xFFu;
-        if (n & 8) byte = (byte & 0x80u) ? 0xFFu : 0u;
+        const uint32_t byte = (uint32_t)(v >> (8 * (n & 7))) & 0xFFu; // __byte_perm uses 3 bits per selector: no sign mode
         r |= byte << (8 * i);
     }
     return r;

@@ -29,7 +29,7 @@ def test_library_builds_and_exports_every_declared_symbol():
         assert hasattr(L, name), f"{name} declared in include/pmp_b200.h but not exported"
     assert sorted(_lib.SYMBOLS) == decl
     L.pmp_abi_version.restype = ctypes.c_int
-    assert L.pmp_abi_version() == _lib.ABI_VERSION == 2
+    assert L.pmp_abi_version() == _lib.ABI_VERSION == 3
 
 
 def test_no_cpu_fallback():

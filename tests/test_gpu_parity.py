@@ -9,6 +9,7 @@ re-sums along whichever equal-cost path its heap order picked) and exactly equal
 integer-weight 4/6-connected grids; paths collision-free under the reference's own
 isCollision; GBFS exact (same sequential algorithm).
 """
+import os
 import math
 
 import numpy as np
@@ -489,3 +490,40 @@ def test_astar_banded_ring_vs_oracle(monkeypatch, bands, window):
             continue
         assert abs(cost - want.cost) <= REL * want.cost
         check_path(occ3, path, s, g, "start_first", oracle.MOTIONS_3D)
+
+
+# ---- known answers at the BENCHMARKED sizes (tests/golden/bench_sizes.json, tools/make_golden_bench.py) ----
+def _bench_golden():
+    import json
+    return json.load(open(os.path.join(os.path.dirname(__file__), "golden", "bench_sizes.json")))
+
+
+@pytest.mark.parametrize("n", [256, 512])
+def test_c4_astar_at_bench_size(n):
+    """config 4 as bench.py runs it (banded ring, 32 768 tiles at n = 512): cost vs the oracle's"""
+    from python_motion_planning_b200 import workloads
+    gold = _bench_golden()[f"c4_{n}"]
+    occ = workloads.boxes3d(n, seed=0)
+    env = pmp.Grid3D(n, n, n, walls=False)
+    env.update(occ)
+    cost, path, _ = pmp.AStar3D((1, 1, 1), (n - 2, n - 2, n - 2), env).plan()
+    want = float.fromhex(gold["cost_hex"])
+    assert abs(cost - want) <= REL * want, (cost, want)
+    assert path[0] == (1, 1, 1) and path[-1] == (n - 2, n - 2, n - 2)
+    assert cost == resum(path[::-1])          # accumulated goal -> start (a_star3d.py:96-103)
+    # equal-cost paths may differ in length by ties only: same number of steps up to the 1/sqrt2/sqrt3 mix
+    assert abs(len(path) - gold["path_len"]) <= 0.2 * gold["path_len"]
+
+
+def test_c3_queries_at_bench_size():
+    """config 3 on the real 1024^2 map: the first 64 of the 4096 seeded queries vs the oracle"""
+    from python_motion_planning_b200 import workloads
+    gold = _bench_golden()["c3_1024_first64"]
+    occ, starts, goals = workloads.random2d(1024, nq=4096, seed=0)
+    env = pmp.Grid(1024, 1024)
+    env.update(occ)
+    res = pmp.plan_batch(env, starts[:64], goals[:64], algo="dijkstra", want_paths=False)
+    want = np.array([float.fromhex(h) for h in gold["cost_hex"]])
+    reach = np.isfinite(want)
+    assert np.array_equal(np.isfinite(res.costs), reach)
+    np.testing.assert_allclose(res.costs[reach], want[reach], rtol=REL, atol=0)

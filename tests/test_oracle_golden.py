@@ -130,3 +130,15 @@ def test_batch_matches_single():
     for q in range(8):
         r = oracle.plan(occ, starts[q], goals[q], algo=oracle.DIJKSTRA)
         assert r.cost == cost[q] and r.n_expand == nexp[q] and len(r.path) == plen[q]
+
+
+def test_field64_config5_crop():
+    """config 5 at a multi-tile size: the oracle's 6-motion Dijkstra field == the unmodified
+    Dijkstra3D's on a 64^3 crop of the obstacle block (tools/make_golden.py field64)"""
+    z = gio.load("field64.npz") if hasattr(gio, "load") else np.load(os.path.join(os.path.dirname(__file__), "golden", "field64.npz"))
+    occ, src = z["occ"], tuple(int(v) for v in z["src"])
+    keep = oracle.motion_costs(oracle.MOTIONS_3D) == 1.0
+    r = oracle.plan(occ, src, None, algo=oracle.DIJKSTRA, motions=oracle.MOTIONS_3D[keep],
+                    motion_g=oracle.motion_costs(oracle.MOTIONS_3D)[keep], want_field=True, want_expand=False)
+    assert np.array_equal(r.g_field, z["g"])
+    assert int(np.isfinite(z["g"]).sum()) == 222454

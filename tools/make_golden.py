@@ -14,6 +14,8 @@ Fixtures
                    planners, both heuristics; cost, path, expansion order with g and h.
   cases3d.npz      examples/3d_example.py defaults, default Grid3D walls (incl. the z-1 quirk,
                    env3d.py:86-92), 6- and 18-connected motion subsets, random boxes.
+  field64.npz      config 5 on a 64^3 crop of its obstacle block (`python tools/make_golden.py field64`):
+                   Dijkstra3D, six unit moves, to exhaustion.
   fields.npz       full cost-to-go fields: Dijkstra3D with an unreachable goal
                    (dijkstra3d.py:86-87 returns CLOSED), 26- and 6-connected; 2D Dijkstra to
                    the farthest corner (CLOSED of the settled region).
@@ -391,6 +393,33 @@ def make_fields(pmp):
     np.savez_compressed(os.path.join(OUT, "fields.npz"), **out)
 
 
+def make_field64(pmp):
+    """BASELINE.json config 5 on a 64^3 crop of its obstacle block: the unmodified Dijkstra3D with
+    env.motions filtered to the six unit moves, run to exhaustion (dijkstra3d.py:39-87).  Closes the
+    chain reference -> oracle -> kernel at a multi-tile size (tests/test_bfs_gpu.py,
+    tests/test_oracle_golden.py)."""
+    ref_harness.fast_grid_map(pmp)
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+    from python_motion_planning_b200 import workloads
+    blk, _ = workloads.replicated_boxes3d(base=128, reps=1)
+    n = 64
+    occ = blk[:n, :n, :n].copy()
+    workloads.seal(occ)
+    env = pmp.Grid3D(n, n, n)
+    env.update(set(map(tuple, np.argwhere(occ).tolist())))
+    env.motions = [m for m in env.motions if m.g == 1]
+    assert len(env.motions) == 6
+    src = (1, 1, 1)
+    assert not occ[src]
+    cost, path, expand = pmp.Dijkstra3D(start=src, goal=(0, 0, 0), env=env).plan()
+    assert cost == float("inf") and path == []
+    field = np.full((n, n, n), np.inf)
+    for e in expand:
+        field[e.current] = e.g
+    print("field64: settled", len(expand), "of", int((~occ).sum()), "max g", float(np.max(field[np.isfinite(field)])))
+    np.savez_compressed(os.path.join(OUT, "field64.npz"), occ=occ, src=np.array(src, dtype=np.int32), g=field)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     pmp = ref_harness.load_reference()
@@ -403,3 +432,5 @@ if __name__ == "__main__":
         make_cases3d(pmp)
     if "fields" in which:
         make_fields(pmp)
+    if "field64" in which:
+        make_field64(pmp)
