@@ -481,9 +481,14 @@ def measure(W, ctx, steps, warmup, dist, sample_clocks=True):
 def kernel_stats(st, dtype, clocks):
     st = [int(v) for v in st]
     if dtype == "u32":      # pmp_bfs (warp-per-tile level solver): see include/pmp_b200.h
+        mhz = ((clocks or {}).get("sm_mhz") or 1965.0)
+        na = max(st[1], 1)
         return {"solver": "k_bfs (one warp per tile)", "tile_activations": st[1], "idle_activations": st[13],
-                "cells_lowered": st[2], "edges_relaxed": st[3], "levels_swept": st[12], "passes": st[14],
-                "requeues": st[5], "remote_pushes": st[7], "kernel_ms": st[8] / 1e6}
+                "cells_lowered": st[2], "edges_relaxed": st[2] * 6, "levels_swept": st[12], "passes": st[14],
+                "requeues": st[5], "remote_pushes": st[7], "kernel_ms": st[8] / 1e6,
+                "us_per_activation_per_warp": {"wait_for_work": st[4] / na / mhz, "setup": st[6] / na / mhz,
+                                               "sweep": st[11] / na / mhz, "extract_store": st[3] / na / mhz,
+                                               "publish": st[0] / na / mhz}}
     mhz = ((clocks or {}).get("sm_mhz") or 1965.0)
     nt = max(st[1], 1)
     return {"rounds": st[0], "tile_activations": st[1], "cells_expanded": st[2], "edges_relaxed": st[3],

@@ -8,6 +8,8 @@
 #include <string.h>
 
 #include "pmp_common.cuh"
+// the warps of a CTA enter every phase of a tile activation together (k_bfs): see the kernel
+#define BFS_PHASE_SYNC() __syncthreads()
 #include "pmp_bfs_core.cuh"
 
 #ifndef BFS_NT
@@ -16,9 +18,57 @@
 #ifndef BFS_MINB
 #define BFS_MINB 4 // resident CTAs per SM the register budget is sized for
 #endif
+#ifndef BFS_TRY_POLLS
+#define BFS_TRY_POLLS 6 // polls of the ring slot (32 ns ... 1 us apart) before a warp joins its CTA's round without a tile
+#endif
+#ifndef BFS_SYNC_NT
+#define BFS_SYNC_NT 128 // threads per CTA of the phase-locked kernel (4 warps in step; measured best of 128 / 256 / 512)
+#endif
 #define BFS_RING_SLACK 8192
 
-__global__ void __launch_bounds__(BFS_NT, BFS_MINB) k_bfs(const __grid_constant__ BfsArgs A) {
+// The search kernel.  Persistent; one warp per tile activation.  The kernel's code is far larger
+// than the instruction caches (a setup, a sweep, an extract and a publish phase of 0.3-1.5 K
+// instructions each); free-running warps sit in different phases and thrash them (ncu: 29 cycles
+// of "no instruction" stall per issued instruction, profiles/r02_notes.md).  So the warps of a CTA
+// move through the phases in step: CTA barriers at the phase boundaries (BFS_PHASE_SYNC inside
+// bfs_process_tile), warps without a tile take the same barriers.  A warp may therefore not block in
+// the queue while its CTA waits for it: it polls its ring slot a few times (bfs_pop_try keeps the
+// ticket) and joins the round empty-handed otherwise.
+__global__ void __launch_bounds__(512, 1) k_bfs(const __grid_constant__ BfsArgs A) {
+    const int lane = (int)(threadIdx.x & 31);
+    bfs_reject_check(A, lane, blockIdx.x == 0 && threadIdx.x < 32);
+    BfsCount cnt;
+    bfs_count_init(cnt);
+    BfsPop P;
+    P.ticket = 0; P.have = 0; P.t0 = 0;
+    for (;;) {
+        u32 item = 0, fin = 0;
+        const long long tp = clock64();
+        if (lane == 0) {
+            bool done = false;
+            item = bfs_pop_try(A, P, BFS_TRY_POLLS, done);
+            fin = done ? 1u : 0u;
+        }
+        item = __shfl_sync(BFS_FULL, item, 0);
+        fin = __shfl_sync(BFS_FULL, fin, 0);
+        if (!__syncthreads_or(item != 0u)) {          // nobody in the CTA has work
+            if (__syncthreads_and(fin != 0u)) break;  // ... and the search is over for everyone
+            continue;
+        }
+        if (item) {
+            cnt.c_pop += (u64)(clock64() - tp);
+            bfs_process_tile<true>(A, item - 1u, lane, cnt);
+        } else {
+            BFS_PHASE_SYNC(); BFS_PHASE_SYNC(); BFS_PHASE_SYNC(); // the three phase boundaries of bfs_process_tile
+        }
+    }
+    bfs_count_flush(A, cnt, lane);
+    if (lane == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[10], (unsigned long long)bfs_now_ns());
+}
+
+// free-running form of the same search (every warp on its own; PMP_B200_BFS_FREE=1): the A/B partner
+// of k_bfs in profiles/r02_notes.md
+__global__ void __launch_bounds__(BFS_NT, BFS_MINB) k_bfs_free(const __grid_constant__ BfsArgs A) {
     bfs_warp_main(A, (int)(threadIdx.x & 31), blockIdx.x == 0 && threadIdx.x < 32);
     if ((threadIdx.x & 31) == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[10], (unsigned long long)bfs_now_ns());
 }
@@ -28,7 +78,6 @@ __global__ void __launch_bounds__(BFS_NT, BFS_MINB) k_bfs(const __grid_constant_
 __global__ void k_bfs_init(BfsArgs A, const int32_t *start, int32_t *status) {
     const GridDev &Gd = A.G;
     A.stats[9] = bfs_now_ns();
-    A.stats[0] = 1;
     if (A.rank == 0) A.ctr[BFS_C_ACTIVE] = 1u;
     int st = PMP_ST_RUNNING;
     if (start) {
@@ -127,17 +176,42 @@ static void bfs_fill_args(const pmp_grid *g, void *g_dev, void *ws_dev, const Bf
     A.max_pops = budget > 0xFFFFFFF0ull ? 0u : (u32)budget;
 }
 
-static int bfs_grid_blocks(int *out) {
-    static int blocks = 0;
-    if (!blocks) {
+__global__ void k_bfs_group(const BfsArgs *args, int n);
+
+// launch shape: persistent grid, every warp resident, a multiple of the SM count.
+// PMP_B200_BFS_FREE=1: the free-running kernel; PMP_B200_BFS_NT: threads per CTA of the phase-locked
+// kernel (default BFS_SYNC_NT); PMP_B200_BFS_CTAS_PER_SM: fewer CTAs than fit.
+struct BfsLaunch { int blocks, nt, free_running; };
+static int bfs_launch_shape(BfsLaunch *out) {
+    static BfsLaunch L = {0, 0, 0};
+    if (!L.blocks) {
         int per_sm = 0, dev = 0, n_sm = 0;
-        PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs, BFS_NT, 0));
+        const char *f = getenv("PMP_B200_BFS_FREE");
+        L.free_running = f && atoi(f) != 0;
+        const char *t = getenv("PMP_B200_BFS_NT");
+        L.nt = L.free_running ? BFS_NT : (t && atoi(t) >= 32 && atoi(t) <= 512 && atoi(t) % 32 == 0 ? atoi(t) : BFS_SYNC_NT);
+        if (L.free_running) PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs_free, L.nt, 0));
+        else PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs, L.nt, 0));
         PMP_CHECK_CUDA(cudaGetDevice(&dev));
         PMP_CHECK_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
         if (per_sm < 1) { pmp_set_error("k_bfs does not fit on an SM"); return -2; }
         const char *e = getenv("PMP_B200_BFS_CTAS_PER_SM");
         if (e && atoi(e) >= 1 && atoi(e) < per_sm) per_sm = atoi(e);
-        blocks = per_sm * n_sm; // persistent: every warp resident, a multiple of the SM count
+        L.blocks = per_sm * n_sm;
+    }
+    *out = L;
+    return 0;
+}
+
+static int bfs_grid_blocks(int *out) { // the free-running group kernel
+    static int blocks = 0;
+    if (!blocks) {
+        int per_sm = 0, dev = 0, n_sm = 0;
+        PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs_group, BFS_NT, 0));
+        PMP_CHECK_CUDA(cudaGetDevice(&dev));
+        PMP_CHECK_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+        if (per_sm < 1) { pmp_set_error("k_bfs_group does not fit on an SM"); return -2; }
+        blocks = per_sm * n_sm;
     }
     *out = blocks;
     return 0;
@@ -152,9 +226,10 @@ static int bfs_reset_ws(const BfsArgs &A, const BfsLayout &L, cudaStream_t s) {
 }
 
 static int bfs_launch_search(const BfsArgs &A, cudaStream_t s) {
-    int blocks = 0;
-    if (bfs_grid_blocks(&blocks)) return -2;
-    k_bfs<<<blocks, BFS_NT, 0, s>>>(A);
+    BfsLaunch L;
+    if (bfs_launch_shape(&L)) return -2;
+    if (L.free_running) k_bfs_free<<<L.blocks, L.nt, 0, s>>>(A);
+    else k_bfs<<<L.blocks, L.nt, 0, s>>>(A);
     PMP_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

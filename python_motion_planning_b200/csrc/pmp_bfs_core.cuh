@@ -41,6 +41,10 @@
 #define BFS_CINV 0xFFFFFFFFu
 #define BFS_NREC 7
 #define BFS_LIM 128      // levels one pass can record (2^BFS_NREC)
+#ifndef BFS_LB
+#define BFS_LB 2      // the level loop is unrolled 2^BFS_LB times (code size vs. static low level bits)
+#endif
+#define BFS_UB (1 << BFS_LB)
 #define BFS_SEEDMAX 63u  // largest seed level relative to the pass base (6 seed planes)
 
 // control block (u32 words; hot counters on separate 128-byte lines)
@@ -52,6 +56,11 @@
 #define BFS_C_ACTIVE 128 // ranks with work in flight (only rank 0's word is used)
 #define BFS_C_SRC 160    // local source cell x, y, z and a valid flag
 #define BFS_C_WORDS 192
+
+// hook: the kernel that keeps the warps of a CTA in step defines this as __syncthreads()
+#ifndef BFS_PHASE_SYNC
+#define BFS_PHASE_SYNC()
+#endif
 
 #define BFS_ERR_TIMEOUT 1u
 #define BFS_ERR_BUDGET 2u
@@ -87,6 +96,7 @@ struct BfsArgs {
 
 struct BfsCount {
     u32 act, idle, lowered, levels, passes, redo, remote;
+    u64 c_pop, c_setup, c_sweep, c_extract, c_publish; // cycles (lane 0's clock) per phase, summed over activations
 };
 
 #ifdef __CUDACC__
@@ -97,6 +107,14 @@ __device__ static inline u64 bfs_now_ns() {
 }
 __device__ static inline void bfs_store(u32 *p, u32 v) { *p = v; }
 __device__ static inline void bfs_store_volatile(u32 *p, u32 v) { *(volatile u32 *)p = v; }
+// release / acquire fence at device scope (the sequentially consistent __threadfence costs more)
+__device__ __forceinline__ void bfs_fence() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+// a field word of the neighbour GPU (NVLink): system-scope load, never served from this SM's L1
+__device__ __forceinline__ u32 bfs_ld_peer(const u32 *p) {
+    u32 v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 // all-ones if bit 7 of byte k of v is set, else 0: PRMT in its sign-replicating form (selector
 // nibble 8 | k) -- __byte_perm() masks the selector to 3 bits, so it takes inline PTX
 __device__ __forceinline__ u32 bfs_byte_sign(u32 v, int k) {
@@ -108,6 +126,8 @@ __device__ __forceinline__ u32 bfs_byte_sign(u32 v, int k) {
 static inline u64 bfs_now_ns() { return 0; }
 static inline void bfs_store(u32 *p, u32 v) { *p = v; }
 static inline void bfs_store_volatile(u32 *p, u32 v) { *(volatile u32 *)p = v; }
+static inline void bfs_fence() { __threadfence(); }
+static inline u32 bfs_ld_peer(const u32 *p) { return *(const volatile u32 *)p; }
 static inline u32 bfs_byte_sign(u32 v, int k) { return ((v >> (8 * k)) & 0x80u) ? 0xFFFFFFFFu : 0u; }
 #endif
 
@@ -143,32 +163,45 @@ __device__ static inline void bfs_push(u32 *ring, u32 cap, u32 *ctr, u32 tile) {
     bfs_store_volatile(&ring[ticket % cap], tile + 1u);
 }
 
-__device__ static inline void bfs_fail(const BfsArgs &A, u32 code) {
+__device__ __noinline__ static void bfs_fail(const BfsArgs &A, u32 code) {
     atomicOr(&A.ctr[BFS_C_ERR], code);
     for (int r = 0; r < A.world; ++r) bfs_store_volatile(&A.peer_ctr[r][BFS_C_DONE], 1u);
 }
 
-// lane 0: next tile id + 1, or 0 when the search is over
-__device__ static inline u32 bfs_pop(const BfsArgs &A) {
-    const u32 ticket = atomicAdd(&A.ctr[BFS_C_HEAD], 1u);
-    if (A.max_pops && ticket > A.max_pops) { bfs_fail(A, BFS_ERR_BUDGET); return 0u; }
-    u32 *slot = &A.ring[ticket % A.ring_cap];
-    unsigned ns = 32, spins = 0;
-    u64 t0 = 0;
-    for (;;) {
+// lane 0's position in the ring: a ticket stays valid across calls of bfs_pop_try until it is served
+struct BfsPop {
+    u32 ticket, have;
+    u64 t0; // when the current wait began (time-out safety net)
+};
+
+// lane 0: try to take the next tile.  Returns tile id + 1; or 0 with `done` set when the search is
+// over; or 0 with `done` clear when nothing arrived within max_polls polls (the ticket is kept).
+__device__ static inline u32 bfs_pop_try(const BfsArgs &A, BfsPop &P, const unsigned max_polls, bool &done) {
+    done = false;
+    if (!P.have) {
+        P.ticket = atomicAdd(&A.ctr[BFS_C_HEAD], 1u);
+        P.have = 1u;
+        P.t0 = 0;
+        if (A.max_pops && P.ticket > A.max_pops) { bfs_fail(A, BFS_ERR_BUDGET); done = true; return 0u; }
+    }
+    u32 *slot = &A.ring[P.ticket % A.ring_cap];
+    unsigned ns = 32;
+    for (unsigned polls = 0;; ++polls) {
         const u32 v = __ldcg(slot);
         if (v) {
             bfs_store_volatile(slot, 0u); // recycle; the ring has more slots than tiles + waiting warps
-            __threadfence();
+            bfs_fence();
+            P.have = 0u;
             return v;
         }
-        if (__ldcg(&A.ctr[BFS_C_DONE])) return 0u;
+        if (__ldcg(&A.ctr[BFS_C_DONE])) { done = true; return 0u; }
+        if (polls >= max_polls) return 0u;
         __nanosleep(ns);
         if (ns < 1024) ns *= 2;
-        if (A.timeout_ns && (++spins & 1023u) == 0) {
+        if (A.timeout_ns && (polls & 1023u) == 1023u) {
             const u64 now = bfs_now_ns();
-            if (!t0) t0 = now;
-            else if (now - t0 > A.timeout_ns) { bfs_fail(A, BFS_ERR_TIMEOUT); return 0u; }
+            if (!P.t0) P.t0 = now;
+            else if (now - P.t0 > A.timeout_ns) { bfs_fail(A, BFS_ERR_TIMEOUT); done = true; return 0u; }
         }
     }
 }
@@ -205,14 +238,14 @@ __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const
     const int last = SA.last > SB.last ? SA.last : SB.last;
     u32 nlev = 0;
     bool fin = false;
-    for (int rb = 0; rb < BFS_LIM && !fin; rb += 8) {
-        // seeds of this block of 8 levels: the three high bits of their level equal rb >> 3
+    for (int rb = 0; rb < BFS_LIM && !fin; rb += BFS_UB) {
+        // seeds of this block of BFS_UB levels: the high bits of their level equal those of rb
         u32 ha0 = 0, ha1 = 0, hb0 = 0, hb1 = 0;
         const bool useA = rb <= SA.last, useB = rb <= SB.last;
         if (useA) {
             ha0 = SA.sv[0]; ha1 = SA.sv[1];
 #pragma unroll
-            for (int b = 3; b < 6; ++b) {
+            for (int b = BFS_LB; b < 6; ++b) {
                 const u32 flip = ((rb >> b) & 1) ? 0u : BFS_FULL;
                 ha0 &= SA.sp[b][0] ^ flip;
                 ha1 &= SA.sp[b][1] ^ flip;
@@ -221,7 +254,7 @@ __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const
         if (useB) {
             hb0 = SB.sv[0]; hb1 = SB.sv[1];
 #pragma unroll
-            for (int b = 3; b < 6; ++b) {
+            for (int b = BFS_LB; b < 6; ++b) {
                 const u32 flip = ((rb >> b) & 1) ? 0u : BFS_FULL;
                 hb0 &= SB.sp[b][0] ^ flip;
                 hb1 &= SB.sp[b][1] ^ flip;
@@ -229,12 +262,12 @@ __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const
         }
         u32 bf0 = 0, bf1 = 0; // cells that got a level inside this block
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < BFS_UB; ++k) {
             u32 f0 = c0, f1 = c1;
             if (useA) {
                 u32 m0 = ha0, m1 = ha1;
 #pragma unroll
-                for (int b = 0; b < 3; ++b) {
+                for (int b = 0; b < BFS_LB; ++b) {
                     m0 &= ((k >> b) & 1) ? SA.sp[b][0] : ~SA.sp[b][0];
                     m1 &= ((k >> b) & 1) ? SA.sp[b][1] : ~SA.sp[b][1];
                 }
@@ -244,7 +277,7 @@ __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const
             if (useB) {
                 u32 m0 = hb0, m1 = hb1;
 #pragma unroll
-                for (int b = 0; b < 3; ++b) {
+                for (int b = 0; b < BFS_LB; ++b) {
                     m0 &= ((k >> b) & 1) ? SB.sp[b][0] : ~SB.sp[b][0];
                     m1 &= ((k >> b) & 1) ? SB.sp[b][1] : ~SB.sp[b][1];
                 }
@@ -254,7 +287,7 @@ __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const
             R0 |= f0; R1 |= f1;
             bf0 |= f0; bf1 |= f1;
 #pragma unroll
-            for (int b = 0; b < 3; ++b)
+            for (int b = 0; b < BFS_LB; ++b)
                 if ((k >> b) & 1) { rec[b][0] |= f0; rec[b][1] |= f1; }
             // neighbours of the frontier: y +- 1 inside a byte, z +- 1 = byte shifts across the two
             // words, x +- 1 = the adjacent lanes
@@ -270,7 +303,7 @@ __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const
             if (rb + k >= last && !__any_sync(BFS_FULL, (c0 | c1) != 0u)) { fin = true; break; }
         }
 #pragma unroll
-        for (int b = 3; b < BFS_NREC; ++b)
+        for (int b = BFS_LB; b < BFS_NREC; ++b)
             if ((rb >> b) & 1) { rec[b][0] |= bf0; rec[b][1] |= bf1; }
     }
     carry0 = fin ? 0u : c0;
@@ -282,59 +315,58 @@ __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const
 // For the cells in N (reached in this pass) the value is base + recorded level.  TOUCHED: the
 // tile already holds values -> min-merge, store only lowered cells; otherwise every word of the
 // tile is written (unreached / blocked cells = all-ones).  Returns the lowered cells in low[].
-template <bool TOUCHED>
+// One (z, word) group of 8 cells: byte zb of the 7 planes + the "not reached" plane -> 8 x 8 bit
+// matrix -> one level byte per cell -> field words.  Returns the lowered cells as 8 bits.
+__device__ __forceinline__ u32 bfs_extract8(const u32 r0, const u32 r1, const u32 r2, const u32 r3, const u32 r4,
+                                            const u32 r5, const u32 r6, const u32 Nw, const u32 zb, const u32 base2,
+                                            u32 *pz, const size_t strideY, const bool inx, const bool touched) {
+    const u32 sel = zb | ((4u + zb) << 4);
+    const u32 t01 = __byte_perm(r0, r1, sel), t23 = __byte_perm(r2, r3, sel);
+    const u32 t45 = __byte_perm(r4, r5, sel), t67 = __byte_perm(r6, ~Nw, sel);
+    u32 lo = __byte_perm(t01, t23, 0x5410u), hi = __byte_perm(t45, t67, 0x5410u);
+    bfs_transpose8(lo, hi);
+    const u32 nb = (Nw >> (zb * 8u)) & 0xFFu; // cells of this group reached in this pass
+    u32 low = 0;
+    u32 *p = pz;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) {
+        const u32 src = y < 4 ? lo : hi;
+        const u32 lv = __byte_perm(src, 0u, 0x4440u | (u32)(y & 3));
+        // a cell that was not reached has bit 7 of its byte set -> an all-ones word ("unreached")
+        const u32 word = bfs_byte_sign(src, y & 3) | (base2 + (lv << 1));
+        if (touched) {
+            // min-merge: only reached cells can be lower (they are free cells, hence inside the row)
+            if ((nb >> y) & 1u) {
+                const u32 own = __ldcg(p);
+                if (word < own) { bfs_store(p, word); low |= 1u << y; } // stored words order like their values
+            }
+        } else if (inx) {
+            bfs_store(p, word);
+        }
+        p += strideY;
+    }
+    return touched ? low : nb;
+}
+
+// ---- levels -> field words -----------------------------------------------------------------------
+// For the cells in N (reached in this pass) the value is base + recorded level.  touched: the
+// tile already holds values -> min-merge, store only lowered cells; otherwise every word of the
+// tile is written (unreached / blocked cells = all-ones).  Adds the lowered cells to low[].
+// A runtime loop over the four byte positions keeps the code small (the kernel is instruction-
+// cache bound when fully unrolled: profiles/r02_notes.md).
 __device__ __forceinline__ void bfs_extract(const u32 (&rec)[BFS_NREC][2], const u32 N0, const u32 N1, const u32 base,
                                             u32 *cell0, const bool inx, const size_t strideY, const size_t strideZ,
-                                            u32 &low0, u32 &low1) {
+                                            const bool touched, u32 &low0, u32 &low1) {
     const u32 base2 = (base << 1) | 1u; // stored word of level 0
     u32 *pz = cell0;
-#pragma unroll
-    for (int w = 0; w < 2; ++w) {
-        const u32 Nw = w ? N1 : N0;
-        u32 loww = 0;
-#pragma unroll
-        for (int zb = 0; zb < 4; ++zb) {
-            // byte zb of the 7 planes + the "not reached" plane -> 8 x 8 bit matrix -> one byte per cell
-            const u32 sel = (u32)zb | ((u32)(4 + zb) << 4);
-            const u32 t01 = __byte_perm(rec[0][w], rec[1][w], sel);
-            const u32 t23 = __byte_perm(rec[2][w], rec[3][w], sel);
-            const u32 t45 = __byte_perm(rec[4][w], rec[5][w], sel);
-            const u32 t67 = __byte_perm(rec[6][w], ~Nw, sel);
-            u32 lo = __byte_perm(t01, t23, 0x5410u), hi = __byte_perm(t45, t67, 0x5410u);
-            bfs_transpose8(lo, hi);
-            u32 own[8];
-            if (TOUCHED) {
-                u32 *q = pz;
-#pragma unroll
-                for (int y = 0; y < 8; ++y) {
-                    own[y] = BFS_RAWINF;
-                    if ((Nw >> (zb * 8 + y)) & 1u) own[y] = __ldcg(q); // reached cells are free cells: inside the row
-                    q += strideY;
-                }
-            }
-            u32 *p = pz;
-#pragma unroll
-            for (int y = 0; y < 8; ++y) {
-                const u32 src = y < 4 ? lo : hi;
-                const u32 lv = __byte_perm(src, 0u, 0x4440u | (u32)(y & 3));
-                // a cell that was not reached has bit 7 of its byte set: the sign-replicating byte
-                // select turns that into an all-ones word ("unreached" in the stored format)
-                const u32 unr = bfs_byte_sign(src, y & 3);
-                const u32 word = unr | (base2 + (lv << 1));
-                if (TOUCHED) {
-                    const bool lower = word < own[y]; // stored words order like their values
-                    if (lower) bfs_store(p, word);
-                    loww |= (lower ? 1u : 0u) << (zb * 8 + y);
-                } else {
-                    if (inx) bfs_store(p, word);
-                }
-                p += strideY;
-            }
-            pz += strideZ;
-        }
-        if (TOUCHED) { if (w) low1 |= loww; else low0 |= loww; }
+#pragma unroll 1
+    for (u32 zb = 0; zb < 4; ++zb) {
+        low0 |= bfs_extract8(rec[0][0], rec[1][0], rec[2][0], rec[3][0], rec[4][0], rec[5][0], rec[6][0], N0, zb, base2,
+                             pz, strideY, inx, touched) << (zb * 8u);
+        low1 |= bfs_extract8(rec[0][1], rec[1][1], rec[2][1], rec[3][1], rec[4][1], rec[5][1], rec[6][1], N1, zb, base2,
+                             pz + 4 * strideZ, strideY, inx, touched) << (zb * 8u);
+        pz += strideZ;
     }
-    if (!TOUCHED) { low0 |= N0; low1 |= N1; }
 }
 
 // candidate value read across a face: halo + 1, or BFS_CINV if the halo cell is unreached
@@ -352,6 +384,8 @@ __device__ __forceinline__ u32 bfs_rel(const u32 c, const u32 base, u32 &far, u3
 }
 
 // ---- one tile activation -----------------------------------------------------------------------
+// SYNC: the phase-locked kernel (CTA barriers at the phase boundaries); false: free-running warps
+template <bool SYNC>
 __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, const int lane, BfsCount &cnt) {
     const GridDev &Gd = A.G;
     const int bx = (int)(t % (u32)A.nbx), by = (int)((t / (u32)A.nbx) % (u32)A.nby), bz = (int)(t / ((u32)A.nbx * (u32)A.nby));
@@ -361,11 +395,14 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
     u32 *cell0 = A.g + (size_t)z0 * sZ + (size_t)y0 * sY + (size_t)(x0 + lane);
     const bool peer_lo = bz == 0 && A.lo.g != nullptr, peer_hi = bz == A.nbz - 1 && A.hi.g != nullptr;
 
+    const long long tc0 = clock64();
     // ---- claim: take the dirty faces, keep Q (nobody else may process or queue the tile) ----
     u32 old = 0;
     if (lane == 0) old = atomicAnd(&A.state[t], BFS_Q | BFS_T);
     old = __shfl_sync(BFS_FULL, old, 0);
-    __threadfence(); // acquire: the neighbours' rows written before they set our dirty bits
+    // acquire: the neighbours' rows written before they set our dirty bits (system scope where a
+    // neighbour is another GPU)
+    if (peer_lo || peer_hi) __threadfence_system(); else bfs_fence();
     const u32 dirty = old & BFS_DIRTY;
     bool touched = (old & BFS_T) != 0u;
     ++cnt.act;
@@ -445,7 +482,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
         u32 h[8], o[8];
 #pragma unroll
         for (int y = 0; y < 8; ++y) {
-            h[y] = inx ? __ldcg(hrow + (size_t)y * sY) : BFS_RAWINF;
+            h[y] = inx ? (peer_lo ? bfs_ld_peer(hrow + (size_t)y * sY) : __ldcg(hrow + (size_t)y * sY)) : BFS_RAWINF;
             o[y] = (touched && inx) ? __ldcg(cell0 + (size_t)y * sY) : BFS_RAWINF;
         }
 #pragma unroll
@@ -460,7 +497,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
         u32 h[8], o[8];
 #pragma unroll
         for (int y = 0; y < 8; ++y) {
-            h[y] = inx ? __ldcg(hrow + (size_t)y * sY) : BFS_RAWINF;
+            h[y] = inx ? (peer_hi ? bfs_ld_peer(hrow + (size_t)y * sY) : __ldcg(hrow + (size_t)y * sY)) : BFS_RAWINF;
             o[y] = (touched && inx) ? __ldcg(cell0 + 7 * sZ + (size_t)y * sY) : BFS_RAWINF;
         }
 #pragma unroll
@@ -527,13 +564,15 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
 
     u32 low0 = 0, low1 = 0; // cells lowered by this activation
     u32 redo = 0;           // dirty faces to look at again (seeds beyond the range of one pass)
-    if (base != BFS_CINV) {
-        // ---- bit-sliced seed levels ----
-        BfsSeeds SA, SB;
-        u32 far = 0, lastA = 0, lastB = 0, anyA = 0, anyB = 0;
+    const bool active = base != BFS_CINV; // uniform: something to sweep from
+    BfsSeeds SA, SB;
 #pragma unroll
-        for (int b = 0; b < 6; ++b) SA.sp[b][0] = SA.sp[b][1] = SB.sp[b][0] = SB.sp[b][1] = 0u;
-        SA.sv[0] = SA.sv[1] = SB.sv[0] = SB.sv[1] = 0u;
+    for (int b = 0; b < 6; ++b) SA.sp[b][0] = SA.sp[b][1] = SB.sp[b][0] = SB.sp[b][1] = 0u;
+    SA.sv[0] = SA.sv[1] = SB.sv[0] = SB.sv[1] = 0u;
+    SA.last = SB.last = -1;
+    if (active) {
+        // ---- bit-sliced seed levels ----
+        u32 far = 0, lastA = 0, lastB = 0, anyA = 0, anyB = 0;
         {
             // relative levels, packed one byte per cell; bit 7 of a byte marks "no seed"
             u32 pYm[2] = {0, 0}, pYp[2] = {0, 0}, pZm[2] = {0, 0}, pZp[2] = {0, 0};
@@ -590,29 +629,46 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
             if (__any_sync(BFS_FULL, far != 0u)) redo = dirty;
         }
 
-        // ---- sweep, extract, store; continuation passes if a wave outlives the recordable range ----
-        u32 R0 = 0, R1 = 0, pbase = base;
-        for (;;) {
-            u32 rec[BFS_NREC][2];
-            u32 carry0, carry1;
+    }
+    cnt.c_setup += (u64)(clock64() - tc0);
+
+    // ---- sweep, extract, store; continuation passes if a wave outlives the recordable range ----
+    // (BFS_PHASE_SYNC: in the phase-locked kernel all warps of the CTA enter each phase together, so
+    // that they share its instructions in the instruction cache)
+    u32 R0 = 0, R1 = 0, pbase = base;
+    u32 rec[BFS_NREC][2];
+    u32 carry0 = 0, carry1 = 0;
+    if (SYNC) { BFS_PHASE_SYNC(); }
+    const long long tc1 = clock64();
+    if (active) {
+        cnt.levels += bfs_sweep(free0, free1, SA, SB, init0, init1, R0, R1, rec, carry0, carry1, lane);
+        ++cnt.passes;
+    }
+    const long long tc2 = clock64();
+    cnt.c_sweep += (u64)(tc2 - tc1);
+    if (SYNC) { BFS_PHASE_SYNC(); }
+    if (active) {
+        bfs_extract(rec, R0, R1, pbase, cell0, inx, sY, sZ, touched, low0, low1);
+        touched = true;
+        while (__any_sync(BFS_FULL, (carry0 | carry1) != 0u)) { // rare: a wave longer than one pass records
             const u32 P0 = R0, P1 = R1;
-            cnt.levels += bfs_sweep(free0, free1, SA, SB, init0, init1, R0, R1, rec, carry0, carry1, lane);
-            ++cnt.passes;
-            if (touched) bfs_extract<true>(rec, R0 & ~P0, R1 & ~P1, pbase, cell0, inx, sY, sZ, low0, low1);
-            else bfs_extract<false>(rec, R0 & ~P0, R1 & ~P1, pbase, cell0, inx, sY, sZ, low0, low1);
-            touched = true;
-            if (!__any_sync(BFS_FULL, (carry0 | carry1) != 0u)) break;
             init0 = carry0; init1 = carry1;
             pbase += BFS_LIM;
             SA.last = -1; SB.last = -1;
+            cnt.levels += bfs_sweep(free0, free1, SA, SB, init0, init1, R0, R1, rec, carry0, carry1, lane);
+            ++cnt.passes;
+            bfs_extract(rec, R0 & ~P0, R1 & ~P1, pbase, cell0, inx, sY, sZ, touched, low0, low1);
         }
         cnt.lowered += (u32)(__popc(low0) + __popc(low1));
     } else {
         ++cnt.idle;
     }
+    cnt.c_extract += (u64)(clock64() - tc2);
+    if (SYNC) { BFS_PHASE_SYNC(); }
 
     // ---- publish: every store above is visible before a neighbour is armed ----
-    __threadfence();
+    const long long tc3 = clock64();
+    if (peer_lo || peer_hi) __threadfence_system(); else bfs_fence();
     __syncwarp();
     // Which neighbours can use what this activation lowered?  Across a face that was NOT read in
     // this activation: any lowered boundary cell with a free cell behind it.  Across a face that
@@ -683,7 +739,8 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
 #pragma unroll
                 for (int y = 0; y < 8; ++y)
                     if ((czm >> y) & 1u) {
-                        const u32 own = __ldcg(cell0 + (size_t)y * sY), h = __ldcg(hrow + (size_t)y * sY);
+                        const u32 own = __ldcg(cell0 + (size_t)y * sY);
+                        const u32 h = peer_lo ? bfs_ld_peer(hrow + (size_t)y * sY) : __ldcg(hrow + (size_t)y * sY);
                         imp |= own + 2u < h;
                     }
             }
@@ -696,7 +753,8 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
 #pragma unroll
                 for (int y = 0; y < 8; ++y)
                     if ((czp >> (24 + y)) & 1u) {
-                        const u32 own = __ldcg(cell0 + 7 * sZ + (size_t)y * sY), h = __ldcg(hrow + (size_t)y * sY);
+                        const u32 own = __ldcg(cell0 + 7 * sZ + (size_t)y * sY);
+                        const u32 h = peer_hi ? bfs_ld_peer(hrow + (size_t)y * sY) : __ldcg(hrow + (size_t)y * sY);
                         imp |= own + 2u < h;
                     }
             }
@@ -748,7 +806,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
     const u32 pushes = __ballot_sync(BFS_FULL, need_push || requeue);
     const int np = __popc(pushes);
     if (np >= 2) {
-        if (lane == 0) { atomicAdd(&A.ctr[BFS_C_INFLIGHT], (u32)(np - 1)); __threadfence(); }
+        if (lane == 0) { atomicAdd(&A.ctr[BFS_C_INFLIGHT], (u32)(np - 1)); bfs_fence(); }
         __syncwarp();
     }
     if (need_push) bfs_push(A.ring, A.ring_cap, A.ctr, ntile);
@@ -757,37 +815,64 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
         if (atomicSub(&A.ctr[BFS_C_INFLIGHT], 1u) == 1u) bfs_rank_idle(A);
     }
     __syncwarp();
+    cnt.c_publish += (u64)(clock64() - tc3);
 }
 
 // ---- persistent warp loop --------------------------------------------------------------------------
-// `first`: this is the first warp of its rank -- it ends the search at once when the source was
-// rejected (blocked / outside the box: k_bfs_init left a flag and queued nothing)
-__device__ static inline void bfs_warp_main(const BfsArgs &A, const int lane, const bool first) {
-    if (first && lane == 0 && __ldcg(&A.ctr[BFS_C_SRC + 3]))
-        for (int r = 0; r < A.world; ++r) bfs_store_volatile(&A.peer_ctr[r][BFS_C_DONE], 1u);
-    BfsCount cnt;
+__device__ static inline void bfs_count_init(BfsCount &cnt) {
     cnt.act = cnt.idle = cnt.lowered = cnt.levels = cnt.passes = cnt.redo = cnt.remote = 0;
-    for (;;) {
-        u32 item = 0;
-        if (lane == 0) item = bfs_pop(A);
-        item = __shfl_sync(BFS_FULL, item, 0);
-        if (item == 0u) break;
-        bfs_process_tile(A, item - 1u, lane, cnt);
-    }
+    cnt.c_pop = cnt.c_setup = cnt.c_sweep = cnt.c_extract = cnt.c_publish = 0;
+}
+
+__device__ static inline void bfs_count_flush(const BfsArgs &A, BfsCount &cnt, const int lane) {
     cnt.lowered = __reduce_add_sync(BFS_FULL, cnt.lowered); // per-lane counters
     cnt.remote = __reduce_add_sync(BFS_FULL, cnt.remote);
-    if (lane == 0 && A.stats) {
-        if (cnt.act) {
-            atomicAdd((unsigned long long *)&A.stats[1], (unsigned long long)cnt.act);
-            atomicAdd((unsigned long long *)&A.stats[2], (unsigned long long)cnt.lowered);
-            atomicAdd((unsigned long long *)&A.stats[3], (unsigned long long)cnt.lowered * 6ull);
-            atomicAdd((unsigned long long *)&A.stats[12], (unsigned long long)cnt.levels);
-            atomicAdd((unsigned long long *)&A.stats[13], (unsigned long long)cnt.idle);
-            atomicAdd((unsigned long long *)&A.stats[14], (unsigned long long)cnt.passes);
-            atomicAdd((unsigned long long *)&A.stats[5], (unsigned long long)cnt.redo);
-            atomicAdd((unsigned long long *)&A.stats[7], (unsigned long long)cnt.remote);
-        }
+    if (lane == 0 && A.stats && cnt.act) {
+        atomicAdd((unsigned long long *)&A.stats[1], (unsigned long long)cnt.act);
+        atomicAdd((unsigned long long *)&A.stats[2], (unsigned long long)cnt.lowered);
+        // phase cycles: [4] waiting for work, [6] claim + occupancy + halo candidates + seeds, [11] level
+        // sweeps, [3] levels -> words + stores, [0] fence + arming + release + pushes
+        atomicAdd((unsigned long long *)&A.stats[4], (unsigned long long)cnt.c_pop);
+        atomicAdd((unsigned long long *)&A.stats[6], (unsigned long long)cnt.c_setup);
+        atomicAdd((unsigned long long *)&A.stats[11], (unsigned long long)cnt.c_sweep);
+        atomicAdd((unsigned long long *)&A.stats[3], (unsigned long long)cnt.c_extract);
+        atomicAdd((unsigned long long *)&A.stats[0], (unsigned long long)cnt.c_publish);
+        atomicAdd((unsigned long long *)&A.stats[12], (unsigned long long)cnt.levels);
+        atomicAdd((unsigned long long *)&A.stats[13], (unsigned long long)cnt.idle);
+        atomicAdd((unsigned long long *)&A.stats[14], (unsigned long long)cnt.passes);
+        atomicAdd((unsigned long long *)&A.stats[5], (unsigned long long)cnt.redo);
+        atomicAdd((unsigned long long *)&A.stats[7], (unsigned long long)cnt.remote);
     }
+}
+
+// the first warp of a rank ends the search at once when the source was rejected (blocked /
+// outside the box: k_bfs_init left a flag and queued nothing)
+__device__ static inline void bfs_reject_check(const BfsArgs &A, const int lane, const bool first) {
+    if (first && lane == 0 && __ldcg(&A.ctr[BFS_C_SRC + 3]))
+        for (int r = 0; r < A.world; ++r) bfs_store_volatile(&A.peer_ctr[r][BFS_C_DONE], 1u);
+}
+
+// free-running form: every warp loops pop -> process on its own (the CPU emulator and the slab
+// group kernel; the single-rank kernel k_bfs keeps the warps of a CTA in the same phase instead)
+__device__ static inline void bfs_warp_main(const BfsArgs &A, const int lane, const bool first) {
+    bfs_reject_check(A, lane, first);
+    BfsCount cnt;
+    bfs_count_init(cnt);
+    BfsPop P;
+    P.ticket = 0; P.have = 0; P.t0 = 0;
+    for (;;) {
+        u32 item = 0;
+        const long long tp = clock64();
+        if (lane == 0) {
+            bool done = false;
+            do item = bfs_pop_try(A, P, 0xFFFFFFFFu, done); while (!item && !done);
+        }
+        item = __shfl_sync(BFS_FULL, item, 0);
+        if (item == 0u) break;
+        cnt.c_pop += (u64)(clock64() - tp);
+        bfs_process_tile<false>(A, item - 1u, lane, cnt);
+    }
+    bfs_count_flush(A, cnt, lane);
 }
 
 // after the search: tiles that were never touched hold no values yet -> all-ones (unreached)

@@ -21,9 +21,11 @@ def env6(occ):
 def main():
     rng = np.random.default_rng(0)
     ok = True
+    quick = "--quick" in sys.argv
+    sizes = [int(a) for a in sys.argv[1:] if a.isdigit()] or [256, 512]
     keep = oracle.motion_costs(oracle.MOTIONS_3D) == 1.0
     motions, mg = oracle.MOTIONS_3D[keep], oracle.motion_costs(oracle.MOTIONS_3D)[keep]
-    for shape, dens in (((40, 24, 20), 0.1), ((48, 17, 9), 0.3), ((70, 33, 41), 0.35), ((33, 9, 9), 0.05),
+    for shape, dens in () if quick else (((40, 24, 20), 0.1), ((48, 17, 9), 0.3), ((70, 33, 41), 0.35), ((33, 9, 9), 0.05),
                         ((130, 70, 50), 0.2), ((96, 96, 96), 0.25), ((16, 8, 8), 0.0), ((200, 40, 24), 0.4)):
         occ = rng.random(shape) < dens
         free = np.argwhere(~occ)
@@ -45,7 +47,7 @@ def main():
     ok &= not np.isfinite(f).any()
     # bigger: the c5 block at 256^3, certificate + timing
     import torch
-    for n in (256, 512):
+    for n in sizes:
         blk, _ = workloads.replicated_boxes3d(base=128, reps=n // 128)
         occ = workloads.replicated_slab(blk, (n, n, n), 0, n)
         env = env6(occ)
@@ -61,8 +63,11 @@ def main():
         _lib.check(dg.L.pmp_verify_field(dg.handle, _lib.W_U32, ws.g.data_ptr(), src.data_ptr(), 0, n, out.data_ptr(), dg.stream()), "verify")
         bad, reached, pend = (int(v) for v in out.cpu())
         s = ws.stats.cpu().numpy()
+        na = max(int(s[1]), 1)
+        ph = {k: round(float(s[i]) / na / 1965.0, 2) for k, i in (("wait", 4), ("setup", 6), ("sweep", 11), ("extract", 3), ("publish", 0))}
         print(f"c5 {n}^3: {dt*1e3:.2f} ms wall, kernel {s[8]/1e6:.2f} ms, certificate violations {bad}, reached {reached}, pending {pend}, "
-              f"activations {s[1]} (idle {s[13]}) lowered {s[2]} levels {s[12]} passes {s[14]} requeues {s[5]} err {s[15]} status {ws.status.cpu().tolist()}", flush=True)
+              f"activations {s[1]} (idle {s[13]}) lowered {s[2]} levels {s[12]} passes {s[14]} requeues {s[5]} err {s[15]} "
+              f"status {ws.status.cpu().tolist()} us/activation/warp {ph}", flush=True)
         ok &= bad == 0 and pend == 0 and s[15] == 0
     print("ALL OK" if ok else "FAILED")
     return 0 if ok else 1
