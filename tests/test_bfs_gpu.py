@@ -133,7 +133,7 @@ def test_slab_multi_gpu_torchrun():
     world = 2 if ng < 4 else 4
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.join(ROOT, "tools", "run_bfs_slab.py"),
-           "--n", str(n), "--steps", "2", "--verify", "--reached", str(reached)]
+           "--size", str(n), "--steps", "2", "--verify", "--reached", str(reached)]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-3000:]
     line = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])

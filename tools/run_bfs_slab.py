@@ -1,7 +1,7 @@
 """One rank of the z-slab field solver with device-side halo exchange (pmp_bfs_slab_*).
 
     torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
-        tools/run_bfs_slab.py --n 768 [--steps 3] [--verify] [--reached R]
+        tools/run_bfs_slab.py --size 768 [--steps 3] [--verify] [--reached R]
 
 The grid is BASELINE.json config 5's: the 128^3 box block replicated to n^3, 6-connected unit
 weights, source (1,1,1).  Rank 0 prints one JSON line: device time per search (max over ranks),
@@ -17,7 +17,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=768)
+    ap.add_argument("--size", dest="n", type=int, default=768)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--verify", action="store_true")
     ap.add_argument("--reached", type=int, default=0, help="expected number of reached cells (0: do not check)")
