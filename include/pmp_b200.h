@@ -268,6 +268,18 @@ int pmp_slab_run(pmp_grid *g, const pmp_sssp_params *params, void *g_dev, void *
 int pmp_slab_merge(pmp_grid *g, int weight, void *g_dev, void *ws_dev, int64_t ws_bytes,
                    int z_local, int mark, const void *plane_dev, uint64_t *out_dev, void *stream);
 
+/* Full unit-weight cost-to-go field WITHOUT any allocation (no counterpart in the reference; added
+ * for callers that cannot call cudaMalloc: CUDA graph capture,
+ * tight serving loops).  Same result as pmp_sssp(full_field = 1, weight = PMP_W_U32) on a 3D grid whose
+ * motion table is the six unit moves, but the workspace lives in a static device array of 1 MiB inside
+ * the library (held by every GPU that loads it): grids up to ~126 000 tiles of 32 x 8 x 8 cells (e.g.
+ * 512^3); larger grids are rejected with an error.  start_dev: int32[3]; g_dev: pcells uint32 in the
+ * search's word format ((value << 1) | 1, all-ones = unreached; pmp_field_finalize decodes);
+ * status_dev (1 x int32) / stats_dev (16 x uint64) may be NULL.  All calls share the array: calls that
+ * overlap on one GPU (two streams, two threads) race -- serialise them. */
+int pmp_cost_field_u32_static(pmp_grid *g, const int32_t *start_dev, uint32_t *g_dev, int32_t *status_dev,
+                              uint64_t *stats_dev, void *stream);
+
 /* ---- z-slabs with device-side halo exchange (round 2): the unit-weight field of BASELINE.json
  *      config 5 (6-connected, cost 1: the field Dijkstra3D.plan computes with env.motions filtered
  *      to the unit moves, dijkstra3d.py:39-126) split over up to 8 GPUs of one node.  Rank p owns

@@ -40,7 +40,7 @@ SYMBOLS = (
     "pmp_line_of_sight", "pmp_shortcut_paths",
     "pmp_bfs_slab_create", "pmp_bfs_slab_destroy", "pmp_bfs_slab_export", "pmp_bfs_slab_connect",
     "pmp_bfs_slab_connect_local", "pmp_bfs_slab_begin", "pmp_bfs_slab_run", "pmp_bfs_slab_run_group",
-    "pmp_bfs_slab_buffers",
+    "pmp_bfs_slab_buffers", "pmp_cost_field_u32_static",
 )
 
 
@@ -125,6 +125,7 @@ def lib():
         "pmp_bfs_slab_run": [vp, vp, vp, vp],
         "pmp_bfs_slab_run_group": [vp, i32, vp],
         "pmp_bfs_slab_buffers": [vp, vp, vp, vp, vp],
+        "pmp_cost_field_u32_static": [vp, vp, vp, vp, vp, vp],
         "pmp_line_of_sight": [vp, i64, vp, vp, vp, vp],
         "pmp_shortcut_paths": [vp, i64, vp, i64, vp, vp, vp, vp, vp],
         "pmp_replan_begin": [vp, ctypes.POINTER(SsspParams), vp, vp, vp, vp, i64, vp, vp, vp, vp],

@@ -264,6 +264,66 @@ int pmp_bfs_field(pmp_grid *g, const int32_t *start_dev, void *g_dev, void *ws_d
 }
 
 // ---------------------------------------------------------------------------------------------
+// pmp_cost_field_u32_static: the same search with its workspace (tile states, ring, counters) in a
+// file-scope device array instead of caller memory -- for callers that cannot allocate (CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Allocates nothing: no cudaMalloc / cudaFree, no
+// allocating library call.  Limit: the workspace of the grid must fit PMP_STATIC_WS_BYTES (1 MiB:
+// grids up to ~126 000 tiles of 32 x 8 x 8 cells, e.g. 512^3).  Every GPU that loads the library holds
+// the array until exit.  All calls share it: it keeps the last call's contents (every word a search
+// reads is cleared at the start of the call), and calls that overlap on one GPU race.
+// ---------------------------------------------------------------------------------------------
+#define PMP_STATIC_WS_BYTES (1u << 20)
+static __device__ __align__(256) unsigned char g_bfs_static_ws[PMP_STATIC_WS_BYTES];
+
+// In host code `g_bfs_static_ws` is a host-side stand-in, not a device address: resolve it once per
+// device, with that device current.
+static int bfs_static_ws_ptr(void **out) {
+    static void *ptr[64] = {nullptr};
+    int dev = 0;
+    PMP_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { pmp_set_error("pmp_cost_field_u32_static: device index %d not supported", dev); return -1; }
+    if (!ptr[dev]) {
+        void *p = nullptr;
+        PMP_CHECK_CUDA(cudaGetSymbolAddress(&p, g_bfs_static_ws));
+        ptr[dev] = p;
+    }
+    *out = ptr[dev];
+    return 0;
+}
+
+extern "C" int pmp_cost_field_u32_static(pmp_grid *g, const int32_t *start_dev, uint32_t *g_dev, int32_t *status_dev,
+                                         uint64_t *stats_dev, void *stream) {
+    if (!g || !start_dev || !g_dev) { pmp_set_error("pmp_cost_field_u32_static: bad arguments"); return -1; }
+    if (!pmp_bfs_applicable(g)) {
+        pmp_set_error("pmp_cost_field_u32_static: needs a 3D grid whose motion table is the six unit moves");
+        return -1;
+    }
+    int dev = 0;
+    PMP_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev != g->device) { pmp_set_error("pmp_cost_field_u32_static: the grid lives on device %d, current device is %d", g->device, dev); return -1; }
+    const BfsLayout L = bfs_layout(g);
+    if (L.total > (size_t)PMP_STATIC_WS_BYTES) {
+        pmp_set_error("pmp_cost_field_u32_static: grid of %u tiles needs %zu B of workspace, the static array holds %u B "
+                      "(use pmp_sssp with caller memory)", L.ntiles, L.total, PMP_STATIC_WS_BYTES);
+        return -1;
+    }
+    void *ws = nullptr;
+    if (bfs_static_ws_ptr(&ws)) return -2;
+    cudaStream_t s = (cudaStream_t)stream;
+    BfsArgs A;
+    bfs_fill_args(g, g_dev, ws, L, A);
+    if (bfs_reset_ws(A, L, s)) return -2; // the array keeps the last call's contents: clear what a search reads
+    k_bfs_init<<<1, 1, 0, s>>>(A, start_dev, status_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    if (bfs_launch_search(A, s)) return -2;
+    if (bfs_launch_fill(A, s)) return -2;
+    k_bfs_finish<<<1, 1, 0, s>>>(A, nullptr, status_dev, (u64 *)stats_dev);
+    PMP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 // z-slabs over several GPUs (BASELINE.json config 5).
 //
 // Rank p owns the planes [z0, z1) of the grid (z0, z1 multiples of 8 except the last z1) as its
