@@ -24,6 +24,9 @@
 #ifndef BFS_SYNC_NT
 #define BFS_SYNC_NT 128 // threads per CTA of the phase-locked kernel (4 warps in step; measured best of 128 / 256 / 512)
 #endif
+#ifndef BFS_SYNC_MINB
+#define BFS_SYNC_MINB 4 // resident CTAs per SM of the phase-locked kernel (122 registers, no spills)
+#endif
 #define BFS_RING_SLACK 8192
 
 // The search kernel.  Persistent; one warp per tile activation.  The kernel's code is far larger
@@ -32,9 +35,9 @@
 // of "no instruction" stall per issued instruction, profiles/r02_notes.md).  So the warps of a CTA
 // move through the phases in step: CTA barriers at the phase boundaries (BFS_PHASE_SYNC inside
 // bfs_process_tile), warps without a tile take the same barriers.  A warp may therefore not block in
-// the queue while its CTA waits for it: it polls its ring slot a few times (bfs_pop_try keeps the
+// the queue while its CTA waits for it: it polls the ring a few times (bfs_pop_warp keeps the
 // ticket) and joins the round empty-handed otherwise.
-__global__ void __launch_bounds__(512, 1) k_bfs(const __grid_constant__ BfsArgs A) {
+__global__ void __launch_bounds__(BFS_SYNC_NT, BFS_SYNC_MINB) k_bfs(const __grid_constant__ BfsArgs A) {
     const int lane = (int)(threadIdx.x & 31);
     bfs_reject_check(A, lane, blockIdx.x == 0 && threadIdx.x < 32);
     BfsCount cnt;
@@ -42,17 +45,11 @@ __global__ void __launch_bounds__(512, 1) k_bfs(const __grid_constant__ BfsArgs 
     BfsPop P;
     P.ticket = 0; P.have = 0; P.t0 = 0;
     for (;;) {
-        u32 item = 0, fin = 0;
         const long long tp = clock64();
-        if (lane == 0) {
-            bool done = false;
-            item = bfs_pop_try(A, P, BFS_TRY_POLLS, done);
-            fin = done ? 1u : 0u;
-        }
-        item = __shfl_sync(BFS_FULL, item, 0);
-        fin = __shfl_sync(BFS_FULL, fin, 0);
+        bool done = false;
+        const u32 item = bfs_pop_warp(A, P, lane, BFS_TRY_POLLS, done);
         if (!__syncthreads_or(item != 0u)) {          // nobody in the CTA has work
-            if (__syncthreads_and(fin != 0u)) break;  // ... and the search is over for everyone
+            if (__syncthreads_and(done)) break;       // ... and the search is over for everyone
             continue;
         }
         if (item) {
@@ -189,7 +186,7 @@ static int bfs_launch_shape(BfsLaunch *out) {
         const char *f = getenv("PMP_B200_BFS_FREE");
         L.free_running = f && atoi(f) != 0;
         const char *t = getenv("PMP_B200_BFS_NT");
-        L.nt = L.free_running ? BFS_NT : (t && atoi(t) >= 32 && atoi(t) <= 512 && atoi(t) % 32 == 0 ? atoi(t) : BFS_SYNC_NT);
+        L.nt = L.free_running ? BFS_NT : (t && atoi(t) >= 32 && atoi(t) <= BFS_SYNC_NT && atoi(t) % 32 == 0 ? atoi(t) : BFS_SYNC_NT);
         if (L.free_running) PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs_free, L.nt, 0));
         else PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs, L.nt, 0));
         PMP_CHECK_CUDA(cudaGetDevice(&dev));

@@ -168,41 +168,76 @@ __device__ __noinline__ static void bfs_fail(const BfsArgs &A, u32 code) {
     for (int r = 0; r < A.world; ++r) bfs_store_volatile(&A.peer_ctr[r][BFS_C_DONE], 1u);
 }
 
-// lane 0's position in the ring: a ticket stays valid across calls of bfs_pop_try until it is served
+// A warp's position in the ring: the ticket stays valid across calls of bfs_pop_warp until it is
+// served (identical in all lanes).
 struct BfsPop {
     u32 ticket, have;
-    u64 t0; // when the current wait began (time-out safety net)
+    u64 t0; // lane 0: when the current wait began (time-out safety net)
 };
+#define BFS_TOMB 0xFFFFFFFFu // ring slot: "the item of this ticket was taken by another warp"
 
-// lane 0: try to take the next tile.  Returns tile id + 1; or 0 with `done` set when the search is
-// over; or 0 with `done` clear when nothing arrived within max_polls polls (the ticket is kept).
-__device__ static inline u32 bfs_pop_try(const BfsArgs &A, BfsPop &P, const unsigned max_polls, bool &done) {
+// The whole warp: try to take a tile.  Returns tile id + 1; or 0 with `done` set when the search is
+// over; or 0 with `done` clear when nothing turned up within max_polls polls (the ticket is kept).
+//
+// Tickets spread the consumers over the slots, but an item is not bound to its ticket holder: a warp
+// whose own slot is still empty also looks at the 31 slots before it and takes the oldest item it
+// finds there.  Those belong to warps that cannot serve their ticket right now (in the phase-locked
+// kernel a warp without a tile sits out its CTA's round at the barriers); without this an item
+// could wait a whole round while other warps idle, and the wave would run out of order.  The taker
+// leaves a tombstone, so the holder knows to draw a new ticket.
+__device__ static inline u32 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int lane, const unsigned max_polls,
+                                          bool &done) {
     done = false;
-    if (!P.have) {
-        P.ticket = atomicAdd(&A.ctr[BFS_C_HEAD], 1u);
-        P.have = 1u;
-        P.t0 = 0;
-        if (A.max_pops && P.ticket > A.max_pops) { bfs_fail(A, BFS_ERR_BUDGET); done = true; return 0u; }
-    }
-    u32 *slot = &A.ring[P.ticket % A.ring_cap];
     unsigned ns = 32;
     for (unsigned polls = 0;; ++polls) {
-        const u32 v = __ldcg(slot);
-        if (v) {
-            bfs_store_volatile(slot, 0u); // recycle; the ring has more slots than tiles + waiting warps
-            bfs_fence();
-            P.have = 0u;
-            return v;
+        if (!P.have) {
+            u32 t = 0;
+            if (lane == 0) t = atomicAdd(&A.ctr[BFS_C_HEAD], 1u);
+            P.ticket = __shfl_sync(BFS_FULL, t, 0);
+            P.have = 1u;
+            if (A.max_pops && P.ticket > A.max_pops) {
+                if (lane == 0) bfs_fail(A, BFS_ERR_BUDGET);
+                done = true;
+                return 0u;
+            }
         }
-        if (__ldcg(&A.ctr[BFS_C_DONE])) { done = true; return 0u; }
+        const u32 idx = P.ticket - 31u + (u32)lane; // lane 31: my own slot
+        u32 *slot = &A.ring[idx % A.ring_cap];
+        const u32 v = (int)idx >= 0 ? __ldcg(slot) : 0u;
+        const u32 own = __shfl_sync(BFS_FULL, v, 31);
+        if (own == BFS_TOMB) { // my item went to another warp: clear the slot, draw a new ticket
+            if (lane == 31) bfs_store_volatile(slot, 0u);
+            P.have = 0u;
+            continue;
+        }
+        const u32 m = __ballot_sync(BFS_FULL, v != 0u && v != BFS_TOMB);
+        if (m) {
+            const int l = (m >> 31) ? 31 : __ffs(m) - 1; // my own, else the oldest one waiting for a busy warp
+            u32 got = 0;
+            if (lane == l) got = atomicCAS(slot, v, l == 31 ? 0u : BFS_TOMB) == v ? v : 0u;
+            got = __shfl_sync(BFS_FULL, got, l);
+            if (got) {
+                bfs_fence();
+                if (l == 31) P.have = 0u;
+                P.t0 = 0;
+                return got;
+            }
+            continue; // somebody else was faster: look again at once
+        }
+        u32 flag = 0;
+        if (lane == 0) {
+            if (__ldcg(&A.ctr[BFS_C_DONE])) flag = 1u;
+            else if (A.timeout_ns && (polls & 1023u) == 1023u) {
+                const u64 now = bfs_now_ns();
+                if (!P.t0) P.t0 = now;
+                else if (now - P.t0 > A.timeout_ns) { bfs_fail(A, BFS_ERR_TIMEOUT); flag = 1u; }
+            }
+        }
+        flag = __shfl_sync(BFS_FULL, flag, 0);
+        if (flag) { done = true; return 0u; }
         if (polls >= max_polls) return 0u;
         __nanosleep(ns);
         if (ns < 1024) ns *= 2;
-        if (A.timeout_ns && (polls & 1023u) == 1023u) {
-            const u64 now = bfs_now_ns();
-            if (!P.t0) P.t0 = now;
-            else if (now - P.t0 > A.timeout_ns) { bfs_fail(A, BFS_ERR_TIMEOUT); done = true; return 0u; }
-        }
     }
 }
 
@@ -231,7 +266,6 @@ struct BfsSeeds {
 __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const BfsSeeds &SA, const BfsSeeds &SB,
                                          const u32 init0, const u32 init1, u32 &R0, u32 &R1, u32 (&rec)[BFS_NREC][2],
                                          u32 &carry0, u32 &carry1, const int lane) {
-    const u32 mUp = lane > 0 ? BFS_FULL : 0u, mDn = lane < 31 ? BFS_FULL : 0u;
 #pragma unroll
     for (int b = 0; b < BFS_NREC; ++b) rec[b][0] = rec[b][1] = 0u;
     u32 c0 = init0, c1 = init1;
@@ -295,8 +329,9 @@ __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const
             u32 n1 = ((f1 << 1) & 0xFEFEFEFEu) | ((f1 >> 1) & 0x7F7F7F7Fu) | (f1 << 8) | (f1 >> 8) | (f0 >> 24);
             const u32 u0 = __shfl_up_sync(BFS_FULL, f0, 1), u1 = __shfl_up_sync(BFS_FULL, f1, 1);
             const u32 d0 = __shfl_down_sync(BFS_FULL, f0, 1), d1 = __shfl_down_sync(BFS_FULL, f1, 1);
-            n0 |= (u0 & mUp) | (d0 & mDn);
-            n1 |= (u1 & mUp) | (d1 & mDn);
+            // (lane 0 / 31 get their own word back from the shuffle: those cells are in R already)
+            n0 |= u0 | d0;
+            n1 |= u1 | d1;
             c0 = n0 & free0 & ~R0;
             c1 = n1 & free1 & ~R1;
             ++nlev;
@@ -396,6 +431,29 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
     const bool peer_lo = bz == 0 && A.lo.g != nullptr, peer_hi = bz == A.nbz - 1 && A.hi.g != nullptr;
 
     const long long tc0 = clock64();
+    // ---- occupancy words (read-only during a search): issued before the claim so that their
+    // latency overlaps the claim's round trip ----
+    const int ly = lane & 7, lzq = lane >> 3; // the (y, z & 3) this lane handles in row-distributed steps
+    const u32 *brow = Gd.bits + ((size_t)(z0 + lzq) * Gd.PY + (size_t)(y0 + ly)) * Gd.wpr + bx;
+    const size_t w1 = (size_t)4 * Gd.PY * Gd.wpr;
+    const u32 oc0 = __ldg(brow), oc1 = __ldg(brow + w1);
+    u32 onb = BFS_FULL; // rows behind the y / z faces; outside the box: blocked
+    {
+        const int i = lane & 7;
+        if (lane < 8) { if (by > 0) onb = __ldg(Gd.bits + ((size_t)(z0 + i) * Gd.PY + (size_t)(y0 - 1)) * Gd.wpr + bx); }
+        else if (lane < 16) { if (by < A.nby - 1) onb = __ldg(Gd.bits + ((size_t)(z0 + i) * Gd.PY + (size_t)(y0 + 8)) * Gd.wpr + bx); }
+        else if (lane < 24) {
+            if (bz > 0) onb = __ldg(Gd.bits + ((size_t)(z0 - 1) * Gd.PY + (size_t)(y0 + i)) * Gd.wpr + bx);
+            else if (peer_lo) onb = 0u; // the peer's occupancy is not mapped here: assume free (conservative)
+        } else {
+            if (bz < A.nbz - 1) onb = __ldg(Gd.bits + ((size_t)(z0 + 8) * Gd.PY + (size_t)(y0 + i)) * Gd.wpr + bx);
+            else if (peer_hi) onb = 0u;
+        }
+    }
+    u32 xa0 = BFS_FULL, xa1 = BFS_FULL, xb0 = BFS_FULL, xb1 = BFS_FULL; // words left / right of the tile's
+    if (bx > 0) { xa0 = __ldg(brow - 1); xa1 = __ldg(brow - 1 + w1); }
+    if (bx < A.nbx - 1) { xb0 = __ldg(brow + 1); xb1 = __ldg(brow + 1 + w1); }
+
     // ---- claim: take the dirty faces, keep Q (nobody else may process or queue the tile) ----
     u32 old = 0;
     if (lane == 0) old = atomicAnd(&A.state[t], BFS_Q | BFS_T);
@@ -407,105 +465,60 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
     bool touched = (old & BFS_T) != 0u;
     ++cnt.act;
 
-    // ---- occupancy: rows -> this lane's column bits ----
-    const int ly = lane & 7, lzq = lane >> 3; // the (y, z & 3) this lane handles in row-distributed steps
-    u32 free0, free1;
-    {
-        const u32 *brow = Gd.bits + ((size_t)(z0 + lzq) * Gd.PY + (size_t)(y0 + ly)) * Gd.wpr + bx;
-        const u32 o0 = __ldg(brow), o1 = __ldg(brow + (size_t)4 * Gd.PY * Gd.wpr);
-        free0 = ~bfs_transpose32(o0, lane);
-        free1 = ~bfs_transpose32(o1, lane);
-    }
-    // free cells on the far side of each face (a neighbour tile is only armed through them)
+    // ---- occupancy rows -> this lane's column bits; free cells on the far side of each face (a
+    // neighbour tile is only armed through them) ----
+    const u32 free0 = ~bfs_transpose32(oc0, lane), free1 = ~bfs_transpose32(oc1, lane);
     u32 ymf0, ymf1, ypf0, ypf1, zmf, zpf, xmf0, xmf1, xpf0, xpf1;
     {
-        u32 o = BFS_FULL; // outside the box: blocked
-        const int i = lane & 7;
-        if (lane < 8) { if (by > 0) o = __ldg(Gd.bits + ((size_t)(z0 + i) * Gd.PY + (size_t)(y0 - 1)) * Gd.wpr + bx); }
-        else if (lane < 16) { if (by < A.nby - 1) o = __ldg(Gd.bits + ((size_t)(z0 + i) * Gd.PY + (size_t)(y0 + 8)) * Gd.wpr + bx); }
-        else if (lane < 24) {
-            if (bz > 0) o = __ldg(Gd.bits + ((size_t)(z0 - 1) * Gd.PY + (size_t)(y0 + i)) * Gd.wpr + bx);
-            else if (peer_lo) o = 0u; // the peer's occupancy is not mapped here: assume free (conservative)
-        } else {
-            if (bz < A.nbz - 1) o = __ldg(Gd.bits + ((size_t)(z0 + 8) * Gd.PY + (size_t)(y0 + i)) * Gd.wpr + bx);
-            else if (peer_hi) o = 0u;
-        }
-        const u32 nf = ~bfs_transpose32(o, lane);
+        const u32 nf = ~bfs_transpose32(onb, lane);
         ymf0 = bfs_spread4(nf); ymf1 = bfs_spread4(nf >> 4);
         ypf0 = bfs_spread4(nf >> 8) << 7; ypf1 = bfs_spread4(nf >> 12) << 7;
         zmf = (nf >> 16) & 0xFFu;
         zpf = nf & 0xFF000000u;
-        const u32 *brow = Gd.bits + ((size_t)(z0 + lzq) * Gd.PY + (size_t)(y0 + ly)) * Gd.wpr + bx;
-        const size_t w1 = (size_t)4 * Gd.PY * Gd.wpr;
-        u32 a0 = BFS_FULL, a1 = BFS_FULL, b0 = BFS_FULL, b1 = BFS_FULL;
-        if (bx > 0) { a0 = __ldg(brow - 1); a1 = __ldg(brow - 1 + w1); }
-        if (bx < A.nbx - 1) { b0 = __ldg(brow + 1); b1 = __ldg(brow + 1 + w1); }
-        xmf0 = __ballot_sync(BFS_FULL, !(a0 >> 31)); xmf1 = __ballot_sync(BFS_FULL, !(a1 >> 31));
-        xpf0 = __ballot_sync(BFS_FULL, !(b0 & 1u)); xpf1 = __ballot_sync(BFS_FULL, !(b1 & 1u));
+        xmf0 = __ballot_sync(BFS_FULL, !(xa0 >> 31)); xmf1 = __ballot_sync(BFS_FULL, !(xa1 >> 31));
+        xpf0 = __ballot_sync(BFS_FULL, !(xb0 & 1u)); xpf1 = __ballot_sync(BFS_FULL, !(xb1 & 1u));
     }
 
     // ---- candidates across the dirty faces: halo + 1 where it beats the own boundary value ----
+    // The four y / z faces run through ONE loop body (runtime face index, results rotated through
+    // the four register arrays): a quarter of the code of four unrolled copies -- the kernel is
+    // instruction-cache sensitive.  Face f: 0 = y-, 1 = y+, 2 = z-, 3 = z+ (dirty bit 4 << f).
     u32 cYm[8], cYp[8], cZm[8], cZp[8], cXm[2], cXp[2];
 #pragma unroll
     for (int i = 0; i < 8; ++i) cYm[i] = cYp[i] = cZm[i] = cZp[i] = BFS_CINV;
     cXm[0] = cXm[1] = cXp[0] = cXp[1] = BFS_CINV;
-    if (dirty & 4u) { // y-: halo rows (y0 - 1, z), own cells (y = 0, z)
-        u32 h[8], o[8];
+#pragma unroll 1
+    for (int f = 0; f < 4; ++f) {
+        u32 tc[8];
 #pragma unroll
-        for (int z = 0; z < 8; ++z) {
-            h[z] = inx ? __ldcg(cell0 + (size_t)z * sZ - sY) : BFS_RAWINF;
-            o[z] = (touched && inx) ? __ldcg(cell0 + (size_t)z * sZ) : BFS_RAWINF;
+        for (int i = 0; i < 8; ++i) tc[i] = BFS_CINV;
+        if ((dirty >> (f + 2)) & 1u) {
+            const bool yface = f < 2, hiside = (f & 1) != 0;
+            const bool peer = f == 2 ? peer_lo : (f == 3 ? peer_hi : false);
+            const size_t step = yface ? sZ : sY; // between the 8 rows of the face
+            // halo rows: the neighbour's boundary rows (on the lowest / highest tile row of a slab the peer GPU's)
+            const u32 *hrow = yface ? (hiside ? cell0 + 8 * sY : cell0 - sY)
+                                    : (f == 2 ? (peer_lo ? A.lo.g + (size_t)A.lo.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 - sZ)
+                                              : (peer_hi ? A.hi.g + (size_t)A.hi.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 + 8 * sZ));
+            const u32 *orow = yface ? (hiside ? cell0 + 7 * sY : cell0) : (hiside ? cell0 + 7 * sZ : cell0);
+            const u32 shb = yface ? (hiside ? 7u : 0u) : (hiside ? 24u : 0u);
+            const u32 fw_lo = yface ? free0 : (hiside ? free1 : free0), fw_hi = yface ? free1 : fw_lo;
+            u32 h[8], o[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                h[i] = inx ? (peer ? bfs_ld_peer(hrow + (size_t)i * step) : __ldcg(hrow + (size_t)i * step)) : BFS_RAWINF;
+                o[i] = (touched && inx) ? __ldcg(orow + (size_t)i * step) : BFS_RAWINF;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const u32 c = bfs_cand(h[i]);
+                const u32 sh = shb + (yface ? (u32)((i & 3) * 8) : (u32)i);
+                const u32 fr = ((i < 4 ? fw_lo : fw_hi) >> sh) & 1u;
+                tc[i] = (fr && c != BFS_CINV && c < (o[i] >> 1)) ? c : BFS_CINV;
+            }
         }
 #pragma unroll
-        for (int z = 0; z < 8; ++z) {
-            const u32 c = bfs_cand(h[z]);
-            const u32 fr = ((z < 4 ? free0 : free1) >> ((z & 3) * 8)) & 1u;
-            cYm[z] = (fr && c != BFS_CINV && c < (o[z] >> 1)) ? c : BFS_CINV;
-        }
-    }
-    if (dirty & 8u) { // y+
-        u32 h[8], o[8];
-#pragma unroll
-        for (int z = 0; z < 8; ++z) {
-            h[z] = inx ? __ldcg(cell0 + (size_t)z * sZ + 8 * sY) : BFS_RAWINF;
-            o[z] = (touched && inx) ? __ldcg(cell0 + (size_t)z * sZ + 7 * sY) : BFS_RAWINF;
-        }
-#pragma unroll
-        for (int z = 0; z < 8; ++z) {
-            const u32 c = bfs_cand(h[z]);
-            const u32 fr = ((z < 4 ? free0 : free1) >> ((z & 3) * 8 + 7)) & 1u;
-            cYp[z] = (fr && c != BFS_CINV && c < (o[z] >> 1)) ? c : BFS_CINV;
-        }
-    }
-    if (dirty & 16u) { // z-: halo rows (y, z0 - 1) -- on the lowest tile row of a slab they are the peer's
-        const u32 *hrow = peer_lo ? A.lo.g + (size_t)A.lo.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 - sZ;
-        u32 h[8], o[8];
-#pragma unroll
-        for (int y = 0; y < 8; ++y) {
-            h[y] = inx ? (peer_lo ? bfs_ld_peer(hrow + (size_t)y * sY) : __ldcg(hrow + (size_t)y * sY)) : BFS_RAWINF;
-            o[y] = (touched && inx) ? __ldcg(cell0 + (size_t)y * sY) : BFS_RAWINF;
-        }
-#pragma unroll
-        for (int y = 0; y < 8; ++y) {
-            const u32 c = bfs_cand(h[y]);
-            const u32 fr = (free0 >> y) & 1u;
-            cZm[y] = (fr && c != BFS_CINV && c < (o[y] >> 1)) ? c : BFS_CINV;
-        }
-    }
-    if (dirty & 32u) { // z+
-        const u32 *hrow = peer_hi ? A.hi.g + (size_t)A.hi.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 + 8 * sZ;
-        u32 h[8], o[8];
-#pragma unroll
-        for (int y = 0; y < 8; ++y) {
-            h[y] = inx ? (peer_hi ? bfs_ld_peer(hrow + (size_t)y * sY) : __ldcg(hrow + (size_t)y * sY)) : BFS_RAWINF;
-            o[y] = (touched && inx) ? __ldcg(cell0 + 7 * sZ + (size_t)y * sY) : BFS_RAWINF;
-        }
-#pragma unroll
-        for (int y = 0; y < 8; ++y) {
-            const u32 c = bfs_cand(h[y]);
-            const u32 fr = (free1 >> (24 + y)) & 1u;
-            cZp[y] = (fr && c != BFS_CINV && c < (o[y] >> 1)) ? c : BFS_CINV;
-        }
+        for (int i = 0; i < 8; ++i) { cYm[i] = cYp[i]; cYp[i] = cZm[i]; cZm[i] = cZp[i]; cZp[i] = tc[i]; }
     }
     // x faces, row-distributed: this lane looks at the cells (y = ly, z = lzq + 4w)
     u32 *colrow = A.g + (size_t)(z0 + lzq) * sZ + (size_t)(y0 + ly) * sY + (size_t)x0;
@@ -861,13 +874,9 @@ __device__ static inline void bfs_warp_main(const BfsArgs &A, const int lane, co
     BfsPop P;
     P.ticket = 0; P.have = 0; P.t0 = 0;
     for (;;) {
-        u32 item = 0;
         const long long tp = clock64();
-        if (lane == 0) {
-            bool done = false;
-            do item = bfs_pop_try(A, P, 0xFFFFFFFFu, done); while (!item && !done);
-        }
-        item = __shfl_sync(BFS_FULL, item, 0);
+        bool done = false;
+        const u32 item = bfs_pop_warp(A, P, lane, 0xFFFFFFFFu, done);
         if (item == 0u) break;
         cnt.c_pop += (u64)(clock64() - tp);
         bfs_process_tile<false>(A, item - 1u, lane, cnt);
