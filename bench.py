@@ -612,6 +612,8 @@ def main():
     if os.path.exists(prof):
         try:
             traffic = json.load(open(prof)).get(f"{args.workload}_{n_head}" if args.workload != "c2" else "c2")
+            if isinstance(traffic, dict):
+                traffic = traffic.get("bytes")
         except Exception:
             pass
     dom = "k_bfs" if W["dtype"] == "u32" else "k_sssp"
