@@ -195,7 +195,17 @@ def build_c5(args, ctx):
             bad, reached, pend = solver.verify(src)          # global numbers (all-reduced)
             assert bad == 0 and pend == 0, f"certificate: {bad} violations, {pend} pending"
             solver.check()
-            local = int(((sl.field[:(solver.z1 - solver.z0) * sl.dg.padded[0] * sl.dg.padded[1]] != -1)).sum().item())
+            npl = sl.dg.padded[0] * sl.dg.padded[1]
+            nzl = solver.z1 - solver.z0
+            local = int(((sl.field[:nzl * npl] != -1)).sum().item())
+            # algorithmic halo bytes of this rank: one 4-byte read per reached cell of each neighbour's boundary plane
+            # = (by symmetry of the exchange) the reached cells of the own boundary planes that face another slab
+            hb = 0
+            if rank > 0:
+                hb += int((sl.field[:npl] != -1).sum().item()) * 4
+            if rank < world - 1:
+                hb += int((sl.field[(nzl - 1) * npl:nzl * npl] != -1).sum().item()) * 4
+            cfg["algorithmic_halo_bytes_rank0"] = hb
             return local * 6, local, local * ALG_BYTES["u32"], float(reached)
 
         def verify():
@@ -486,6 +496,8 @@ def kernel_stats(st, dtype, clocks):
         return {"solver": "k_bfs (one warp per tile)", "tile_activations": st[1], "idle_activations": st[13],
                 "cells_lowered": st[2], "edges_relaxed": st[2] * 6, "levels_swept": st[12], "passes": st[14],
                 "requeues": st[5], "remote_pushes": st[7], "kernel_ms": st[8] / 1e6,
+                "rank0_busy_ms": (st[16] - st[9]) / 1e6 if len(st) > 17 and st[16] else None,
+                "nvlink_bytes_read_rank0": st[17] * 128 if len(st) > 17 else 0,
                 "us_per_activation_per_warp": {"wait_for_work": st[4] / na / mhz, "setup": st[6] / na / mhz,
                                                "sweep": st[11] / na / mhz, "extract_store": st[3] / na / mhz,
                                                "publish": st[0] / na / mhz}}

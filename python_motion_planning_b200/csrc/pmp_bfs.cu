@@ -132,7 +132,7 @@ static BfsLayout bfs_layout(const pmp_grid *g) {
     L.state = o; o = bfs_align(o + (size_t)L.ntiles * 4);
     L.ring = o; o = bfs_align(o + (size_t)L.ring_cap * 4);
     L.ctr = o; o = bfs_align(o + BFS_C_WORDS * 4);
-    L.stats = o; o = bfs_align(o + 16 * 8);
+    L.stats = o; o = bfs_align(o + 32 * 8);
     L.total = o;
     return L;
 }
@@ -218,7 +218,7 @@ static int bfs_reset_ws(const BfsArgs &A, const BfsLayout &L, cudaStream_t s) {
     PMP_CHECK_CUDA(cudaMemsetAsync(A.state, 0, (size_t)L.ntiles * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ring, 0, (size_t)L.ring_cap * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, BFS_C_WORDS * 4, s));
-    PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 16 * 8, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 32 * 8, s));
     return 0;
 }
 
@@ -357,7 +357,7 @@ static BfsLayout bfs_layout_tiles(int nbx, int nby, int nbz) {
     L.state = o; o = bfs_align(o + (size_t)L.ntiles * 4);
     L.ring = o; o = bfs_align(o + (size_t)L.ring_cap * 4);
     L.ctr = o; o = bfs_align(o + BFS_C_WORDS * 4);
-    L.stats = o; o = bfs_align(o + 16 * 8);
+    L.stats = o; o = bfs_align(o + 32 * 8);
     L.total = o;
     return L;
 }

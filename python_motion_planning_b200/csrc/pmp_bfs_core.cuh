@@ -96,6 +96,7 @@ struct BfsArgs {
 
 struct BfsCount {
     u32 act, idle, lowered, levels, passes, redo, remote;
+    u32 peer_rows; // 128-byte rows of a neighbour GPU's field read over NVLink (halo pulls + arming checks)
     u64 c_pop, c_setup, c_sweep, c_extract, c_publish; // cycles (lane 0's clock) per phase, summed over activations
 };
 
@@ -463,6 +464,8 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
     if (peer_lo || peer_hi) __threadfence_system(); else bfs_fence();
     const u32 dirty = old & BFS_DIRTY;
     bool touched = (old & BFS_T) != 0u;
+    if (cnt.act == 0 && lane == 0 && A.stats && !__ldcg(&A.stats[18])) // [18]: when this rank started its first activation
+        atomicCAS((unsigned long long *)&A.stats[18], 0ull, (unsigned long long)bfs_now_ns());
     ++cnt.act;
 
     // ---- occupancy rows -> this lane's column bits; free cells on the far side of each face (a
@@ -503,6 +506,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
             const u32 *orow = yface ? (hiside ? cell0 + 7 * sY : cell0) : (hiside ? cell0 + 7 * sZ : cell0);
             const u32 shb = yface ? (hiside ? 7u : 0u) : (hiside ? 24u : 0u);
             const u32 fw_lo = yface ? free0 : (hiside ? free1 : free0), fw_hi = yface ? free1 : fw_lo;
+            if (peer) cnt.peer_rows += 8;
             u32 h[8], o[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -748,6 +752,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
         if (__any_sync(BFS_FULL, czm != 0u)) {
             bool imp = !(dirty & 16u) && czm != 0u;
             if (dirty & 16u) {
+                if (peer_lo) cnt.peer_rows += (u32)__popc(__reduce_or_sync(BFS_FULL, czm));
                 const u32 *hrow = peer_lo ? A.lo.g + (size_t)A.lo.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 - sZ;
 #pragma unroll
                 for (int y = 0; y < 8; ++y)
@@ -762,6 +767,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
         if (__any_sync(BFS_FULL, czp != 0u)) {
             bool imp = !(dirty & 32u) && czp != 0u;
             if (dirty & 32u) {
+                if (peer_hi) cnt.peer_rows += (u32)__popc(__reduce_or_sync(BFS_FULL, czp >> 24));
                 const u32 *hrow = peer_hi ? A.hi.g + (size_t)A.hi.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 + 8 * sZ;
 #pragma unroll
                 for (int y = 0; y < 8; ++y)
@@ -829,11 +835,15 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
     }
     __syncwarp();
     cnt.c_publish += (u64)(clock64() - tc3);
+    // [16]: when this rank finished its last activation (its busy span = [16] - [9]; the kernel itself runs
+    // until the LAST rank is done)
+    if (lane == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[16], (unsigned long long)bfs_now_ns());
 }
 
 // ---- persistent warp loop --------------------------------------------------------------------------
 __device__ static inline void bfs_count_init(BfsCount &cnt) {
     cnt.act = cnt.idle = cnt.lowered = cnt.levels = cnt.passes = cnt.redo = cnt.remote = 0;
+    cnt.peer_rows = 0;
     cnt.c_pop = cnt.c_setup = cnt.c_sweep = cnt.c_extract = cnt.c_publish = 0;
 }
 
@@ -855,6 +865,7 @@ __device__ static inline void bfs_count_flush(const BfsArgs &A, BfsCount &cnt, c
         atomicAdd((unsigned long long *)&A.stats[14], (unsigned long long)cnt.passes);
         atomicAdd((unsigned long long *)&A.stats[5], (unsigned long long)cnt.redo);
         atomicAdd((unsigned long long *)&A.stats[7], (unsigned long long)cnt.remote);
+        if (cnt.peer_rows) atomicAdd((unsigned long long *)&A.stats[14 + 3], (unsigned long long)cnt.peer_rows); // [17]
     }
 }
 

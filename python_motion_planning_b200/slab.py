@@ -325,7 +325,7 @@ class BfsSlab:
         _lib.check(L.pmp_bfs_slab_buffers(h, ctypes.byref(fp), ctypes.byref(nb), ctypes.byref(sp), ctypes.byref(cp)),
                    "pmp_bfs_slab_buffers")
         self.field = t.as_tensor(_DevMem(fp.value, nb.value // 4, self), device=self.dg.device)   # raw words
-        self._stats_arena = t.as_tensor(_DevMem(sp.value, 32, self), device=self.dg.device).view(t.int64)
+        self._stats_arena = t.as_tensor(_DevMem(sp.value, 64, self), device=self.dg.device).view(t.int64)   # 32 counters
         self.stats = t.zeros(16, dtype=t.int64, device=self.dg.device)
         self.status = t.zeros(1, dtype=t.int32, device=self.dg.device)
         self._start = t.zeros(3, dtype=t.int32, device=self.dg.device)

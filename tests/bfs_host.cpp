@@ -132,7 +132,7 @@ int main(int argc, char **argv) {
         A.ring_cap = A.ntiles + 64 + (u32)(g_warps);
         K.ring.assign(A.ring_cap, 0);
         K.ctr.assign(BFS_C_WORDS, 0);
-        K.stats.assign(16, 0);
+        K.stats.assign(32, 0);
         A.g = K.g.data(); A.state = K.state.data(); A.ring = K.ring.data(); A.ctr = K.ctr.data();
         A.stats = K.stats.data();
         A.rank = r; A.world = nr;

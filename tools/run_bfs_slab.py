@@ -53,6 +53,14 @@ def main():
     solver.check()
     t = torch.tensor([sum(ms) / len(ms)], dtype=torch.float64, device="cuda")
     st = solver.slab.stats.clone()
+    per_rank = None
+    if d is not None:        # every rank's counters of the last search, for the per-slab breakdown
+        mine = torch.from_numpy(solver.slab.stats_host().copy()).to("cuda")
+        allst = [torch.empty_like(mine) for _ in range(world)]
+        d.all_gather(allst, mine)
+        per_rank = [{"rank": r, "first_ms": (a[18].item() - a[9].item()) / 1e6, "busy_ms": (a[16].item() - a[9].item()) / 1e6, "activations": a[1].item(), "idle": a[13].item(),
+                     "lowered": a[2].item(), "remote_pushes": a[7].item(), "nvlink_bytes_read": a[17].item() * 128}
+                    for r, a in enumerate(allst)]
     if d is not None:
         d.all_reduce(t, op=d.ReduceOp.MAX)
         d.all_reduce(st, op=d.ReduceOp.SUM)
@@ -66,6 +74,8 @@ def main():
                    gteps=6.0 * reached / (float(t[0]) * 1e-3) / 1e9)
         ok = bad == 0 and pend == 0 and (args.reached == 0 or reached == args.reached)
     out["ok"] = ok
+    if per_rank:
+        out["per_rank"] = per_rank
     if rank == 0:
         print(json.dumps(out), flush=True)
     if d is not None:
