@@ -272,7 +272,7 @@ int pmp_slab_merge(pmp_grid *g, int weight, void *g_dev, void *ws_dev, int64_t w
  * the request of the run's operators, for callers that cannot call cudaMalloc: CUDA graph capture,
  * tight serving loops).  Same result as pmp_sssp(full_field = 1, weight = PMP_W_U32) on a 3D grid whose
  * motion table is the six unit moves, but the workspace lives in a static device array of 1 MiB inside
- * the library (held by every GPU that loads it): grids up to ~126 000 tiles of 32 x 8 x 8 cells (e.g.
+ * the library (held by every GPU that loads it): grids up to ~81 000 tiles of 32 x 8 x 8 cells (e.g.
  * 512^3); larger grids are rejected with an error.  start_dev: int32[3]; g_dev: pcells uint32 in the
  * search's word format ((value << 1) | 1, all-ones = unreached; pmp_field_finalize decodes);
  * status_dev (1 x int32) / stats_dev (16 x uint64) may be NULL.  All calls share the array: calls that

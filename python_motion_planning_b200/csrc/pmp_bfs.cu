@@ -27,6 +27,9 @@
 #ifndef BFS_SYNC_MINB
 #define BFS_SYNC_MINB 4 // resident CTAs per SM of the phase-locked kernel (122 registers, no spills)
 #endif
+#ifndef BFS_PACE_DEFAULT
+#define BFS_PACE_DEFAULT 1024 // measured: 256 starves (48 ms at 2 GPUs), 512-1024 best (22.1 ms, 1.003x cells lowered), 8192 ~ unpaced
+#endif
 #define BFS_RING_SLACK 8192
 
 // The search kernel.  Persistent; one warp per tile activation.  The kernel's code is far larger
@@ -43,18 +46,18 @@ __global__ void __launch_bounds__(BFS_SYNC_NT, BFS_SYNC_MINB) k_bfs(const __grid
     BfsCount cnt;
     bfs_count_init(cnt);
     BfsPop P;
-    P.ticket = 0; P.have = 0; P.t0 = 0;
+    P.ticket = 0; P.have = 0; P.t0 = 0; P.held = 0; P.held_polls = 0;
     for (;;) {
         const long long tp = clock64();
         bool done = false;
-        const u32 item = bfs_pop_warp(A, P, lane, BFS_TRY_POLLS, done);
-        if (!__syncthreads_or(item != 0u)) {          // nobody in the CTA has work
+        const u64 item = bfs_pop_warp(A, P, lane, BFS_TRY_POLLS, done);
+        if (!__syncthreads_or(item != 0ull)) {          // nobody in the CTA has work
             if (__syncthreads_and(done)) break;       // ... and the search is over for everyone
             continue;
         }
         if (item) {
             cnt.c_pop += (u64)(clock64() - tp);
-            bfs_process_tile<true>(A, item - 1u, lane, cnt);
+            bfs_process_tile<true>(A, item, lane, cnt);
         } else {
             BFS_PHASE_SYNC(); BFS_PHASE_SYNC(); BFS_PHASE_SYNC(); // the three phase boundaries of bfs_process_tile
         }
@@ -83,7 +86,7 @@ __global__ void k_bfs_init(BfsArgs A, const int32_t *start, int32_t *status) {
         if (ok) {
             const u32 t = (u32)(((sz / 8) * A.nby + sy / 8) * A.nbx + sx / 32);
             A.state[t] = BFS_SRC | BFS_Q;
-            A.ring[0] = t + 1u;
+            A.ring[0] = (u64)(t + 1u); // sequence number 0
             A.ctr[BFS_C_TAIL] = 1u;
             A.ctr[BFS_C_INFLIGHT] = 1u;
             A.ctr[BFS_C_SRC] = (u32)sx; A.ctr[BFS_C_SRC + 1] = (u32)sy; A.ctr[BFS_C_SRC + 2] = (u32)sz;
@@ -130,7 +133,7 @@ static BfsLayout bfs_layout(const pmp_grid *g) {
     L.ring_cap = L.ntiles + BFS_RING_SLACK;
     size_t o = 0;
     L.state = o; o = bfs_align(o + (size_t)L.ntiles * 4);
-    L.ring = o; o = bfs_align(o + (size_t)L.ring_cap * 4);
+    L.ring = o; o = bfs_align(o + (size_t)L.ring_cap * 8);
     L.ctr = o; o = bfs_align(o + BFS_C_WORDS * 4);
     L.stats = o; o = bfs_align(o + 32 * 8);
     L.total = o;
@@ -159,7 +162,7 @@ static void bfs_fill_args(const pmp_grid *g, void *g_dev, void *ws_dev, const Bf
     A.ntiles = L.ntiles;
     A.g = (u32 *)g_dev;
     A.state = (u32 *)(ws + L.state);
-    A.ring = (u32 *)(ws + L.ring);
+    A.ring = (u64 *)(ws + L.ring);
     A.ring_cap = L.ring_cap;
     A.ctr = (u32 *)(ws + L.ctr);
     A.stats = (u64 *)(ws + L.stats);
@@ -171,6 +174,8 @@ static void bfs_fill_args(const pmp_grid *g, void *g_dev, void *ws_dev, const Bf
     // a tile is activated a few times; a search that pops 64x its tiles is stuck (abort with PMP_ST_ERROR)
     const u64 budget = 64ull * L.ntiles + (1ull << 20);
     A.max_pops = budget > 0xFFFFFFF0ull ? 0u : (u32)budget;
+    A.pace_window = 0; // single grid: no pacing (pmp_bfs_slab_create turns it on for world > 1)
+    A.pace_hold_polls = 8000; // ~2-4 ms at most per held entry
 }
 
 __global__ void k_bfs_group(const BfsArgs *args, int n);
@@ -216,7 +221,7 @@ static int bfs_grid_blocks(int *out) { // the free-running group kernel
 
 static int bfs_reset_ws(const BfsArgs &A, const BfsLayout &L, cudaStream_t s) {
     PMP_CHECK_CUDA(cudaMemsetAsync(A.state, 0, (size_t)L.ntiles * 4, s));
-    PMP_CHECK_CUDA(cudaMemsetAsync(A.ring, 0, (size_t)L.ring_cap * 4, s));
+    PMP_CHECK_CUDA(cudaMemsetAsync(A.ring, 0, (size_t)L.ring_cap * 8, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.ctr, 0, BFS_C_WORDS * 4, s));
     PMP_CHECK_CUDA(cudaMemsetAsync(A.stats, 0, 32 * 8, s));
     return 0;
@@ -266,7 +271,7 @@ int pmp_bfs_field(pmp_grid *g, const int32_t *start_dev, void *g_dev, void *ws_d
 // capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
 // Allocates nothing: no cudaMalloc / cudaFree, no
 // allocating library call.  Limit: the workspace of the grid must fit PMP_STATIC_WS_BYTES (1 MiB:
-// grids up to ~126 000 tiles of 32 x 8 x 8 cells, e.g. 512^3).  Every GPU that loads the library holds
+// grids up to ~81 000 tiles of 32 x 8 x 8 cells, e.g. 512^3).  Every GPU that loads the library holds
 // the array until exit.  All calls share it: it keeps the last call's contents (every word a search
 // reads is cleared at the start of the call), and calls that overlap on one GPU race.
 // ---------------------------------------------------------------------------------------------
@@ -355,7 +360,7 @@ static BfsLayout bfs_layout_tiles(int nbx, int nby, int nbz) {
     L.ring_cap = L.ntiles + BFS_RING_SLACK;
     size_t o = 0;
     L.state = o; o = bfs_align(o + (size_t)L.ntiles * 4);
-    L.ring = o; o = bfs_align(o + (size_t)L.ring_cap * 4);
+    L.ring = o; o = bfs_align(o + (size_t)L.ring_cap * 8);
     L.ctr = o; o = bfs_align(o + BFS_C_WORDS * 4);
     L.stats = o; o = bfs_align(o + 32 * 8);
     L.total = o;
@@ -389,6 +394,10 @@ extern "C" int pmp_bfs_slab_create(pmp_grid *g, int rank, int world, pmp_bfs_sla
     }
     bfs_fill_args(g, s->arena, s->arena + s->field_bytes, s->L, s->A);
     s->A.rank = rank; s->A.world = world;
+    {
+        const char *pw = getenv("PMP_B200_BFS_PACE"); // entries a slab may run ahead of the global FIFO position (0: off)
+        s->A.pace_window = world > 1 ? (u32)(pw ? atoi(pw) : BFS_PACE_DEFAULT) : 0u;
+    }
     s->A.peer_ctr[rank] = s->A.ctr;
     if (world == 1) s->connected = true;
     *out = s;
@@ -430,7 +439,7 @@ static int bfs_set_peer(pmp_bfs_slab *s, int r, char *base, const int64_t *info)
         BfsPeer &P = r < s->rank ? s->A.lo : s->A.hi;
         P.g = (u32 *)base;
         P.state = (u32 *)(ws + PL.state);
-        P.ring = (u32 *)(ws + PL.ring);
+        P.ring = (u64 *)(ws + PL.ring);
         P.ctr = (u32 *)(ws + PL.ctr);
         P.ring_cap = PL.ring_cap;
         P.nbz = PL.nbz;

@@ -55,7 +55,13 @@
 #define BFS_C_ERR 97
 #define BFS_C_ACTIVE 128 // ranks with work in flight (only rank 0's word is used)
 #define BFS_C_SRC 160    // local source cell x, y, z and a valid flag
-#define BFS_C_WORDS 192
+// multi-GPU pacing (bfs_seq_*): entries pushed / started on this rank, and the other ranks' counts as they
+// last reported them
+#define BFS_C_PUSHED 192
+#define BFS_C_STARTED 224
+#define BFS_C_GP 256     // + r: entries pushed by rank r
+#define BFS_C_GS 288     // + r: entries started by rank r
+#define BFS_C_WORDS 320
 
 // hook: the kernel that keeps the warps of a CTA in step defines this as __syncthreads()
 #ifndef BFS_PHASE_SYNC
@@ -68,7 +74,7 @@
 struct BfsPeer {
     u32 *g;      // peer field (nullptr: no neighbour slab on this side)
     u32 *state;
-    u32 *ring;
+    u64 *ring;
     u32 *ctr;
     u32 ring_cap;
     int nbz;     // z tile rows of the peer
@@ -82,7 +88,7 @@ struct BfsArgs {
     u32 ntiles;
     u32 *g;
     u32 *state;
-    u32 *ring;
+    u64 *ring;   // entries: (global sequence number << 32) | (tile id + 1); 0 = empty slot
     u32 ring_cap;
     u32 *ctr;
     u64 *stats;
@@ -92,6 +98,9 @@ struct BfsArgs {
     u32 *active;         // rank 0's BFS_C_ACTIVE word
     u64 timeout_ns;      // spin-loop safety net (0: none)
     u32 max_pops;        // activation budget of this rank (0: none): a search that needs more is aborted
+    u32 pace_window;     // multi-GPU: an entry waits while its sequence number is more than this ahead of the number of
+                         // entries started on all ranks (bfs_seq_*; 0: no pacing -- single-GPU runs never pace)
+    u32 pace_hold_polls; // polls (~0.25 us each) an entry is held at most before it is served regardless
 };
 
 struct BfsCount {
@@ -159,9 +168,36 @@ __device__ __forceinline__ void bfs_transpose8(u32 &lo, u32 &hi) {
 }
 
 // ---- ring ------------------------------------------------------------------------------------
-__device__ static inline void bfs_push(u32 *ring, u32 cap, u32 *ctr, u32 tile) {
+__device__ static inline void bfs_push(u64 *ring, u32 cap, u32 *ctr, u32 tile, u32 level) {
     const u32 ticket = atomicAdd(&ctr[BFS_C_TAIL], 1u);
-    bfs_store_volatile(&ring[ticket % cap], tile + 1u);
+    *(volatile u64 *)&ring[ticket % cap] = ((u64)level << 32) | (u64)(tile + 1u);
+}
+
+// ---- multi-GPU: one FIFO served by all GPUs --------------------------------------------------------
+// One GPU keeps the wave in order for free: a single FIFO, so a tile is served about one queue latency
+// (~1 ms at 1536^3) after it was armed, by which time its other neighbours have delivered too.  With
+// one FIFO per slab that is lost: a slab with a short queue serves a tile the moment it is armed, runs
+// ahead along whatever route reaches it first, and lowers the same cells again and again as the bulk of
+// the wave arrives (8 GPUs, 1536^3: 1.6x the cells lowered, the far slabs 2.8x -- profiles/r02_notes.md).
+// So the slabs emulate ONE queue: every entry carries a global sequence number (the number of entries
+// pushed on all ranks so far, as far as the pusher knows), every rank counts the entries it has started,
+// and a rank starts its head entry only when the entries started on all ranks together come within
+// `pace_window` of that number -- i.e. when a single FIFO over all slabs would have reached it.  The
+// counts are exchanged every BFS_SEQ_PUB events per rank (plain remote stores, no atomics); an entry is
+// held for at most pace_hold_polls polls, so pacing can delay but never deadlock.
+#define BFS_SEQ_PUB 128u
+__device__ static inline u32 bfs_seq_sum(const BfsArgs &A, const int base_word, const int own_word) {
+    u32 s = __ldcg(&A.ctr[own_word]); // own count: exact
+    for (int r = 0; r < A.world; ++r)
+        if (r != A.rank) s += __ldcg(&A.ctr[base_word + r]);
+    return s;
+}
+// one more entry pushed / started on this rank; tell the others every BFS_SEQ_PUB events
+__device__ static inline void bfs_seq_bump(const BfsArgs &A, const int own_word, const int base_word) {
+    const u32 n = atomicAdd(&A.ctr[own_word], 1u) + 1u;
+    if ((n & (BFS_SEQ_PUB - 1u)) == 0u)
+        for (int r = 0; r < A.world; ++r)
+            if (r != A.rank) bfs_store_volatile(&A.peer_ctr[r][base_word + A.rank], n);
 }
 
 __device__ __noinline__ static void bfs_fail(const BfsArgs &A, u32 code) {
@@ -172,13 +208,15 @@ __device__ __noinline__ static void bfs_fail(const BfsArgs &A, u32 code) {
 // A warp's position in the ring: the ticket stays valid across calls of bfs_pop_warp until it is
 // served (identical in all lanes).
 struct BfsPop {
-    u32 ticket, have;
-    u64 t0; // lane 0: when the current wait began (time-out safety net)
+    u32 ticket, have, held_polls;
+    u64 held;       // an entry taken from the ring that waits for its turn in the global order (0: none)
+    u64 t0;         // lane 0: when the current wait began (time-out safety net)
 };
-#define BFS_TOMB 0xFFFFFFFFu // ring slot: "the item of this ticket was taken by another warp"
+#define BFS_TOMB (~0ull) // ring slot: "the item of this ticket was taken by another warp"
 
-// The whole warp: try to take a tile.  Returns tile id + 1; or 0 with `done` set when the search is
-// over; or 0 with `done` clear when nothing turned up within max_polls polls (the ticket is kept).
+// The whole warp: try to take a tile.  Returns the ring entry (sequence number << 32 | tile id + 1); or 0
+// with `done` set when the search is over; or 0 with `done` clear when nothing turned up within
+// max_polls polls (the ticket, or an entry held back by the pacing, is kept for the next call).
 //
 // Tickets spread the consumers over the slots, but an item is not bound to its ticket holder: a warp
 // whose own slot is still empty also looks at the 31 slots before it and takes the oldest item it
@@ -186,44 +224,64 @@ struct BfsPop {
 // kernel a warp without a tile sits out its CTA's round at the barriers); without this an item
 // could wait a whole round while other warps idle, and the wave would run out of order.  The taker
 // leaves a tombstone, so the holder knows to draw a new ticket.
-__device__ static inline u32 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int lane, const unsigned max_polls,
+__device__ static inline u64 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int lane, const unsigned max_polls,
                                           bool &done) {
     done = false;
     unsigned ns = 32;
     for (unsigned polls = 0;; ++polls) {
-        if (!P.have) {
-            u32 t = 0;
-            if (lane == 0) t = atomicAdd(&A.ctr[BFS_C_HEAD], 1u);
-            P.ticket = __shfl_sync(BFS_FULL, t, 0);
-            P.have = 1u;
-            if (A.max_pops && P.ticket > A.max_pops) {
-                if (lane == 0) bfs_fail(A, BFS_ERR_BUDGET);
-                done = true;
-                return 0u;
+        u64 got = P.held;
+        if (!got) {
+            if (!P.have) {
+                u32 t = 0;
+                if (lane == 0) t = atomicAdd(&A.ctr[BFS_C_HEAD], 1u);
+                P.ticket = __shfl_sync(BFS_FULL, t, 0);
+                P.have = 1u;
+                if (A.max_pops && P.ticket > A.max_pops) {
+                    if (lane == 0) bfs_fail(A, BFS_ERR_BUDGET);
+                    done = true;
+                    return 0ull;
+                }
             }
-        }
-        const u32 idx = P.ticket - 31u + (u32)lane; // lane 31: my own slot
-        u32 *slot = &A.ring[idx % A.ring_cap];
-        const u32 v = (int)idx >= 0 ? __ldcg(slot) : 0u;
-        const u32 own = __shfl_sync(BFS_FULL, v, 31);
-        if (own == BFS_TOMB) { // my item went to another warp: clear the slot, draw a new ticket
-            if (lane == 31) bfs_store_volatile(slot, 0u);
-            P.have = 0u;
-            continue;
-        }
-        const u32 m = __ballot_sync(BFS_FULL, v != 0u && v != BFS_TOMB);
-        if (m) {
-            const int l = (m >> 31) ? 31 : __ffs(m) - 1; // my own, else the oldest one waiting for a busy warp
-            u32 got = 0;
-            if (lane == l) got = atomicCAS(slot, v, l == 31 ? 0u : BFS_TOMB) == v ? v : 0u;
-            got = __shfl_sync(BFS_FULL, got, l);
-            if (got) {
+            const u32 idx = P.ticket - 31u + (u32)lane; // lane 31: my own slot
+            u64 *slot = &A.ring[idx % A.ring_cap];
+            const u64 v = (int)idx >= 0 ? __ldcg(slot) : 0ull;
+            const u32 own_lo = __shfl_sync(BFS_FULL, (u32)v, 31), own_hi = __shfl_sync(BFS_FULL, (u32)(v >> 32), 31);
+            if ((own_lo & own_hi) == 0xFFFFFFFFu) { // my item went to another warp: clear the slot, draw a new ticket
+                if (lane == 31) *(volatile u64 *)slot = 0ull;
+                P.have = 0u;
+                continue;
+            }
+            const u32 m = __ballot_sync(BFS_FULL, v != 0ull && v != BFS_TOMB);
+            if (m) {
+                const int l = (m >> 31) ? 31 : __ffs(m) - 1; // my own, else the oldest one waiting for a busy warp
+                u64 g = 0;
+                if (lane == l) g = atomicCAS((unsigned long long *)slot, (unsigned long long)v, l == 31 ? 0ull : BFS_TOMB) == v ? v : 0ull;
+                got = ((u64)__shfl_sync(BFS_FULL, (u32)(g >> 32), l) << 32) | (u64)__shfl_sync(BFS_FULL, (u32)g, l);
+                if (!got) continue; // somebody else was faster: look again at once
                 bfs_fence();
                 if (l == 31) P.have = 0u;
                 P.t0 = 0;
+                P.held_polls = 0;
+            }
+        }
+        if (got) {
+            // pacing (multi-GPU only): would a single FIFO over all slabs have reached this entry yet?
+            u32 hold = 0;
+            if (A.pace_window) {
+                if (lane == 0 && P.held_polls < A.pace_hold_polls && !__ldcg(&A.ctr[BFS_C_DONE]))
+                    hold = (int)((u32)(got >> 32) - (bfs_seq_sum(A, BFS_C_GS, BFS_C_STARTED) + A.pace_window)) > 0 ? 1u : 0u;
+                hold = __shfl_sync(BFS_FULL, hold, 0);
+            }
+            if (!hold) {
+                P.held = 0ull;
+                if (A.pace_window && lane == 0) bfs_seq_bump(A, BFS_C_STARTED, BFS_C_GS);
                 return got;
             }
-            continue; // somebody else was faster: look again at once
+            P.held = got;
+            ++P.held_polls;
+            if (polls >= max_polls) return 0ull;
+            __nanosleep(256);
+            continue;
         }
         u32 flag = 0;
         if (lane == 0) {
@@ -235,8 +293,8 @@ __device__ static inline u32 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int
             }
         }
         flag = __shfl_sync(BFS_FULL, flag, 0);
-        if (flag) { done = true; return 0u; }
-        if (polls >= max_polls) return 0u;
+        if (flag) { done = true; return 0ull; }
+        if (polls >= max_polls) return 0ull;
         __nanosleep(ns);
         if (ns < 1024) ns *= 2;
     }
@@ -422,7 +480,8 @@ __device__ __forceinline__ u32 bfs_rel(const u32 c, const u32 base, u32 &far, u3
 // ---- one tile activation -----------------------------------------------------------------------
 // SYNC: the phase-locked kernel (CTA barriers at the phase boundaries); false: free-running warps
 template <bool SYNC>
-__device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, const int lane, BfsCount &cnt) {
+__device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 entry, const int lane, BfsCount &cnt) {
+    const u32 t = (u32)entry - 1u; // tile id (the upper half, the entry's sequence number, has served its purpose)
     const GridDev &Gd = A.G;
     const int bx = (int)(t % (u32)A.nbx), by = (int)((t / (u32)A.nbx) % (u32)A.nby), bz = (int)(t / ((u32)A.nbx * (u32)A.nby));
     const int x0 = bx * 32, y0 = by * 8, z0 = bz * 8;
@@ -781,6 +840,12 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
         }
     }
 
+    // sequence number of everything this activation queues: the entries pushed so far on all ranks
+    u32 seq_out = 0;
+    if (A.pace_window) {
+        if (lane == 0) seq_out = bfs_seq_sum(A, BFS_C_GP, BFS_C_PUSHED);
+        seq_out = __shfl_sync(BFS_FULL, seq_out, 0);
+    }
     // lanes 1..6 arm the six neighbours, lane 0 releases the tile -- all in parallel
     bool need_push = false, requeue = false;
     u32 ntile = 0;
@@ -799,7 +864,8 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
                 if (atomicAdd(&P.ctr[BFS_C_INFLIGHT], 1u) == 0u)
                     cnt.remote += atomicAdd(A.active, 1u) == 0xFFFFFFFFu; // the returned value: performed before we go on
                 __threadfence_system();
-                bfs_push(P.ring, P.ring_cap, P.ctr, ntile);
+                if (A.pace_window) bfs_seq_bump(A, BFS_C_PUSHED, BFS_C_GP);
+                bfs_push(P.ring, P.ring_cap, P.ctr, ntile, seq_out);
                 ++cnt.remote;
             }
         } else {
@@ -828,8 +894,11 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u32 t, 
         if (lane == 0) { atomicAdd(&A.ctr[BFS_C_INFLIGHT], (u32)(np - 1)); bfs_fence(); }
         __syncwarp();
     }
-    if (need_push) bfs_push(A.ring, A.ring_cap, A.ctr, ntile);
-    if (requeue) { bfs_push(A.ring, A.ring_cap, A.ctr, t); ++cnt.redo; }
+    if (need_push || requeue) {
+        if (A.pace_window) bfs_seq_bump(A, BFS_C_PUSHED, BFS_C_GP);
+        bfs_push(A.ring, A.ring_cap, A.ctr, requeue ? t : ntile, seq_out);
+        if (requeue) ++cnt.redo;
+    }
     if (np == 0 && lane == 0) {
         if (atomicSub(&A.ctr[BFS_C_INFLIGHT], 1u) == 1u) bfs_rank_idle(A);
     }
@@ -883,14 +952,14 @@ __device__ static inline void bfs_warp_main(const BfsArgs &A, const int lane, co
     BfsCount cnt;
     bfs_count_init(cnt);
     BfsPop P;
-    P.ticket = 0; P.have = 0; P.t0 = 0;
+    P.ticket = 0; P.have = 0; P.t0 = 0; P.held = 0; P.held_polls = 0;
     for (;;) {
         const long long tp = clock64();
         bool done = false;
-        const u32 item = bfs_pop_warp(A, P, lane, 0xFFFFFFFFu, done);
-        if (item == 0u) break;
+        const u64 item = bfs_pop_warp(A, P, lane, 0xFFFFFFFFu, done);
+        if (item == 0ull) break;
         cnt.c_pop += (u64)(clock64() - tp);
-        bfs_process_tile<false>(A, item - 1u, lane, cnt);
+        bfs_process_tile<false>(A, item, lane, cnt);
     }
     bfs_count_flush(A, cnt, lane);
 }

@@ -19,7 +19,8 @@
 
 struct Rank {
     BfsArgs A;
-    std::vector<u32> bits, g, state, ring, ctr;
+    std::vector<u32> bits, g, state, ctr;
+    std::vector<u64> ring;
     std::vector<u64> stats;
     int z0, z1;
 };
@@ -137,6 +138,8 @@ int main(int argc, char **argv) {
         A.stats = K.stats.data();
         A.rank = r; A.world = nr;
         A.timeout_ns = 0;
+        A.pace_window = nr > 1 ? 8 : 0; // tight: entries are held often
+        A.pace_hold_polls = 40;
     }
     for (int r = 0; r < nr; ++r) {
         BfsArgs &A = R[r].A;
@@ -161,7 +164,7 @@ int main(int argc, char **argv) {
         const int lz = sz - K.z0;
         const u32 t = (u32)(((lz / 8) * K.A.nby + sy / 8) * K.A.nbx + sx / 32);
         K.state[t] = BFS_SRC | BFS_Q;
-        K.ring[0] = t + 1;
+        K.ring[0] = (u64)(t + 1);
         K.ctr[BFS_C_TAIL] = 1;
         K.ctr[BFS_C_INFLIGHT] = 1;
         K.ctr[BFS_C_SRC] = (u32)sx; K.ctr[BFS_C_SRC + 1] = (u32)sy; K.ctr[BFS_C_SRC + 2] = (u32)lz;
