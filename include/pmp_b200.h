@@ -88,6 +88,16 @@ int pmp_grid_set_dense_xyz(pmp_grid *g, const uint8_t *occ_dev, void *stream);
  * bitorder="little") viewed as uint32 when X is a multiple of 32).  1/8 of the bytes of the dense
  * forms; 2D grids: Z = 1. */
 int pmp_grid_set_packed(pmp_grid *g, const uint32_t *rows_dev, void *stream);
+/* The same from PINNED HOST memory, streamed: the rows are copied in z chunks of ~planes_per_chunk planes
+ * on copy_stream (the copy engine) straight into the grid's bitmask, each chunk followed by a ready flag,
+ * and the call returns at once.  A unit-weight field search (pmp_sssp full_field / PMP_W_U32 on the six
+ * unit moves) launched on search_stream right after it starts while the upload is still running: its
+ * kernel waits per tile for the chunks it needs.  Every other entry point first waits for the whole
+ * upload.  Needs the rows to be the grid's own layout: 3D, X % 32 == 0, Y % 8 == 0, Z % 8 == 0 (else -1:
+ * upload to the device yourself and call pmp_grid_set_packed).  The host buffer must stay untouched
+ * until the next operation on search_stream after the search has completed. */
+int pmp_grid_set_packed_host_streamed(pmp_grid *g, const uint32_t *rows_host_pinned, int planes_per_chunk,
+                                      void *search_stream, void *copy_stream);
 /* Toggle single cells without rebuilding (obstacle edits between plans). value: 1 block, 0 free */
 int pmp_grid_edit_cells(pmp_grid *g, const int32_t *coords_dev, int64_t n, int value, void *stream);
 /* Copy the device bitmask to host: words_per_row * PY * PZ uint32 (bit x%32 of word x/32). Synchronous. */

@@ -32,7 +32,7 @@ def check_status(status, what="search"):
 SYMBOLS = (
     "pmp_last_error", "pmp_abi_version", "pmp_device_count",
     "pmp_grid_create", "pmp_grid_destroy", "pmp_grid_layout", "pmp_grid_set_cells",
-    "pmp_grid_set_dense", "pmp_grid_set_dense_xyz", "pmp_grid_set_packed", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
+    "pmp_grid_set_dense", "pmp_grid_set_dense_xyz", "pmp_grid_set_packed", "pmp_grid_set_packed_host_streamed", "pmp_grid_edit_cells", "pmp_grid_read_bits", "pmp_grid_count_free",
     "pmp_grid_set_motions", "pmp_grid_set_corner_cutting", "pmp_sssp_sizes", "pmp_sssp", "pmp_field_finalize",
     "pmp_count_settled", "pmp_extract_paths", "pmp_verify_field", "pmp_gbfs", "pmp_bestfirst",
     "pmp_lpa_star", "pmp_d_star",
@@ -98,6 +98,7 @@ def lib():
         "pmp_grid_set_dense": [vp, vp, vp],
         "pmp_grid_set_dense_xyz": [vp, vp, vp],
         "pmp_grid_set_packed": [vp, vp, vp],
+        "pmp_grid_set_packed_host_streamed": [vp, vp, i32, vp, vp],
         "pmp_grid_edit_cells": [vp, vp, i64, i32, vp],
         "pmp_grid_read_bits": [vp, vp, i64],
         "pmp_grid_count_free": [vp, vp],

@@ -106,11 +106,14 @@ def cost_field(env, source, weight="f64", window=0.0, to_host=True):
     indexed [x, y(, z)] with +inf for unreachable cells, or (Workspace, stats) with
     to_host=False (the field stays on the device: Workspace.g[0], padded layout)."""
     ndim = env._ndim
-    dg = env.device_grid()
-    dg.set_motions(*motion_table(env, ndim))
+    dg = env.device_grid(sync=False)
     wt = _lib.W_U32 if weight == "u32" else _lib.W_F64
     ws = engine.get_workspace(dg, 1, wt)
+    # the query goes up first: a streamed occupancy upload (update_packed with pinned rows) keeps the H2D copy engine
+    # busy for milliseconds, and the search is meant to start behind its first chunk, not behind its last
     engine.upload_queries(ws, [tuple(source)], None, ndim)
+    env.device_grid()
+    dg.set_motions(*motion_table(env, ndim))
     engine.sssp(ws, _lib.DIJKSTRA, 0, full_field=True, window=window, have_goals=False)
     if not to_host:
         return ws, ws.stats        # asynchronous: the caller checks ws.status (engine.check_field_status)

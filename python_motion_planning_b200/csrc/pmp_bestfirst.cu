@@ -146,6 +146,7 @@ extern "C" int pmp_bestfirst(const pmp_grid *g, int algo, int heuristic, int64_t
                              int64_t order_cap, uint32_t *path_dev, int64_t path_cap,
                              int32_t *path_len_dev, double *cost_dev, int32_t *n_expand_dev,
                              void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || nq < 1 || !starts_dev || !goals_dev || !heap_dev || heap_cap < 1 || !closed_g_dev ||
         !closed_h_dev || !closed_parent_dev || !order_dev || order_cap < 1 || !path_dev ||
         path_cap < 1 || !path_len_dev || !cost_dev || !n_expand_dev) {
@@ -318,6 +319,7 @@ extern "C" int pmp_lpa_star(const pmp_grid *g, int variant, int op, int heuristi
                             uint32_t *list_dev, int64_t list_cap, int64_t *ctl_dev, uint32_t *expand_dev,
                             int64_t expand_cap, uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
                             double *cost_dev, int32_t *n_expand_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || (variant != 0 && variant != 1) || (op != 0 && op != 1) || !start_goal_dev || (op == 1 && !change_dev) || !g_dev || !rhs_dev ||
         !key_dev || !list_dev || list_cap < 1 || !ctl_dev || !expand_dev || expand_cap < 1 || !path_dev ||
         path_cap < 1 || !path_len_dev || !cost_dev || !n_expand_dev) {
@@ -339,6 +341,7 @@ extern "C" int pmp_d_star(const pmp_grid *g, int op, const int32_t *start_goal_d
                           int64_t *ctl_dev, uint32_t *expand_dev, int64_t expand_cap, uint32_t *path_dev,
                           int64_t path_cap, int32_t *path_len_dev, double *cost_dev, int32_t *n_expand_dev,
                           void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || (op != 0 && op != 1) || !start_goal_dev || !h_dev || !k_dev || !parent_dev || !tag_dev ||
         !list_dev || list_cap < 1 || !ctl_dev || !expand_dev || expand_cap < 1 || !path_dev || path_cap < 1 ||
         !path_len_dev || !cost_dev || !n_expand_dev) {

@@ -82,7 +82,12 @@ __global__ void k_bfs_init(BfsArgs A, const int32_t *start, int32_t *status) {
     int st = PMP_ST_RUNNING;
     if (start) {
         const int sx = start[0], sy = start[1], sz = start[2];
-        const bool ok = sx >= 0 && sy >= 0 && sz >= 0 && sx < Gd.X && sy < Gd.Y && sz < Gd.Z && !cell_blocked(Gd, sx, sy, sz);
+        bool ok = sx >= 0 && sy >= 0 && sz >= 0 && sx < Gd.X && sy < Gd.Y && sz < Gd.Z;
+        if (ok && Gd.ready) { // streamed upload: the source's planes must have arrived (one thread: poll here)
+            const u32 *f = Gd.ready + (sz >> Gd.ready_shift);
+            for (unsigned w = 0; w < (1u << 24) && bfs_ld_acquire_sys(f) == 0u; ++w) __nanosleep(200);
+        }
+        ok = ok && !cell_blocked(Gd, sx, sy, sz);
         if (ok) {
             const u32 t = (u32)(((sz / 8) * A.nby + sy / 8) * A.nbx + sx / 32);
             A.state[t] = BFS_SRC | BFS_Q;
@@ -262,6 +267,9 @@ int pmp_bfs_field(pmp_grid *g, const int32_t *start_dev, void *g_dev, void *ws_d
     if (bfs_launch_fill(A, s)) return -2;
     k_bfs_finish<<<1, 1, 0, s>>>(A, gcost_dev, status_dev, (u64 *)stats_dev);
     PMP_CHECK_CUDA(cudaGetLastError());
+    // a streamed occupancy upload was consumed chunk by chunk by k_bfs (GridDev.ready); whatever comes next on
+    // this stream sees all of it
+    if (pmp_grid_upload_fence(g, s)) return -2;
     return 0;
 }
 
@@ -304,6 +312,7 @@ extern "C" int pmp_cost_field_u32_static(pmp_grid *g, const int32_t *start_dev, 
     int dev = 0;
     PMP_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev != g->device) { pmp_set_error("pmp_cost_field_u32_static: the grid lives on device %d, current device is %d", g->device, dev); return -1; }
+    if (pmp_grid_upload_fence(g, (cudaStream_t)stream)) return -2;
     const BfsLayout L = bfs_layout(g);
     if (L.total > (size_t)PMP_STATIC_WS_BYTES) {
         pmp_set_error("pmp_cost_field_u32_static: grid of %u tiles needs %zu B of workspace, the static array holds %u B "
@@ -495,6 +504,7 @@ extern "C" int pmp_bfs_slab_connect_local(pmp_bfs_slab **slabs, int n) {
 extern "C" int pmp_bfs_slab_begin(pmp_bfs_slab *s, const int32_t *start_local_dev, int32_t *status_dev, void *stream) {
     if (!s || !s->connected) { pmp_set_error("pmp_bfs_slab_begin: slab not connected"); return -1; }
     cudaStream_t st = (cudaStream_t)stream;
+    if (pmp_grid_upload_fence(s->grid, st)) return -2; // (the slab's copy of the grid description does not follow uploads)
     if (bfs_reset_ws(s->A, s->L, st)) return -2;
     k_bfs_init<<<1, 1, 0, st>>>(s->A, start_local_dev, status_dev);
     PMP_CHECK_CUDA(cudaGetLastError());

@@ -105,6 +105,7 @@ struct BfsArgs {
 
 struct BfsCount {
     u32 act, idle, lowered, levels, passes, redo, remote;
+    u32 all_up;    // streamed occupancy upload: the last chunk has been seen, no more flag checks
     u32 peer_rows; // 128-byte rows of a neighbour GPU's field read over NVLink (halo pulls + arming checks)
     u64 c_pop, c_setup, c_sweep, c_extract, c_publish; // cycles (lane 0's clock) per phase, summed over activations
 };
@@ -125,6 +126,11 @@ __device__ __forceinline__ u32 bfs_ld_peer(const u32 *p) {
     asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ u32 bfs_ld_acquire_sys(const u32 *p) {
+    u32 v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 // all-ones if bit 7 of byte k of v is set, else 0: PRMT in its sign-replicating form (selector
 // nibble 8 | k) -- __byte_perm() masks the selector to 3 bits, so it takes inline PTX
 __device__ __forceinline__ u32 bfs_byte_sign(u32 v, int k) {
@@ -138,6 +144,7 @@ static inline void bfs_store(u32 *p, u32 v) { *p = v; }
 static inline void bfs_store_volatile(u32 *p, u32 v) { *(volatile u32 *)p = v; }
 static inline void bfs_fence() { __threadfence(); }
 static inline u32 bfs_ld_peer(const u32 *p) { return *(const volatile u32 *)p; }
+static inline u32 bfs_ld_acquire_sys(const u32 *p) { return *(const volatile u32 *)p; }
 static inline u32 bfs_byte_sign(u32 v, int k) { return ((v >> (8 * k)) & 0x80u) ? 0xFFFFFFFFu : 0u; }
 #endif
 
@@ -203,6 +210,36 @@ __device__ static inline void bfs_seq_bump(const BfsArgs &A, const int own_word,
 __device__ __noinline__ static void bfs_fail(const BfsArgs &A, u32 code) {
     atomicOr(&A.ctr[BFS_C_ERR], code);
     for (int r = 0; r < A.world; ++r) bfs_store_volatile(&A.peer_ctr[r][BFS_C_DONE], 1u);
+}
+
+// Streamed occupancy upload (GridDev.ready): wait until the planes [zlo, zhi] of the bitmask have arrived.
+// Lanes 0 and 1 poll the flags of the first and the last chunk involved (chunks arrive in z order, and a
+// tile's rows span at most two) with acquire loads -- no fence, this sits on every activation's critical
+// path; lane 2 looks at the very last chunk: once that is there the caller stops asking (returns true).
+// Bounded by the kernel's time-out.
+__device__ static inline bool bfs_wait_planes(const BfsArgs &A, int zlo, int zhi, const int lane) {
+    const GridDev &Gd = A.G;
+    u32 last = 0;
+    if (lane < 3) {
+        zlo = zlo < 0 ? 0 : zlo;
+        zhi = zhi > Gd.PZ - 1 ? Gd.PZ - 1 : zhi;
+        const u32 *f = Gd.ready + ((lane == 0 ? zlo : (lane == 1 ? zhi : Gd.PZ - 1)) >> Gd.ready_shift);
+        if (lane == 2) last = bfs_ld_acquire_sys(f);
+        else {
+            unsigned polls = 0;
+            u64 t0 = 0;
+            while (bfs_ld_acquire_sys(f) == 0u) {
+                __nanosleep(200);
+                if (A.timeout_ns && (++polls & 1023u) == 0u) {
+                    const u64 now = bfs_now_ns();
+                    if (!t0) t0 = now;
+                    else if (now - t0 > A.timeout_ns) { bfs_fail(A, BFS_ERR_TIMEOUT); break; }
+                }
+                if (__ldcg(&A.ctr[BFS_C_DONE])) break;
+            }
+        }
+    }
+    return __shfl_sync(BFS_FULL, last, 2) != 0u;
 }
 
 // A warp's position in the ring: the ticket stays valid across calls of bfs_pop_warp until it is
@@ -491,6 +528,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     const bool peer_lo = bz == 0 && A.lo.g != nullptr, peer_hi = bz == A.nbz - 1 && A.hi.g != nullptr;
 
     const long long tc0 = clock64();
+    if (Gd.ready && !cnt.all_up) cnt.all_up = bfs_wait_planes(A, z0 - 1, z0 + 8, lane) ? 1u : 0u; // occupancy still uploading (e2e overlap)
     // ---- occupancy words (read-only during a search): issued before the claim so that their
     // latency overlaps the claim's round trip ----
     const int ly = lane & 7, lzq = lane >> 3; // the (y, z & 3) this lane handles in row-distributed steps
@@ -913,6 +951,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
 __device__ static inline void bfs_count_init(BfsCount &cnt) {
     cnt.act = cnt.idle = cnt.lowered = cnt.levels = cnt.passes = cnt.redo = cnt.remote = 0;
     cnt.peer_rows = 0;
+    cnt.all_up = 0;
     cnt.c_pop = cnt.c_setup = cnt.c_sweep = cnt.c_extract = cnt.c_publish = 0;
 }
 

@@ -38,7 +38,17 @@ struct pmp_grid {
     double hm_scale; // largest a with a*manhattan admissible
     bool integer_costs;
     int cut; // corner cutting allowed (pmp_grid_set_corner_cutting)
+    // streamed occupancy upload (pmp_grid_set_packed_host_streamed): flags + the event that marks its end
+    u32 *ready_dev;      // owned; n_ready words
+    u32 *ones_host;      // owned, pinned: the source of the flag writes
+    int n_ready;
+    cudaEvent_t ev_reset, ev_uploaded; // owned (created on first use)
+    bool upload_pending; // kernels that cannot wait for chunks must wait for ev_uploaded first (pmp_grid_upload_fence)
 };
+
+// make `stream` wait for a streamed occupancy upload still in flight; every entry point that reads the
+// bitmask and cannot wait chunk by chunk calls this first
+int pmp_grid_upload_fence(pmp_grid *g, cudaStream_t stream);
 
 // ---- weight traits: how a cost field element is stored, compared and advanced ----
 struct WF64 {

@@ -293,6 +293,9 @@ extern "C" int pmp_grid_set_corner_cutting(pmp_grid *g, int allow) {
 
 extern "C" int pmp_grid_destroy(pmp_grid *g) {
     if (!g) return 0;
+    if (g->ready_dev) cudaFree(g->ready_dev);
+    if (g->ones_host) cudaFreeHost(g->ones_host);
+    if (g->ev_reset) { cudaEventDestroy(g->ev_reset); cudaEventDestroy(g->ev_uploaded); }
     cudaFree(g->bits);
     delete g;
     return 0;
@@ -314,6 +317,7 @@ static unsigned blocks_for(size_t n, int per) {
 }
 
 extern "C" int pmp_grid_set_cells(pmp_grid *g, const int32_t *coords_dev, int64_t n, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || (n > 0 && !coords_dev) || n < 0) { pmp_set_error("pmp_grid_set_cells: bad arguments"); return -1; }
     cudaStream_t s = (cudaStream_t)stream;
     const size_t n_words = (size_t)g->d.wpr * g->d.PY * g->d.PZ;
@@ -324,6 +328,7 @@ extern "C" int pmp_grid_set_cells(pmp_grid *g, const int32_t *coords_dev, int64_
 }
 
 extern "C" int pmp_grid_edit_cells(pmp_grid *g, const int32_t *coords_dev, int64_t n, int value, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || (n > 0 && !coords_dev) || n < 0) { pmp_set_error("pmp_grid_edit_cells: bad arguments"); return -1; }
     if (n > 0)
         k_bits_scatter<<<blocks_for((size_t)n, 256), 256, 0, (cudaStream_t)stream>>>(g->d, g->bits, coords_dev, n, value ? 1 : 0);
@@ -332,6 +337,7 @@ extern "C" int pmp_grid_edit_cells(pmp_grid *g, const int32_t *coords_dev, int64
 }
 
 extern "C" int pmp_grid_set_dense(pmp_grid *g, const uint8_t *occ_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || !occ_dev) { pmp_set_error("pmp_grid_set_dense: bad arguments"); return -1; }
     const size_t n_words = (size_t)g->d.wpr * g->d.PY * g->d.PZ;
     k_bits_pack_dense<<<blocks_for(n_words, 8), 256, 0, (cudaStream_t)stream>>>(g->d, g->bits, occ_dev);
@@ -340,6 +346,7 @@ extern "C" int pmp_grid_set_dense(pmp_grid *g, const uint8_t *occ_dev, void *str
 }
 
 extern "C" int pmp_grid_set_dense_xyz(pmp_grid *g, const uint8_t *occ_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || !occ_dev) { pmp_set_error("pmp_grid_set_dense_xyz: bad arguments"); return -1; }
     if (g->d.Y > 65535 || g->d.wpr > 65535) { pmp_set_error("pmp_grid_set_dense_xyz: grid too wide"); return -1; }
     cudaStream_t s = (cudaStream_t)stream;
@@ -353,6 +360,7 @@ extern "C" int pmp_grid_set_dense_xyz(pmp_grid *g, const uint8_t *occ_dev, void 
 }
 
 extern "C" int pmp_grid_set_packed(pmp_grid *g, const uint32_t *rows_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || !rows_dev) { pmp_set_error("pmp_grid_set_packed: bad arguments"); return -1; }
     const size_t n_words = (size_t)g->d.wpr * g->d.PY * g->d.PZ;
     k_bits_from_packed<<<blocks_for(n_words, 256), 256, 0, (cudaStream_t)stream>>>(g->d, g->bits, rows_dev, (g->d.X + 31) / 32);
@@ -360,8 +368,66 @@ extern "C" int pmp_grid_set_packed(pmp_grid *g, const uint32_t *rows_dev, void *
     return 0;
 }
 
+// ---- streamed upload: the search may start while the occupancy is still arriving -----------------------
+int pmp_grid_upload_fence(pmp_grid *g, cudaStream_t stream) {
+    if (!g || !g->upload_pending) return 0;
+    PMP_CHECK_CUDA(cudaStreamWaitEvent(stream, g->ev_uploaded, 0));
+    g->upload_pending = false;
+    g->d.ready = nullptr;
+    return 0;
+}
+
+extern "C" int pmp_grid_set_packed_host_streamed(pmp_grid *g, const uint32_t *rows_host_pinned, int planes_per_chunk,
+                                                 void *search_stream, void *copy_stream) {
+    if (!g || !rows_host_pinned || !copy_stream || copy_stream == search_stream) {
+        pmp_set_error("pmp_grid_set_packed_host_streamed: bad arguments (needs a copy stream of its own)");
+        return -1;
+    }
+    const GridDev &d = g->d;
+    if (d.ndim != 3 || d.X % 32 || d.PY != d.Y || d.PZ != d.Z) {
+        pmp_set_error("pmp_grid_set_packed_host_streamed: needs X %% 32 == 0, Y %% 8 == 0, Z %% 8 == 0 (the rows must be the "
+                      "grid's own layout); use pmp_grid_set_packed");
+        return -1;
+    }
+    int shift = 3;
+    while ((1 << (shift + 1)) <= planes_per_chunk && shift < 10) ++shift; // chunks of 2^shift >= 8 planes
+    const int cp = 1 << shift, nchunks = (d.Z + cp - 1) / cp;
+    if (g->n_ready < nchunks) {
+        if (g->ready_dev) cudaFree(g->ready_dev);
+        if (g->ones_host) cudaFreeHost(g->ones_host);
+        g->ready_dev = nullptr; g->ones_host = nullptr; g->n_ready = 0;
+        PMP_CHECK_CUDA(cudaMalloc(&g->ready_dev, (size_t)nchunks * 4));
+        PMP_CHECK_CUDA(cudaHostAlloc(&g->ones_host, (size_t)nchunks * 4, cudaHostAllocDefault));
+        for (int i = 0; i < nchunks; ++i) g->ones_host[i] = 1u;
+        g->n_ready = nchunks;
+    }
+    if (!g->ev_reset) {
+        PMP_CHECK_CUDA(cudaEventCreateWithFlags(&g->ev_reset, cudaEventDisableTiming));
+        PMP_CHECK_CUDA(cudaEventCreateWithFlags(&g->ev_uploaded, cudaEventDisableTiming));
+    }
+    cudaStream_t ss = (cudaStream_t)search_stream, cs = (cudaStream_t)copy_stream;
+    // the flags go back to zero in search-stream order (after earlier searches, before the next one); the
+    // copies start after that
+    PMP_CHECK_CUDA(cudaMemsetAsync(g->ready_dev, 0, (size_t)nchunks * 4, ss));
+    PMP_CHECK_CUDA(cudaEventRecord(g->ev_reset, ss));
+    PMP_CHECK_CUDA(cudaStreamWaitEvent(cs, g->ev_reset, 0));
+    const size_t plane_words = (size_t)d.wpr * d.PY;
+    for (int c = 0; c < nchunks; ++c) {
+        const int z0 = c * cp, z1 = z0 + cp < d.Z ? z0 + cp : d.Z;
+        PMP_CHECK_CUDA(cudaMemcpyAsync(g->bits + (size_t)z0 * plane_words, rows_host_pinned + (size_t)z0 * plane_words,
+                                       (size_t)(z1 - z0) * plane_words * 4, cudaMemcpyHostToDevice, cs));
+        PMP_CHECK_CUDA(cudaMemcpyAsync(g->ready_dev + c, g->ones_host + c, 4, cudaMemcpyHostToDevice, cs));
+    }
+    PMP_CHECK_CUDA(cudaEventRecord(g->ev_uploaded, cs));
+    g->d.ready = g->ready_dev;
+    g->d.ready_shift = shift;
+    g->upload_pending = true;
+    return 0;
+}
+
 extern "C" int pmp_grid_read_bits(const pmp_grid *g, uint32_t *bits_host, int64_t n_words) {
     if (!g || !bits_host) { pmp_set_error("pmp_grid_read_bits: bad arguments"); return -1; }
+    if (g->upload_pending) { cudaEventSynchronize(g->ev_uploaded); }
     const int64_t have = (int64_t)g->d.wpr * g->d.PY * g->d.PZ;
     if (n_words != have) { pmp_set_error("pmp_grid_read_bits: expected %lld words", (long long)have); return -1; }
     PMP_CHECK_CUDA(cudaMemcpy(bits_host, g->bits, (size_t)have * 4, cudaMemcpyDeviceToHost));
@@ -370,6 +436,7 @@ extern "C" int pmp_grid_read_bits(const pmp_grid *g, uint32_t *bits_host, int64_
 
 extern "C" int pmp_grid_count_free(const pmp_grid *g, int64_t *n_free) {
     if (!g || !n_free) { pmp_set_error("pmp_grid_count_free: bad arguments"); return -1; }
+    if (g->upload_pending) cudaEventSynchronize(g->ev_uploaded);
     u64 *d_out = nullptr;
     PMP_CHECK_CUDA(cudaMalloc(&d_out, 8));
     cudaMemset(d_out, 0, 8);

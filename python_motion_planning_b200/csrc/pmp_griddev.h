@@ -16,5 +16,9 @@ struct GridDev {
     u32 ntiles;
     u64 pcells;
     const u32 *bits; // occupancy, 1 = blocked; row (y,z) at ((z*PY)+y)*wpr
+    // streamed upload in progress (pmp_grid_set_packed_host_streamed): ready[c] != 0 once the planes
+    // [c << ready_shift, (c + 1) << ready_shift) of `bits` have arrived; nullptr: everything is there
+    const u32 *ready;
+    int ready_shift;
 };
 

@@ -20,6 +20,7 @@ __global__ void k_line_of_sight(const GridDev G, size_t n, const int32_t *a, con
 
 extern "C" int pmp_line_of_sight(const pmp_grid *g, int64_t n, const int32_t *a_dev, const int32_t *b_dev,
                                  uint8_t *out_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || n < 0 || (n && (!a_dev || !b_dev || !out_dev))) {
         pmp_set_error("pmp_line_of_sight: bad arguments");
         return -1;
@@ -82,6 +83,7 @@ __global__ void k_shortcut_paths(const GridDev G, u32 nq, const u32 *path, int64
 extern "C" int pmp_shortcut_paths(const pmp_grid *g, int64_t nq, const uint32_t *path_dev, int64_t path_cap,
                                   const int32_t *path_len_dev, uint32_t *out_path_dev, int32_t *out_len_dev,
                                   double *out_cost_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || nq < 1 || !path_dev || path_cap < 1 || !path_len_dev || !out_path_dev || !out_len_dev || !out_cost_dev) {
         pmp_set_error("pmp_shortcut_paths: bad arguments");
         return -1;

@@ -188,6 +188,7 @@ extern "C" int pmp_extract_paths(const pmp_grid *g, int weight, int64_t nq,
                                  const int32_t *starts_dev, const int32_t *goals_dev, const void *g_dev,
                                  uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
                                  double *cost_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || nq < 1 || !starts_dev || !goals_dev || !g_dev || !path_dev || path_cap < 1 || !path_len_dev || !cost_dev) {
         pmp_set_error("pmp_extract_paths: bad arguments");
         return -1;
@@ -262,6 +263,7 @@ __global__ void k_verify_field(const GridDev G, const __grid_constant__ Motions 
 extern "C" int pmp_verify_field(const pmp_grid *g, int weight, const void *g_dev,
                                 const int32_t *source_dev, int z_lo, int z_hi, uint64_t *out_dev,
                                 void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || !g_dev || !out_dev || z_lo < 0 || z_hi > g->d.PZ || z_lo > z_hi) {
         pmp_set_error("pmp_verify_field: bad arguments");
         return -1;
@@ -463,6 +465,7 @@ extern "C" int pmp_gbfs(const pmp_grid *g, int heuristic, int64_t nq,
                         uint32_t *parent_dev, void *heap_dev, int64_t heap_cap,
                         uint32_t *path_dev, int64_t path_cap, int32_t *path_len_dev,
                         double *cost_dev, int32_t *n_expand_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     if (!g || nq < 1 || !starts_dev || !goals_dev || !parent_dev || !heap_dev || heap_cap < 1 ||
         !path_dev || path_cap < 1 || !path_len_dev || !cost_dev || !n_expand_dev) {
         pmp_set_error("pmp_gbfs: bad arguments");

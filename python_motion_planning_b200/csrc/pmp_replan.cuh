@@ -207,6 +207,7 @@ static int replan_check(pmp_grid *g, const pmp_sssp_params *P, const int32_t *st
 extern "C" int pmp_replan_begin(pmp_grid *g, const pmp_sssp_params *P, const int32_t *start_dev,
                                 const int32_t *goal_dev, void *g_dev, void *ws_dev, int64_t ws_bytes,
                                 double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     WsLayout L;
     if (replan_check(g, P, start_dev, goal_dev, g_dev, ws_dev, ws_bytes, L)) return -1;
     return sssp_from_scratch(g, P, 1, start_dev, goal_dev, g_dev, ws_dev, ws_bytes, gcost_dev, status_dev,
@@ -235,6 +236,7 @@ extern "C" int pmp_replan_update(pmp_grid *g, const pmp_sssp_params *P, const in
                                  const int32_t *cells_dev, const uint8_t *blocked_dev, int64_t n_changes,
                                  uint32_t *scratch_dev, int64_t scratch_words,
                                  double *gcost_dev, int32_t *status_dev, uint64_t *stats_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     WsLayout L;
     if (replan_check(g, P, start_dev, goal_dev, g_dev, ws_dev, ws_bytes, L)) return -1;
     if (n_changes < 0 || n_changes > 0x7FFFFFF || (n_changes && (!cells_dev || !blocked_dev))) {

@@ -1316,6 +1316,7 @@ static int sssp_from_scratch(pmp_grid *g, const pmp_sssp_params *P, int64_t nq, 
     if (nq == 1 && P->full_field && P->weight == PMP_W_U32 && !no_prune && pmp_bfs_applicable(g) &&
         !getenv("PMP_B200_OLD_BFS"))
         return pmp_bfs_field(g, starts_dev, g_dev, ws_dev, ws_bytes, gcost_dev, status_dev, stats_dev, stream);
+    if (pmp_grid_upload_fence(g, s)) return -2; // k_sssp cannot wait chunk by chunk for a streamed occupancy upload
     SsspArgs A;
     fill_args(g, P, nq, starts_dev, goals_dev, g_dev, ws_dev, L, A, no_prune);
     const size_t gsz = (size_t)nq * g->d.pcells * (P->weight == PMP_W_F64 ? 8 : 4);
@@ -1440,6 +1441,7 @@ static int slab_check(pmp_grid *g, const pmp_sssp_params *P, void *g_dev, void *
 
 extern "C" int pmp_slab_begin(pmp_grid *g, const pmp_sssp_params *P, const int32_t *start_dev,
                               void *g_dev, void *ws_dev, int64_t ws_bytes, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     WsLayout L;
     if (slab_check(g, P, g_dev, ws_dev, ws_bytes, L)) return -1;
     cudaStream_t s = (cudaStream_t)stream;
@@ -1462,6 +1464,7 @@ extern "C" int pmp_slab_begin(pmp_grid *g, const pmp_sssp_params *P, const int32
 
 extern "C" int pmp_slab_run(pmp_grid *g, const pmp_sssp_params *P, void *g_dev, void *ws_dev,
                             int64_t ws_bytes, double key_bound, uint64_t *out_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     WsLayout L;
     if (slab_check(g, P, g_dev, ws_dev, ws_bytes, L)) return -1;
     if (!out_dev) { pmp_set_error("pmp_slab_run: out_dev is NULL"); return -1; }
@@ -1488,6 +1491,7 @@ extern "C" int pmp_slab_run(pmp_grid *g, const pmp_sssp_params *P, void *g_dev, 
 
 extern "C" int pmp_slab_merge(pmp_grid *g, int weight, void *g_dev, void *ws_dev, int64_t ws_bytes,
                               int z_local, int mark, const void *plane_dev, uint64_t *out_dev, void *stream) {
+    if (g && pmp_grid_upload_fence((pmp_grid *)g, (cudaStream_t)stream)) return -2; // a streamed occupancy upload must have landed
     pmp_sssp_params Q;
     memset(&Q, 0, sizeof Q);
     Q.weight = weight; Q.full_field = 1; Q.algo = PMP_DIJKSTRA;

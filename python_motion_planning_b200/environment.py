@@ -13,6 +13,7 @@ import weakref
 from math import sqrt
 
 import itertools
+import os
 
 import numpy as np
 
@@ -217,6 +218,19 @@ class DeviceGrid:
         if isinstance(rows, t.Tensor):
             if rows.numel() != want or rows.element_size() != 4:
                 raise ValueError(f"packed occupancy: expected {want} 32-bit words")
+            if (not rows.is_cuda and rows.is_pinned() and rows.is_contiguous() and self.ndim == 3 and X % 32 == 0
+                    and self.padded[1] == Y and self.padded[2] == Z and not os.environ.get("PMP_B200_NO_STREAMED_UPLOAD")):
+                # pinned host rows in the grid's own layout: streamed upload -- the copy engine fills the bitmask chunk
+                # by chunk while a unit-weight field search launched next already runs behind it (k_bfs waits per tile
+                # for the chunks it needs); every other entry point waits for the whole upload first
+                if getattr(self, "_copy_stream", None) is None:
+                    self._copy_stream = t.cuda.Stream(device=self.device)
+                _lib.check(self.L.pmp_grid_set_packed_host_streamed(self.handle, rows.data_ptr(), 32, self.stream(),
+                                                                    self._copy_stream.cuda_stream),
+                           "pmp_grid_set_packed_host_streamed")
+                self.h2d_bytes = rows.numel() * 4
+                self._keep = rows
+                return
             self.h2d_bytes = 0 if rows.is_cuda else rows.numel() * 4
             dev = rows.contiguous().to(self.device, non_blocking=True)
         else:
@@ -365,11 +379,15 @@ class _EnvBase:
             occ[tuple(a.T)] = True
         return occ
 
-    def device_grid(self, force=False):
-        """The DeviceGrid mirroring this environment, uploading the occupancy if it changed."""
+    def device_grid(self, force=False, sync=True):
+        """The DeviceGrid mirroring this environment, uploading the occupancy if it changed (sync=False: only
+        create / return the handle -- callers that want their own small uploads queued ahead of a large streamed
+        occupancy upload call it once without and once with sync)."""
         if self._device is None:
             self._device = DeviceGrid(self._ndim, self._dims())
         dg = self._device
+        if not sync:
+            return dg
         small_set = self._dense is None and self._packed is None and len(self._obstacles) <= self._ALWAYS_SYNC_LIMIT
         if force or small_set or self._device_version != self._version:
             if self._packed is not None:

@@ -138,3 +138,29 @@ def test_slab_multi_gpu_torchrun():
     assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-3000:]
     line = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
     assert line["ok"] and line["violations"] == 0 and line["pending"] == 0 and line["reached"] == reached
+
+
+def test_streamed_packed_upload_overlaps_search():
+    """Grid3D.update_packed(pinned host rows) -> pmp_grid_set_packed_host_streamed: the field search starts while the
+    occupancy is still arriving (k_bfs waits per tile for the chunks it needs); results equal the oracle's, twice in a
+    row with different maps on the same grid, and entry points that cannot wait chunk-wise see the complete map."""
+    import torch
+    rng = np.random.default_rng(21)
+    shape = (96, 40, 160)                    # X % 32 == 0, Y % 8 == 0, Z % 8 == 0: the rows are the grid's own layout
+    env = pmp.Grid3D(*shape, walls=False)
+    env.motions = [m for m in env.motions if m.g == 1]
+    for k in range(2):
+        occ = rng.random(shape) < (0.2 + 0.1 * k)
+        free = np.argwhere(~occ)
+        src = tuple(int(v) for v in free[rng.integers(0, len(free))])
+        rows = torch.from_numpy(workloads.pack_rows(occ).view(np.int32)).pin_memory()
+        env.update_packed(rows)
+        f = pmp.cost_field(env, src, weight="u32")
+        assert np.array_equal(f, oracle_field(occ, src)), k
+        assert np.array_equal(env.device_grid().read_bits(), occ)          # the whole map landed
+    # a planner that cannot wait chunk by chunk, right after a streamed upload
+    occ = rng.random(shape) < 0.15
+    env.update_packed(torch.from_numpy(workloads.pack_rows(occ).view(np.int32)).pin_memory())
+    f64 = pmp.cost_field(env, src if not occ[src] else tuple(int(v) for v in np.argwhere(~occ)[0]))   # fp64 path: k_sssp
+    s2 = src if not occ[src] else tuple(int(v) for v in np.argwhere(~occ)[0])
+    assert np.array_equal(f64, oracle_field(occ, s2))
