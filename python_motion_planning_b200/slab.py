@@ -410,6 +410,20 @@ def solve_group(slabs, Z, source_global):
     _lib.check(L.pmp_bfs_slab_run_group(arr, n, slabs[0].dg.stream()), "pmp_bfs_slab_run_group")
 
 
+def gather_slab_records(dist, handle64, info8, device="cpu"):
+    """all-gather the (64-byte IPC handle, 8 x int64 layout) records of every rank's slab arena, ordered by rank --
+    the only data the ranks exchange through torch.distributed for the device-side halo protocol"""
+    import torch
+    rec = np.zeros(128, dtype=np.uint8)
+    rec[:64] = np.frombuffer(handle64, dtype=np.uint8)
+    rec[64:] = np.array(info8, dtype=np.int64).view(np.uint8)
+    mine = torch.from_numpy(rec).to(device)
+    allr = [torch.empty_like(mine) for _ in range(dist.get_world_size())]
+    dist.all_gather(allr, mine)
+    recs = [a.cpu().numpy() for a in allr]
+    return [r[:64].tobytes() for r in recs], [r[64:].view(np.int64).tolist() for r in recs]
+
+
 class BfsSlabSolver:
     """The unit-weight field of one large grid over `world` GPUs, one process per GPU.
 
@@ -425,17 +439,10 @@ class BfsSlabSolver:
                             (shape[0], shape[1], self.z1 - self.z0) if packed else None)
         self.torch = self.slab.torch
         if world > 1:
-            t = self.torch
             h, info = self.slab.export()
-            rec = np.zeros(128, dtype=np.uint8)
-            rec[:64] = np.frombuffer(h, dtype=np.uint8)
-            rec[64:] = np.array(info, dtype=np.int64).view(np.uint8)
             dev = self.slab.dg.device if dist.get_backend() == "nccl" else "cpu"
-            mine = t.from_numpy(rec).to(dev)
-            allr = [t.empty_like(mine) for _ in range(world)]
-            dist.all_gather(allr, mine)
-            recs = [a.cpu().numpy() for a in allr]
-            self.slab.connect([r[:64].tobytes() for r in recs], [r[64:].view(np.int64).tolist() for r in recs])
+            handles, infos = gather_slab_records(dist, h, info, dev)
+            self.slab.connect(handles, infos)
         self.bytes_halo = 0
 
     def _barrier(self):

@@ -239,3 +239,51 @@ def test_batch_sharding_gathers_every_query():
         assert np.array_equal(costs, ref)                    # every rank holds all answers
         assert np.array_equal(plen, ref_len.astype(np.int32))
         assert have_paths == list(range(*shard))             # paths only for the own shard
+
+
+# ---- round 2: host logic of the device-side halo protocol (slab.BfsSlabSolver) ----
+def _records_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from python_motion_planning_b200 import slab
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    try:
+        handle = bytes([(rank * 7 + i) % 251 for i in range(64)])          # stands in for a cudaIpcMemHandle_t
+        z0, z1 = slab.slab_range8(200, rank, world)
+        info = [48, 192, (z1 - z0 + 7) // 8, z1 - z0, 1000 + rank, 2000 + rank, 1536, 1536]
+        handles, infos = slab.gather_slab_records(dist, handle, info, "cpu")
+        q.put((rank, handles, infos))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_slab_record_exchange_is_ordered_by_rank(world):
+    """every rank ends up with every rank's (IPC handle, layout) record, ordered by rank: what
+    pmp_bfs_slab_connect needs; and the 8-aligned slab ranges tile the grid"""
+    import torch.multiprocessing as mp
+    from python_motion_planning_b200 import slab
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_records_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, handles, infos in got:
+        assert len(handles) == world and len(infos) == world
+        for r in range(world):
+            assert handles[r] == bytes([(r * 7 + i) % 251 for i in range(64)])
+            z0, z1 = slab.slab_range8(200, r, world)
+            assert infos[r][3] == z1 - z0 and infos[r][4] == 1000 + r
+    for Z in (8, 64, 200, 1536, 1537):
+        for w in (1, 2, 3, 5, 8):
+            if (Z + 7) // 8 < w:
+                continue
+            edges = [slab.slab_range8(Z, r, w) for r in range(w)]
+            assert edges[0][0] == 0 and edges[-1][1] == Z
+            for (a0, a1), (b0, b1) in zip(edges[:-1], edges[1:]):
+                assert a1 == b0 and a1 % 8 == 0 and a1 > a0
