@@ -299,6 +299,7 @@ class _EnvBase:
         self._device = None
         self._device_version = -1
         self._version = 0
+        self._synced_set = None   # copy of the obstacle set as last uploaded (small sets: detects in-place edits)
 
     def update_packed(self, rows):
         """Occupancy as bit rows [Z][Y][ceil(X/32)] of uint32 (bit i of word w <-> x = 32 w + i, 1 =
@@ -389,12 +390,15 @@ class _EnvBase:
         if not sync:
             return dg
         small_set = self._dense is None and self._packed is None and len(self._obstacles) <= self._ALWAYS_SYNC_LIMIT
+        if small_set and not force and self._device_version == self._version and self._obstacles == self._synced_set:
+            return dg          # in-place edits are looked for on every plan(); nothing changed since the last upload
         if force or small_set or self._device_version != self._version:
             if self._packed is not None:
                 dg.set_packed(self._packed)
             elif self._dense is not None:
                 dg.set_dense(self._dense)
             else:
+                self._synced_set = set(self._obstacles) if small_set else None
                 n = len(self._obstacles)
                 coords = np.fromiter(itertools.chain.from_iterable(self._obstacles), dtype=np.int32,
                                      count=n * self._ndim).reshape(n, self._ndim)
