@@ -304,11 +304,25 @@ def build_c4(args, ctx, n=None, small=False):
         return {"cost": cost, "oracle_cost": None}
 
     def e2e(step):
-        env.update(host_occ)                      # H2D of the occupancy from pinned memory
+        env.update(host_occ)                      # H2D of the occupancy from pinned memory, one byte per cell
         cost, path, expand = pmp.AStar3D(start, goal, env).plan()   # H2D query, D2H cost + path
         return cost, host_occ.numel() + 24, 32 + 4 * len(path)
 
-    return dict(run=run, events=events, account=account, verify=verify, e2e=e2e, name=name, dtype="f64", queries=1,
+    host_rows = torch.from_numpy(workloads.pack_rows(occ).view(np.int32)).pin_memory()
+
+    def e2e_packed():
+        """the same for a caller that holds the map as bits (Grid3D.update_packed: 1/8 of the upload)"""
+        ts = []
+        for _ in range(5):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            env.update_packed(host_rows)
+            cost, path, expand = pmp.AStar3D(start, goal, env).plan()
+            ts.append((time.perf_counter() - t0) * 1e3)
+        env.update(host_occ)
+        return {"ms_per_step": float(np.median(ts)), "h2d_bytes_per_step": host_rows.numel() * 4 + 24, "cost": cost}
+
+    return dict(run=run, events=events, account=account, verify=verify, e2e=e2e, e2e_packed=e2e_packed, name=name, dtype="f64", queries=1,
                 scaling="weak", parallelism="independent replicas", stats=lambda: ws.stats.cpu().numpy(), K=26,
                 cfg={"grid": list(dims), "connectivity": 26, "heuristic": "euclidean", "free_cells": int((~occ).sum())})
 
@@ -601,6 +615,7 @@ def main():
         if rank == 0:
             W4 = build_c4(args, solo, n=512)
             extras["c4"] = sub_record(W4, measure(W4, solo, max(3, args.steps // 2), 3, None, sample_clocks=False), 1)
+            extras["c4"]["e2e_packed_input"] = W4["e2e_packed"]()
             del W4
             torch.cuda.empty_cache()
         if dist is not None:
