@@ -190,16 +190,18 @@ __global__ void k_bfs_group(const BfsArgs *args, int n);
 // kernel (default BFS_SYNC_NT); PMP_B200_BFS_CTAS_PER_SM: fewer CTAs than fit.
 struct BfsLaunch { int blocks, nt, free_running; };
 static int bfs_launch_shape(BfsLaunch *out) {
-    static BfsLaunch L = {0, 0, 0};
+    static BfsLaunch cache[64]; // per device (zero-initialised)
+    int dev = 0;
+    PMP_CHECK_CUDA(cudaGetDevice(&dev));
+    BfsLaunch &L = cache[dev & 63];
     if (!L.blocks) {
-        int per_sm = 0, dev = 0, n_sm = 0;
+        int per_sm = 0, n_sm = 0;
         const char *f = getenv("PMP_B200_BFS_FREE");
         L.free_running = f && atoi(f) != 0;
         const char *t = getenv("PMP_B200_BFS_NT");
         L.nt = L.free_running ? BFS_NT : (t && atoi(t) >= 32 && atoi(t) <= BFS_SYNC_NT && atoi(t) % 32 == 0 ? atoi(t) : BFS_SYNC_NT);
         if (L.free_running) PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs_free, L.nt, 0));
         else PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs, L.nt, 0));
-        PMP_CHECK_CUDA(cudaGetDevice(&dev));
         PMP_CHECK_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
         if (per_sm < 1) { pmp_set_error("k_bfs does not fit on an SM"); return -2; }
         const char *e = getenv("PMP_B200_BFS_CTAS_PER_SM");
@@ -211,11 +213,13 @@ static int bfs_launch_shape(BfsLaunch *out) {
 }
 
 static int bfs_grid_blocks(int *out) { // the free-running group kernel
-    static int blocks = 0;
+    static int cache[64];
+    int dev = 0;
+    PMP_CHECK_CUDA(cudaGetDevice(&dev));
+    int &blocks = cache[dev & 63];
     if (!blocks) {
-        int per_sm = 0, dev = 0, n_sm = 0;
+        int per_sm = 0, n_sm = 0;
         PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs_group, BFS_NT, 0));
-        PMP_CHECK_CUDA(cudaGetDevice(&dev));
         PMP_CHECK_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
         if (per_sm < 1) { pmp_set_error("k_bfs_group does not fit on an SM"); return -2; }
         blocks = per_sm * n_sm;

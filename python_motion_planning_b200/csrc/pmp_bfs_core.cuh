@@ -561,7 +561,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     if (peer_lo || peer_hi) __threadfence_system(); else bfs_fence();
     const u32 dirty = old & BFS_DIRTY;
     bool touched = (old & BFS_T) != 0u;
-    if (cnt.act == 0 && lane == 0 && A.stats && !__ldcg(&A.stats[18])) // [18]: when this rank started its first activation
+    if (A.world > 1 && cnt.act == 0 && lane == 0 && A.stats && !__ldcg(&A.stats[18])) // [18]: when this rank started its first activation
         atomicCAS((unsigned long long *)&A.stats[18], 0ull, (unsigned long long)bfs_now_ns());
     ++cnt.act;
 
@@ -944,7 +944,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     cnt.c_publish += (u64)(clock64() - tc3);
     // [16]: when this rank finished its last activation (its busy span = [16] - [9]; the kernel itself runs
     // until the LAST rank is done)
-    if (lane == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[16], (unsigned long long)bfs_now_ns());
+    if (A.world > 1 && lane == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[16], (unsigned long long)bfs_now_ns());
 }
 
 // ---- persistent warp loop --------------------------------------------------------------------------
