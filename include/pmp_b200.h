@@ -301,7 +301,10 @@ int pmp_cost_field_u32_static(pmp_grid *g, const int32_t *start_dev, uint32_t *g
  *      brackets one kernel launch per rank with two barriers.
  *      Protocol (python_motion_planning_b200/slab.py, BfsSlabSolver): create; export; all-gather
  *      the (handle, info) pairs (torch.distributed); connect; then per search: begin, barrier,
- *      run, barrier.  SURVEY.md 8(b) sketched "pmp_slab_* taking an ncclComm_t": the exchange
+ *      run, barrier.  Ordering across slabs: the slabs emulate ONE queue (ring entries carry a global
+ *      sequence number; a rank starts an entry only when the entries started on all ranks come within
+ *      a window of it, PMP_B200_BFS_PACE, default 1024, 0 = off) -- without it a slab with a short queue
+ *      runs ahead and recomputes its cells as the bulk of the wave arrives.  SURVEY.md 8(b) sketched "pmp_slab_* taking an ncclComm_t": the exchange
  *      itself needs no communicator, only the peers' mapped arenas. ---- */
 typedef struct pmp_bfs_slab pmp_bfs_slab;
 int pmp_bfs_slab_create(pmp_grid *g_local, int rank, int world, pmp_bfs_slab **out);
