@@ -40,6 +40,9 @@
 // bfs_process_tile), warps without a tile take the same barriers.  A warp may therefore not block in
 // the queue while its CTA waits for it: it polls the ring a few times (bfs_pop_warp keeps the
 // ticket) and joins the round empty-handed otherwise.
+// MULTI = false: a whole grid on one GPU (no peer, pacing or remote-queue code in the kernel at all);
+// MULTI = true: one z-slab of several (pmp_bfs_slab_*).
+template <bool MULTI>
 __global__ void __launch_bounds__(BFS_SYNC_NT, BFS_SYNC_MINB) k_bfs(const __grid_constant__ BfsArgs A) {
     const int lane = (int)(threadIdx.x & 31);
     bfs_reject_check(A, lane, blockIdx.x == 0 && threadIdx.x < 32);
@@ -50,16 +53,18 @@ __global__ void __launch_bounds__(BFS_SYNC_NT, BFS_SYNC_MINB) k_bfs(const __grid
     for (;;) {
         const long long tp = clock64();
         bool done = false;
-        const u64 item = bfs_pop_warp(A, P, lane, BFS_TRY_POLLS, done);
+        const u64 item = bfs_pop_warp<MULTI>(A, P, lane, BFS_TRY_POLLS, done);
         if (!__syncthreads_or(item != 0ull)) {          // nobody in the CTA has work
             if (__syncthreads_and(done)) break;       // ... and the search is over for everyone
             continue;
         }
         if (item) {
             cnt.c_pop += (u64)(clock64() - tp);
-            bfs_process_tile<true>(A, item, lane, cnt);
+            bfs_process_tile<true, MULTI>(A, item, lane, cnt);
         } else {
-            BFS_PHASE_SYNC(); BFS_PHASE_SYNC(); BFS_PHASE_SYNC(); // the three phase boundaries of bfs_process_tile
+            if (BFS_SYNC_MASK & 1) BFS_PHASE_SYNC(); // the phase boundaries of bfs_process_tile
+            if (BFS_SYNC_MASK & 2) BFS_PHASE_SYNC();
+            if (BFS_SYNC_MASK & 4) BFS_PHASE_SYNC();
         }
     }
     bfs_count_flush(A, cnt, lane);
@@ -69,7 +74,7 @@ __global__ void __launch_bounds__(BFS_SYNC_NT, BFS_SYNC_MINB) k_bfs(const __grid
 // free-running form of the same search (every warp on its own; PMP_B200_BFS_FREE=1): the A/B partner
 // of k_bfs in profiles/r02_notes.md
 __global__ void __launch_bounds__(BFS_NT, BFS_MINB) k_bfs_free(const __grid_constant__ BfsArgs A) {
-    bfs_warp_main(A, (int)(threadIdx.x & 31), blockIdx.x == 0 && threadIdx.x < 32);
+    bfs_warp_main<false>(A, (int)(threadIdx.x & 31), blockIdx.x == 0 && threadIdx.x < 32);
     if ((threadIdx.x & 31) == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[10], (unsigned long long)bfs_now_ns());
 }
 
@@ -201,7 +206,7 @@ static int bfs_launch_shape(BfsLaunch *out) {
         const char *t = getenv("PMP_B200_BFS_NT");
         L.nt = L.free_running ? BFS_NT : (t && atoi(t) >= 32 && atoi(t) <= BFS_SYNC_NT && atoi(t) % 32 == 0 ? atoi(t) : BFS_SYNC_NT);
         if (L.free_running) PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs_free, L.nt, 0));
-        else PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs, L.nt, 0));
+        else PMP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bfs<true>, L.nt, 0)); // (the larger of the two)
         PMP_CHECK_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
         if (per_sm < 1) { pmp_set_error("k_bfs does not fit on an SM"); return -2; }
         const char *e = getenv("PMP_B200_BFS_CTAS_PER_SM");
@@ -239,8 +244,9 @@ static int bfs_reset_ws(const BfsArgs &A, const BfsLayout &L, cudaStream_t s) {
 static int bfs_launch_search(const BfsArgs &A, cudaStream_t s) {
     BfsLaunch L;
     if (bfs_launch_shape(&L)) return -2;
-    if (L.free_running) k_bfs_free<<<L.blocks, L.nt, 0, s>>>(A);
-    else k_bfs<<<L.blocks, L.nt, 0, s>>>(A);
+    if (L.free_running && A.world == 1) k_bfs_free<<<L.blocks, L.nt, 0, s>>>(A);
+    else if (A.world > 1) k_bfs<true><<<L.blocks, L.nt, 0, s>>>(A);
+    else k_bfs<false><<<L.blocks, L.nt, 0, s>>>(A);
     PMP_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -529,7 +535,7 @@ extern "C" int pmp_bfs_slab_run(pmp_bfs_slab *s, int32_t *status_dev, uint64_t *
 __global__ void __launch_bounds__(BFS_NT, BFS_MINB) k_bfs_group(const BfsArgs *args, int n) {
     const u32 gwarp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const BfsArgs &A = args[gwarp % (u32)n];
-    bfs_warp_main(A, (int)(threadIdx.x & 31), gwarp < (u32)n);
+    bfs_warp_main<true>(A, (int)(threadIdx.x & 31), gwarp < (u32)n);
     if ((threadIdx.x & 31) == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[10], (unsigned long long)bfs_now_ns());
 }
 

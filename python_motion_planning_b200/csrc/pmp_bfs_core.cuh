@@ -67,6 +67,9 @@
 #ifndef BFS_PHASE_SYNC
 #define BFS_PHASE_SYNC()
 #endif
+#ifndef BFS_SYNC_MASK
+#define BFS_SYNC_MASK 7 // which phase boundaries carry a barrier: 1 setup|sweep, 2 sweep|extract, 4 extract|publish
+#endif
 
 #define BFS_ERR_TIMEOUT 1u
 #define BFS_ERR_BUDGET 2u
@@ -217,7 +220,7 @@ __device__ __noinline__ static void bfs_fail(const BfsArgs &A, u32 code) {
 // tile's rows span at most two) with acquire loads -- no fence, this sits on every activation's critical
 // path; lane 2 looks at the very last chunk: once that is there the caller stops asking (returns true).
 // Bounded by the kernel's time-out.
-__device__ static inline bool bfs_wait_planes(const BfsArgs &A, int zlo, int zhi, const int lane) {
+__device__ __noinline__ static bool bfs_wait_planes(const BfsArgs &A, int zlo, int zhi, const int lane) {
     const GridDev &Gd = A.G;
     u32 last = 0;
     if (lane < 3) {
@@ -261,6 +264,8 @@ struct BfsPop {
 // kernel a warp without a tile sits out its CTA's round at the barriers); without this an item
 // could wait a whole round while other warps idle, and the wave would run out of order.  The taker
 // leaves a tombstone, so the holder knows to draw a new ticket.
+// MULTI: this rank is one of several slabs (pacing, peer queues); false strips all of it from the single-GPU kernel
+template <bool MULTI>
 __device__ static inline u64 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int lane, const unsigned max_polls,
                                           bool &done) {
     done = false;
@@ -304,14 +309,14 @@ __device__ static inline u64 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int
         if (got) {
             // pacing (multi-GPU only): would a single FIFO over all slabs have reached this entry yet?
             u32 hold = 0;
-            if (A.pace_window) {
+            if (MULTI && A.pace_window) {
                 if (lane == 0 && P.held_polls < A.pace_hold_polls && !__ldcg(&A.ctr[BFS_C_DONE]))
                     hold = (int)((u32)(got >> 32) - (bfs_seq_sum(A, BFS_C_GS, BFS_C_STARTED) + A.pace_window)) > 0 ? 1u : 0u;
                 hold = __shfl_sync(BFS_FULL, hold, 0);
             }
             if (!hold) {
                 P.held = 0ull;
-                if (A.pace_window && lane == 0) bfs_seq_bump(A, BFS_C_STARTED, BFS_C_GS);
+                if (MULTI && A.pace_window && lane == 0) bfs_seq_bump(A, BFS_C_STARTED, BFS_C_GS);
                 return got;
             }
             P.held = got;
@@ -339,7 +344,7 @@ __device__ static inline u64 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int
 
 // this rank has nothing in flight any more: leave the set of active ranks; the last one ends
 // the search everywhere
-__device__ static inline void bfs_rank_idle(const BfsArgs &A) {
+__device__ __noinline__ static void bfs_rank_idle(const BfsArgs &A) {
     __threadfence_system();
     if (atomicSub(A.active, 1u) == 1u) {
         for (int r = 0; r < A.world; ++r) bfs_store_volatile(&A.peer_ctr[r][BFS_C_DONE], 1u);
@@ -516,7 +521,7 @@ __device__ __forceinline__ u32 bfs_rel(const u32 c, const u32 base, u32 &far, u3
 
 // ---- one tile activation -----------------------------------------------------------------------
 // SYNC: the phase-locked kernel (CTA barriers at the phase boundaries); false: free-running warps
-template <bool SYNC>
+template <bool SYNC, bool MULTI>
 __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 entry, const int lane, BfsCount &cnt) {
     const u32 t = (u32)entry - 1u; // tile id (the upper half, the entry's sequence number, has served its purpose)
     const GridDev &Gd = A.G;
@@ -525,7 +530,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     const size_t sY = (size_t)Gd.PX, sZ = (size_t)Gd.PX * Gd.PY;
     const bool inx = x0 + lane < Gd.PX;
     u32 *cell0 = A.g + (size_t)z0 * sZ + (size_t)y0 * sY + (size_t)(x0 + lane);
-    const bool peer_lo = bz == 0 && A.lo.g != nullptr, peer_hi = bz == A.nbz - 1 && A.hi.g != nullptr;
+    const bool peer_lo = MULTI && bz == 0 && A.lo.g != nullptr, peer_hi = MULTI && bz == A.nbz - 1 && A.hi.g != nullptr;
 
     const long long tc0 = clock64();
     if (Gd.ready && !cnt.all_up) cnt.all_up = bfs_wait_planes(A, z0 - 1, z0 + 8, lane) ? 1u : 0u; // occupancy still uploading (e2e overlap)
@@ -561,7 +566,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     if (peer_lo || peer_hi) __threadfence_system(); else bfs_fence();
     const u32 dirty = old & BFS_DIRTY;
     bool touched = (old & BFS_T) != 0u;
-    if (A.world > 1 && cnt.act == 0 && lane == 0 && A.stats && !__ldcg(&A.stats[18])) // [18]: when this rank started its first activation
+    if (MULTI && cnt.act == 0 && lane == 0 && A.stats && !__ldcg(&A.stats[18])) // [18]: when this rank started its first activation
         atomicCAS((unsigned long long *)&A.stats[18], 0ull, (unsigned long long)bfs_now_ns());
     ++cnt.act;
 
@@ -749,36 +754,37 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     // ---- sweep, extract, store; continuation passes if a wave outlives the recordable range ----
     // (BFS_PHASE_SYNC: in the phase-locked kernel all warps of the CTA enter each phase together, so
     // that they share its instructions in the instruction cache)
+    // One instance of the sweep and of the extraction in the code (the kernel is instruction-cache bound):
+    // a wave that outlives the recordable range of a pass (rare: corridors winding inside a tile) goes round
+    // the same loop again without the barriers -- every warp of the CTA takes each barrier exactly once.
     u32 R0 = 0, R1 = 0, pbase = base;
     u32 rec[BFS_NREC][2];
     u32 carry0 = 0, carry1 = 0;
-    if (SYNC) { BFS_PHASE_SYNC(); }
+    if (SYNC && (BFS_SYNC_MASK & 1)) { BFS_PHASE_SYNC(); }
     const long long tc1 = clock64();
-    if (active) {
-        cnt.levels += bfs_sweep(free0, free1, SA, SB, init0, init1, R0, R1, rec, carry0, carry1, lane);
-        ++cnt.passes;
-    }
-    const long long tc2 = clock64();
-    cnt.c_sweep += (u64)(tc2 - tc1);
-    if (SYNC) { BFS_PHASE_SYNC(); }
-    if (active) {
-        bfs_extract(rec, R0, R1, pbase, cell0, inx, sY, sZ, touched, low0, low1);
-        touched = true;
-        while (__any_sync(BFS_FULL, (carry0 | carry1) != 0u)) { // rare: a wave longer than one pass records
-            const u32 P0 = R0, P1 = R1;
-            init0 = carry0; init1 = carry1;
-            pbase += BFS_LIM;
-            SA.last = -1; SB.last = -1;
+    long long tsw = 0;
+    for (int pass = 0;; ++pass) {
+        const u32 P0 = R0, P1 = R1;
+        const long long ta = clock64();
+        if (active) {
             cnt.levels += bfs_sweep(free0, free1, SA, SB, init0, init1, R0, R1, rec, carry0, carry1, lane);
             ++cnt.passes;
-            bfs_extract(rec, R0 & ~P0, R1 & ~P1, pbase, cell0, inx, sY, sZ, touched, low0, low1);
         }
-        cnt.lowered += (u32)(__popc(low0) + __popc(low1));
-    } else {
-        ++cnt.idle;
+        tsw += clock64() - ta;
+        if (SYNC && (BFS_SYNC_MASK & 2) && pass == 0) { BFS_PHASE_SYNC(); }
+        if (!active) break;
+        bfs_extract(rec, R0 & ~P0, R1 & ~P1, pbase, cell0, inx, sY, sZ, touched, low0, low1);
+        touched = true;
+        if (!__any_sync(BFS_FULL, (carry0 | carry1) != 0u)) break;
+        init0 = carry0; init1 = carry1;
+        pbase += BFS_LIM;
+        SA.last = -1; SB.last = -1;
     }
-    cnt.c_extract += (u64)(clock64() - tc2);
-    if (SYNC) { BFS_PHASE_SYNC(); }
+    if (active) cnt.lowered += (u32)(__popc(low0) + __popc(low1));
+    else ++cnt.idle;
+    cnt.c_sweep += (u64)tsw;
+    cnt.c_extract += (u64)(clock64() - tc1 - tsw);
+    if (SYNC && (BFS_SYNC_MASK & 4)) { BFS_PHASE_SYNC(); }
 
     // ---- publish: every store above is visible before a neighbour is armed ----
     const long long tc3 = clock64();
@@ -819,68 +825,42 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
             }
             arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << 1;
         }
-        // y / z faces: this lane's own column
-        const u32 cym0 = low0 & ymf0, cym1 = low1 & ymf1, cyp0 = low0 & ypf0, cyp1 = low1 & ypf1;
-        const u32 czm = low0 & zmf, czp = low1 & zpf;
-        if (__any_sync(BFS_FULL, (cym0 | cym1) != 0u)) {
-            bool imp = !(dirty & 4u) && (cym0 | cym1) != 0u;
-            if (dirty & 4u) {
+        // y / z faces (this lane's own column) through one loop body, like the candidates: face f = 0 y-, 1 y+,
+        // 2 z-, 3 z+ (arm bit 2 + f).  The lowered cells that have a free cell behind the face are gathered
+        // into 8 bits (one per row of the face).
+        const u32 cm[4] = {bfs_compress4(low0 & ymf0) | (bfs_compress4(low1 & ymf1) << 4),
+                           bfs_compress4((low0 & ypf0) >> 7) | (bfs_compress4((low1 & ypf1) >> 7) << 4),
+                           low0 & zmf, (low1 & zpf) >> 24};
+#pragma unroll 1
+        for (int f = 0; f < 4; ++f) {
+            const u32 c = f == 0 ? cm[0] : (f == 1 ? cm[1] : (f == 2 ? cm[2] : cm[3]));
+            if (!__any_sync(BFS_FULL, c != 0u)) continue;
+            bool imp = c != 0u;
+            if ((dirty >> (f + 2)) & 1u) { // the wave came through this face: only real improvements count
+                imp = false;
+                const bool yface = f < 2, hiside = (f & 1) != 0;
+                const bool peer = f == 2 ? peer_lo : (f == 3 ? peer_hi : false);
+                const size_t step = yface ? sZ : sY;
+                const u32 *hrow = yface ? (hiside ? cell0 + 8 * sY : cell0 - sY)
+                                        : (f == 2 ? (peer_lo ? A.lo.g + (size_t)A.lo.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 - sZ)
+                                                  : (peer_hi ? A.hi.g + (size_t)A.hi.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 + 8 * sZ));
+                const u32 *orow = yface ? (hiside ? cell0 + 7 * sY : cell0) : (hiside ? cell0 + 7 * sZ : cell0);
+                if (MULTI && peer) cnt.peer_rows += (u32)__popc(__reduce_or_sync(BFS_FULL, c));
 #pragma unroll
-                for (int z = 0; z < 8; ++z)
-                    if (((z < 4 ? cym0 : cym1) >> ((z & 3) * 8)) & 1u) {
-                        const u32 own = __ldcg(cell0 + (size_t)z * sZ), h = __ldcg(cell0 + (size_t)z * sZ - sY);
+                for (int i = 0; i < 8; ++i)
+                    if ((c >> i) & 1u) {
+                        const u32 own = __ldcg(orow + (size_t)i * step);
+                        const u32 h = (MULTI && peer) ? bfs_ld_peer(hrow + (size_t)i * step) : __ldcg(hrow + (size_t)i * step);
                         imp |= own + 2u < h;
                     }
             }
-            arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << 2;
-        }
-        if (__any_sync(BFS_FULL, (cyp0 | cyp1) != 0u)) {
-            bool imp = !(dirty & 8u) && (cyp0 | cyp1) != 0u;
-            if (dirty & 8u) {
-#pragma unroll
-                for (int z = 0; z < 8; ++z)
-                    if (((z < 4 ? cyp0 : cyp1) >> ((z & 3) * 8 + 7)) & 1u) {
-                        const u32 own = __ldcg(cell0 + (size_t)z * sZ + 7 * sY), h = __ldcg(cell0 + (size_t)z * sZ + 8 * sY);
-                        imp |= own + 2u < h;
-                    }
-            }
-            arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << 3;
-        }
-        if (__any_sync(BFS_FULL, czm != 0u)) {
-            bool imp = !(dirty & 16u) && czm != 0u;
-            if (dirty & 16u) {
-                if (peer_lo) cnt.peer_rows += (u32)__popc(__reduce_or_sync(BFS_FULL, czm));
-                const u32 *hrow = peer_lo ? A.lo.g + (size_t)A.lo.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 - sZ;
-#pragma unroll
-                for (int y = 0; y < 8; ++y)
-                    if ((czm >> y) & 1u) {
-                        const u32 own = __ldcg(cell0 + (size_t)y * sY);
-                        const u32 h = peer_lo ? bfs_ld_peer(hrow + (size_t)y * sY) : __ldcg(hrow + (size_t)y * sY);
-                        imp |= own + 2u < h;
-                    }
-            }
-            arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << 4;
-        }
-        if (__any_sync(BFS_FULL, czp != 0u)) {
-            bool imp = !(dirty & 32u) && czp != 0u;
-            if (dirty & 32u) {
-                if (peer_hi) cnt.peer_rows += (u32)__popc(__reduce_or_sync(BFS_FULL, czp >> 24));
-                const u32 *hrow = peer_hi ? A.hi.g + (size_t)A.hi.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 + 8 * sZ;
-#pragma unroll
-                for (int y = 0; y < 8; ++y)
-                    if ((czp >> (24 + y)) & 1u) {
-                        const u32 own = __ldcg(cell0 + 7 * sZ + (size_t)y * sY);
-                        const u32 h = peer_hi ? bfs_ld_peer(hrow + (size_t)y * sY) : __ldcg(hrow + (size_t)y * sY);
-                        imp |= own + 2u < h;
-                    }
-            }
-            arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << 5;
+            arms |= (__any_sync(BFS_FULL, imp) ? 1u : 0u) << (f + 2);
         }
     }
 
     // sequence number of everything this activation queues: the entries pushed so far on all ranks
     u32 seq_out = 0;
-    if (A.pace_window) {
+    if (MULTI && A.pace_window) {
         if (lane == 0) seq_out = bfs_seq_sum(A, BFS_C_GP, BFS_C_PUSHED);
         seq_out = __shfl_sync(BFS_FULL, seq_out, 0);
     }
@@ -892,7 +872,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         const int nx = bx + (f == 0 ? -1 : (f == 1 ? 1 : 0)), ny = by + (f == 2 ? -1 : (f == 3 ? 1 : 0));
         const int nz = bz + (f == 4 ? -1 : (f == 5 ? 1 : 0));
         const u32 bit = (1u << (f ^ 1)) | BFS_Q;
-        if (nz < 0 || nz >= A.nbz) { // the neighbour tile lives on the peer GPU
+        if (MULTI && (nz < 0 || nz >= A.nbz)) { // the neighbour tile lives on the peer GPU
             const BfsPeer &P = nz < 0 ? A.lo : A.hi;
             ntile = (u32)((P.bzadj * A.nby + ny) * A.nbx + nx);
             const u32 was = atomicOr(&P.state[ntile], bit);
@@ -933,7 +913,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         __syncwarp();
     }
     if (need_push || requeue) {
-        if (A.pace_window) bfs_seq_bump(A, BFS_C_PUSHED, BFS_C_GP);
+        if (MULTI && A.pace_window) bfs_seq_bump(A, BFS_C_PUSHED, BFS_C_GP);
         bfs_push(A.ring, A.ring_cap, A.ctr, requeue ? t : ntile, seq_out);
         if (requeue) ++cnt.redo;
     }
@@ -944,7 +924,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     cnt.c_publish += (u64)(clock64() - tc3);
     // [16]: when this rank finished its last activation (its busy span = [16] - [9]; the kernel itself runs
     // until the LAST rank is done)
-    if (A.world > 1 && lane == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[16], (unsigned long long)bfs_now_ns());
+    if (MULTI && lane == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[16], (unsigned long long)bfs_now_ns());
 }
 
 // ---- persistent warp loop --------------------------------------------------------------------------
@@ -979,13 +959,14 @@ __device__ static inline void bfs_count_flush(const BfsArgs &A, BfsCount &cnt, c
 
 // the first warp of a rank ends the search at once when the source was rejected (blocked /
 // outside the box: k_bfs_init left a flag and queued nothing)
-__device__ static inline void bfs_reject_check(const BfsArgs &A, const int lane, const bool first) {
+__device__ __noinline__ static void bfs_reject_check(const BfsArgs &A, const int lane, const bool first) {
     if (first && lane == 0 && __ldcg(&A.ctr[BFS_C_SRC + 3]))
         for (int r = 0; r < A.world; ++r) bfs_store_volatile(&A.peer_ctr[r][BFS_C_DONE], 1u);
 }
 
 // free-running form: every warp loops pop -> process on its own (the CPU emulator and the slab
 // group kernel; the single-rank kernel k_bfs keeps the warps of a CTA in the same phase instead)
+template <bool MULTI>
 __device__ static inline void bfs_warp_main(const BfsArgs &A, const int lane, const bool first) {
     bfs_reject_check(A, lane, first);
     BfsCount cnt;
@@ -995,10 +976,10 @@ __device__ static inline void bfs_warp_main(const BfsArgs &A, const int lane, co
     for (;;) {
         const long long tp = clock64();
         bool done = false;
-        const u64 item = bfs_pop_warp(A, P, lane, 0xFFFFFFFFu, done);
+        const u64 item = bfs_pop_warp<MULTI>(A, P, lane, 0xFFFFFFFFu, done);
         if (item == 0ull) break;
         cnt.c_pop += (u64)(clock64() - tp);
-        bfs_process_tile<false>(A, item, lane, cnt);
+        bfs_process_tile<false, MULTI>(A, item, lane, cnt);
     }
     bfs_count_flush(A, cnt, lane);
 }

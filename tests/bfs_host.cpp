@@ -30,7 +30,8 @@ static int g_warps = 4;
 
 static void entry(int warp, int lane, void *) {
     const int r = warp / g_warps;
-    bfs_warp_main(R[r].A, lane, warp % g_warps == 0);
+    if (R.size() > 1) bfs_warp_main<true>(R[r].A, lane, warp % g_warps == 0);
+    else bfs_warp_main<false>(R[r].A, lane, warp % g_warps == 0);
 }
 
 static uint64_t rng_state;
