@@ -692,39 +692,40 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     if (active) {
         // ---- bit-sliced seed levels ----
         u32 far = 0, lastA = 0, lastB = 0, anyA = 0, anyB = 0;
-        {
-            // relative levels, packed one byte per cell; bit 7 of a byte marks "no seed"
-            u32 pYm[2] = {0, 0}, pYp[2] = {0, 0}, pZm[2] = {0, 0}, pZp[2] = {0, 0};
+        // The four y / z faces through one loop body again (the candidate arrays are rotated through cYm):
+        // relative levels packed one byte per cell (bit 7 = "no seed"), then sliced into the six seed planes.
+        //   y faces: cell (y, z) of word z >> 2 sits at bit (z & 3) * 8 + y -- the packed bytes line up (y = 0 / 7);
+        //   z faces: cell (y, z = 0) at bit y of word 0, (y, z = 7) at bit 24 + y of word 1.
+#pragma unroll 1
+        for (int f = 0; f < 4; ++f) {
+            u32 p0 = 0, p1 = 0;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                pYm[i >> 2] |= bfs_rel(cYm[i], base, far, anyA, lastA) << ((i & 3) * 8);
-                pYp[i >> 2] |= bfs_rel(cYp[i], base, far, anyA, lastA) << ((i & 3) * 8);
-                pZm[i >> 2] |= bfs_rel(cZm[i], base, far, anyA, lastA) << ((i & 3) * 8);
-                pZp[i >> 2] |= bfs_rel(cZp[i], base, far, anyA, lastA) << ((i & 3) * 8);
+                const u32 r = bfs_rel(cYm[i], base, far, anyA, lastA) << ((i & 3) * 8);
+                if (i < 4) p0 |= r; else p1 |= r;
             }
-            // y faces: cell (y, z) of word z >> 2 sits at bit (z & 3) * 8 + y: the packed bytes line up
-#pragma unroll
-            for (int w = 0; w < 2; ++w) {
-                const u32 vm = (~pYm[w] >> 7) & 0x01010101u, vp = (~pYp[w] >> 7) & 0x01010101u;
-                SA.sv[w] |= vm | (vp << 7);
-#pragma unroll
-                for (int b = 0; b < 6; ++b)
-                    SA.sp[b][w] |= ((pYm[w] >> b) & vm) | (((pYp[w] >> b) & vp) << 7);
-            }
-            // z faces: cell (y, z = 0) at bit y of word 0, (y, z = 7) at bit 24 + y of word 1
-            {
-                const u32 vm = bfs_compress4(~pZm[0] >> 7) | (bfs_compress4(~pZm[1] >> 7) << 4);
-                const u32 vp = bfs_compress4(~pZp[0] >> 7) | (bfs_compress4(~pZp[1] >> 7) << 4);
-                SA.sv[0] |= vm;
-                SA.sv[1] |= vp << 24;
+            if (f < 2) {
+                const u32 sh = f ? 7u : 0u;
+                const u32 v0 = (~p0 >> 7) & 0x01010101u, v1 = (~p1 >> 7) & 0x01010101u;
+                SA.sv[0] |= v0 << sh; SA.sv[1] |= v1 << sh;
 #pragma unroll
                 for (int b = 0; b < 6; ++b) {
-                    const u32 nm = bfs_compress4(pZm[0] >> b) | (bfs_compress4(pZm[1] >> b) << 4);
-                    const u32 np = bfs_compress4(pZp[0] >> b) | (bfs_compress4(pZp[1] >> b) << 4);
-                    SA.sp[b][0] |= nm & vm;
-                    SA.sp[b][1] |= (np & vp) << 24;
+                    SA.sp[b][0] |= ((p0 >> b) & v0) << sh;
+                    SA.sp[b][1] |= ((p1 >> b) & v1) << sh;
+                }
+            } else {
+                const u32 v = bfs_compress4(~p0 >> 7) | (bfs_compress4(~p1 >> 7) << 4);
+                const u32 m0 = f == 2 ? BFS_FULL : 0u; // z-: word 0, bits 0..7; z+: word 1, bits 24..31
+                SA.sv[0] |= v & m0; SA.sv[1] |= (v << 24) & ~m0;
+#pragma unroll
+                for (int b = 0; b < 6; ++b) {
+                    const u32 n = (bfs_compress4(p0 >> b) | (bfs_compress4(p1 >> b) << 4)) & v;
+                    SA.sp[b][0] |= n & m0;
+                    SA.sp[b][1] |= (n << 24) & ~m0;
                 }
             }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { const u32 t0 = cYm[i]; cYm[i] = cYp[i]; cYp[i] = cZm[i]; cZm[i] = cZp[i]; cZp[i] = t0; }
         }
         // x faces: the ballots assemble lane 0's (x-) and lane 31's (x+) words
 #pragma unroll
