@@ -28,7 +28,25 @@ struct Rank {
 static std::vector<Rank> R;
 static int g_warps = 4;
 
+// streamed occupancy upload (GridDev.ready): an extra "copy engine" fiber sets the chunk flags one by one
+// while the search runs; the occupancy words of a chunk are garbage until its flag is set
+static std::vector<u32> g_ready, g_bits_final;
+static int g_stream_shift = -1;
+
 static void entry(int warp, int lane, void *) {
+    if (warp == (int)R.size() * g_warps) { // the copy-engine fiber (lane 0 only; the other lanes leave at once)
+        if (lane != 0) return;
+        Rank &K = R[0];
+        const int cp = 1 << g_stream_shift, PZ = K.A.G.PZ;
+        const size_t plane = (size_t)K.A.G.wpr * K.A.G.PY;
+        for (int c = 0; c * cp < PZ; ++c) {
+            for (int k = 0; k < 40; ++k) simt::yield();                       // the copy takes a while
+            const size_t a = (size_t)c * cp * plane, b = std::min((size_t)(c + 1) * cp, (size_t)PZ) * plane;
+            for (size_t i = a; i < b; ++i) K.bits[i] = g_bits_final[i];          // the chunk lands ...
+            g_ready[c] = 1;                                                      // ... then its flag
+        }
+        return;
+    }
     const int r = warp / g_warps;
     if (R.size() > 1) bfs_warp_main<true>(R[r].A, lane, warp % g_warps == 0);
     else bfs_warp_main<false>(R[r].A, lane, warp % g_warps == 0);
@@ -47,6 +65,7 @@ int main(int argc, char **argv) {
     const int dens = atoi(argv[5]), nr = atoi(argv[6]);
     g_warps = atoi(argv[7]);
     const int mode = argc > 8 ? atoi(argv[8]) : 0;
+    g_stream_shift = argc > 9 ? atoi(argv[9]) : -1; // >= 3: planes per chunk = 2^shift, single rank only
     rng_state = seed * 0x9E3779B97F4A7C15ull + 99;
     for (int i = 0; i < 8; ++i) rnd32();
 
@@ -171,7 +190,16 @@ int main(int argc, char **argv) {
         K.ctr[BFS_C_SRC] = (u32)sx; K.ctr[BFS_C_SRC + 1] = (u32)sy; K.ctr[BFS_C_SRC + 2] = (u32)lz;
     }
 
-    simt::run(nr * g_warps, entry, nullptr, seed, 3);
+    if (g_stream_shift >= 3 && nr == 1) {
+        Rank &K = R[0];
+        g_bits_final = K.bits;
+        for (auto &w : K.bits) w = 0xA5A5A5A5u ^ (u32)(&w - K.bits.data()); // garbage until the chunk "arrives"
+        g_ready.assign((K.A.G.PZ >> g_stream_shift) + 2, 0);
+        K.A.G.ready = g_ready.data();
+        K.A.G.ready_shift = g_stream_shift;
+        // the source's chunk must be there before the init step reads it (k_bfs_init waits for it on the device)
+    } else g_stream_shift = -1;
+    simt::run(nr * g_warps + (g_stream_shift >= 3 ? 1 : 0), entry, nullptr, seed, 3);
 
     // ---- fill untouched tiles, compare ----
     size_t bad = 0, reached = 0;

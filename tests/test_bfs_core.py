@@ -68,6 +68,14 @@ def test_field_multi_slab(exe, cfg):
     assert int(st["bad"]) == 0
 
 
+@pytest.mark.parametrize("cfg", [(64, 24, 64, 31, 20, 1, 3, 0, 3), (40, 16, 48, 32, 10, 1, 2, 1, 4), (96, 16, 40, 33, 0, 1, 4, 2, 3)])
+def test_streamed_occupancy(exe, cfg):
+    """GridDev.ready: the occupancy arrives chunk by chunk (a copy-engine fiber) while the search runs; a tile
+    waits for the chunks its rows lie in and never reads words that have not landed (they hold garbage)"""
+    st = run(exe, *cfg)
+    assert int(st["bad"]) == 0
+
+
 def test_interleavings(exe):
     """the same case under different warp interleavings (the seed drives the scheduler too)"""
     for seed in range(20, 28):
