@@ -19,7 +19,7 @@
 #define BFS_MINB 4 // resident CTAs per SM the register budget is sized for
 #endif
 #ifndef BFS_TRY_POLLS
-#define BFS_TRY_POLLS 6 // polls of the ring slot (32 ns ... 1 us apart) before a warp joins its CTA's round without a tile
+#define BFS_TRY_POLLS 3 // polls of the ring slot (32, 64, 128 ns apart) before a warp joins its CTA's round without a tile
 #endif
 #ifndef BFS_SYNC_NT
 #define BFS_SYNC_NT 128 // threads per CTA of the phase-locked kernel (4 warps in step; measured best of 128 / 256 / 512)

@@ -67,6 +67,9 @@
 #ifndef BFS_PHASE_SYNC
 #define BFS_PHASE_SYNC()
 #endif
+#ifndef BFS_SLEEP_CAP
+#define BFS_SLEEP_CAP 128 // longest back-off (ns) of a warp polling an empty ring slot (1024 -> 128: -3..6 % at 1536^3)
+#endif
 #ifndef BFS_SYNC_MASK
 #define BFS_SYNC_MASK 7 // which phase boundaries carry a barrier: 1 setup|sweep, 2 sweep|extract, 4 extract|publish
 #endif
@@ -338,7 +341,7 @@ __device__ static inline u64 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int
         if (flag) { done = true; return 0ull; }
         if (polls >= max_polls) return 0ull;
         __nanosleep(ns);
-        if (ns < 1024) ns *= 2;
+        if (ns < BFS_SLEEP_CAP) ns *= 2;
     }
 }
 
