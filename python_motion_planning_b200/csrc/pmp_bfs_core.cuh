@@ -303,7 +303,8 @@ __device__ static inline u64 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int
                 if (lane == l) g = atomicCAS((unsigned long long *)slot, (unsigned long long)v, l == 31 ? 0ull : BFS_TOMB) == v ? v : 0ull;
                 got = ((u64)__shfl_sync(BFS_FULL, (u32)(g >> 32), l) << 32) | (u64)__shfl_sync(BFS_FULL, (u32)g, l);
                 if (!got) continue; // somebody else was faster: look again at once
-                bfs_fence();
+                // no fence here: the entry only names a tile; the claim that follows (an atomic on the tile's
+                // state word, then a fence) is what orders the field reads behind the neighbours' stores
                 if (l == 31) P.have = 0u;
                 P.t0 = 0;
                 P.held_polls = 0;

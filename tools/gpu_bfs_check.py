@@ -22,6 +22,9 @@ def main():
     rng = np.random.default_rng(0)
     ok = True
     quick = "--quick" in sys.argv
+    reps = 3
+    if "--reps" in sys.argv:
+        reps = int(sys.argv.pop(sys.argv.index("--reps") + 1))
     sizes = [int(a) for a in sys.argv[1:] if a.isdigit()] or [256, 512]
     keep = oracle.motion_costs(oracle.MOTIONS_3D) == 1.0
     motions, mg = oracle.MOTIONS_3D[keep], oracle.motion_costs(oracle.MOTIONS_3D)[keep]
@@ -51,12 +54,14 @@ def main():
         blk, _ = workloads.replicated_boxes3d(base=128, reps=n // 128)
         occ = workloads.replicated_slab(blk, (n, n, n), 0, n)
         env = env6(occ)
-        for rep in range(3):
+        kms = []
+        for rep in range(reps):
             torch.cuda.synchronize()
             t0 = time.perf_counter()
             ws, st = pmp.cost_field(env, (1, 1, 1), weight="u32", to_host=False)
             torch.cuda.synchronize()
             dt = time.perf_counter() - t0
+            kms.append(float(ws.stats[8].item()) / 1e6)
         dg = env.device_grid()
         out = torch.zeros(3, dtype=torch.int64, device=dg.device)
         src = torch.tensor([1, 1, 1], dtype=torch.int32, device=dg.device)
@@ -65,7 +70,8 @@ def main():
         s = ws.stats.cpu().numpy()
         na = max(int(s[1]), 1)
         ph = {k: round(float(s[i]) / na / 1965.0, 2) for k, i in (("wait", 4), ("setup", 6), ("sweep", 11), ("extract", 3), ("publish", 0))}
-        print(f"c5 {n}^3: {dt*1e3:.2f} ms wall, kernel {s[8]/1e6:.2f} ms, certificate violations {bad}, reached {reached}, pending {pend}, "
+        ks = sorted(kms[1:] or kms)
+        print(f"c5 {n}^3: {dt*1e3:.2f} ms wall, kernel {s[8]/1e6:.2f} ms (median {ks[len(ks)//2]:.2f} min {ks[0]:.2f} of {len(ks)}), certificate violations {bad}, reached {reached}, pending {pend}, "
               f"activations {s[1]} (idle {s[13]}) lowered {s[2]} levels {s[12]} passes {s[14]} requeues {s[5]} err {s[15]} "
               f"status {ws.status.cpu().tolist()} us/activation/warp {ph}", flush=True)
         ok &= bad == 0 and pend == 0 and s[15] == 0
