@@ -170,14 +170,19 @@ __device__ __forceinline__ u32 bfs_transpose32(u32 v, const int lane) {
     return v;
 }
 
-// 8 x 8 bit-matrix transpose of the 64-bit value hi:lo (row k = byte k)
+// 8 x 8 bit-matrix transpose of the 64-bit value hi:lo (row k = byte k).  The first two butterfly steps
+// never move a bit across the two words, the third swaps the high nibbles of lo's bytes with the low
+// nibbles of hi's -- written on the 32-bit halves (the 64-bit form costs funnel shifts: 36 instead of 20
+// instructions, 16 times per activation).
 __device__ __forceinline__ void bfs_transpose8(u32 &lo, u32 &hi) {
-    u64 x = (u64)lo | ((u64)hi << 32), t;
-    t = (x ^ (x >> 7)) & 0x00AA00AA00AA00AAull; x = x ^ t ^ (t << 7);
-    t = (x ^ (x >> 14)) & 0x0000CCCC0000CCCCull; x = x ^ t ^ (t << 14);
-    t = (x ^ (x >> 28)) & 0x00000000F0F0F0F0ull; x = x ^ t ^ (t << 28);
-    lo = (u32)x;
-    hi = (u32)(x >> 32);
+    u32 t;
+    t = (lo ^ (lo >> 7)) & 0x00AA00AAu; lo = lo ^ t ^ (t << 7);
+    t = (hi ^ (hi >> 7)) & 0x00AA00AAu; hi = hi ^ t ^ (t << 7);
+    t = (lo ^ (lo >> 14)) & 0x0000CCCCu; lo = lo ^ t ^ (t << 14);
+    t = (hi ^ (hi >> 14)) & 0x0000CCCCu; hi = hi ^ t ^ (t << 14);
+    const u32 nl = (lo & 0x0F0F0F0Fu) | ((hi << 4) & 0xF0F0F0F0u);
+    hi = (hi & 0xF0F0F0F0u) | ((lo >> 4) & 0x0F0F0F0Fu);
+    lo = nl;
 }
 
 // ---- ring ------------------------------------------------------------------------------------
@@ -451,15 +456,14 @@ __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const
     return nlev;
 }
 
-// ---- levels -> field words -----------------------------------------------------------------------
-// For the cells in N (reached in this pass) the value is base + recorded level.  TOUCHED: the
-// tile already holds values -> min-merge, store only lowered cells; otherwise every word of the
-// tile is written (unreached / blocked cells = all-ones).  Returns the lowered cells in low[].
 // One (z, word) group of 8 cells: byte zb of the 7 planes + the "not reached" plane -> 8 x 8 bit
 // matrix -> one level byte per cell -> field words.  Returns the lowered cells as 8 bits.
+// TOUCHED: the tile already holds values -> min-merge, store only lowered cells; otherwise every word of the
+// group is written (unreached / blocked cells = all-ones) and the lowered cells are the reached ones.
+template <bool TOUCHED>
 __device__ __forceinline__ u32 bfs_extract8(const u32 r0, const u32 r1, const u32 r2, const u32 r3, const u32 r4,
                                             const u32 r5, const u32 r6, const u32 Nw, const u32 zb, const u32 base2,
-                                            u32 *pz, const size_t strideY, const bool inx, const bool touched) {
+                                            u32 *pz, const size_t strideY) {
     const u32 sel = zb | ((4u + zb) << 4);
     const u32 t01 = __byte_perm(r0, r1, sel), t23 = __byte_perm(r2, r3, sel);
     const u32 t45 = __byte_perm(r4, r5, sel), t67 = __byte_perm(r6, ~Nw, sel);
@@ -474,39 +478,44 @@ __device__ __forceinline__ u32 bfs_extract8(const u32 r0, const u32 r1, const u3
         const u32 lv = __byte_perm(src, 0u, 0x4440u | (u32)(y & 3));
         // a cell that was not reached has bit 7 of its byte set -> an all-ones word ("unreached")
         const u32 word = bfs_byte_sign(src, y & 3) | (base2 + (lv << 1));
-        if (touched) {
+        if (TOUCHED) {
             // min-merge: only reached cells can be lower (they are free cells, hence inside the row)
             if ((nb >> y) & 1u) {
                 const u32 own = __ldcg(p);
                 if (word < own) { bfs_store(p, word); low |= 1u << y; } // stored words order like their values
             }
-        } else if (inx) {
+        } else {
             bfs_store(p, word);
         }
         p += strideY;
     }
-    return touched ? low : nb;
+    return TOUCHED ? low : nb;
 }
 
 // ---- levels -> field words -----------------------------------------------------------------------
-// For the cells in N (reached in this pass) the value is base + recorded level.  touched: the
-// tile already holds values -> min-merge, store only lowered cells; otherwise every word of the
-// tile is written (unreached / blocked cells = all-ones).  Adds the lowered cells to low[].
-// A runtime loop over the four byte positions keeps the code small (the kernel is instruction-
-// cache bound when fully unrolled: profiles/r02_notes.md).
+// For the cells in N (reached in this pass) the value is base + recorded level.  Adds the lowered cells
+// to low[].  A runtime loop over the four byte positions keeps the code small; the two forms (first
+// visit of a tile: plain stores of all 64 words of the lane's column, no branches; later visits:
+// min-merge of the reached cells) have a loop each.
+template <bool TOUCHED>
+__device__ __forceinline__ void bfs_extract_loop(const u32 (&rec)[BFS_NREC][2], const u32 N0, const u32 N1, const u32 base2,
+                                                 u32 *pz, const size_t strideY, const size_t strideZ, u32 &low0, u32 &low1) {
+#pragma unroll 1
+    for (u32 zb = 0; zb < 4; ++zb) {
+        low0 |= bfs_extract8<TOUCHED>(rec[0][0], rec[1][0], rec[2][0], rec[3][0], rec[4][0], rec[5][0], rec[6][0], N0, zb, base2,
+                                      pz, strideY) << (zb * 8u);
+        low1 |= bfs_extract8<TOUCHED>(rec[0][1], rec[1][1], rec[2][1], rec[3][1], rec[4][1], rec[5][1], rec[6][1], N1, zb, base2,
+                                      pz + 4 * strideZ, strideY) << (zb * 8u);
+        pz += strideZ;
+    }
+}
 __device__ __forceinline__ void bfs_extract(const u32 (&rec)[BFS_NREC][2], const u32 N0, const u32 N1, const u32 base,
                                             u32 *cell0, const bool inx, const size_t strideY, const size_t strideZ,
                                             const bool touched, u32 &low0, u32 &low1) {
     const u32 base2 = (base << 1) | 1u; // stored word of level 0
-    u32 *pz = cell0;
-#pragma unroll 1
-    for (u32 zb = 0; zb < 4; ++zb) {
-        low0 |= bfs_extract8(rec[0][0], rec[1][0], rec[2][0], rec[3][0], rec[4][0], rec[5][0], rec[6][0], N0, zb, base2,
-                             pz, strideY, inx, touched) << (zb * 8u);
-        low1 |= bfs_extract8(rec[0][1], rec[1][1], rec[2][1], rec[3][1], rec[4][1], rec[5][1], rec[6][1], N1, zb, base2,
-                             pz + 4 * strideZ, strideY, inx, touched) << (zb * 8u);
-        pz += strideZ;
-    }
+    if (touched) bfs_extract_loop<true>(rec, N0, N1, base2, cell0, strideY, strideZ, low0, low1);
+    else if (inx) bfs_extract_loop<false>(rec, N0, N1, base2, cell0, strideY, strideZ, low0, low1);
+    // (a lane whose column lies outside the box has no free cell: N = 0, nothing lowered)
 }
 
 // candidate value read across a face: halo + 1, or BFS_CINV if the halo cell is unreached
@@ -700,7 +709,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         // relative levels packed one byte per cell (bit 7 = "no seed"), then sliced into the six seed planes.
         //   y faces: cell (y, z) of word z >> 2 sits at bit (z & 3) * 8 + y -- the packed bytes line up (y = 0 / 7);
         //   z faces: cell (y, z = 0) at bit y of word 0, (y, z = 7) at bit 24 + y of word 1.
-#pragma unroll 1
+    #pragma unroll 1
         for (int f = 0; f < 4; ++f) {
             u32 p0 = 0, p1 = 0;
 #pragma unroll
@@ -836,7 +845,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         const u32 cm[4] = {bfs_compress4(low0 & ymf0) | (bfs_compress4(low1 & ymf1) << 4),
                            bfs_compress4((low0 & ypf0) >> 7) | (bfs_compress4((low1 & ypf1) >> 7) << 4),
                            low0 & zmf, (low1 & zpf) >> 24};
-#pragma unroll 1
+    #pragma unroll 1
         for (int f = 0; f < 4; ++f) {
             const u32 c = f == 0 ? cm[0] : (f == 1 ? cm[1] : (f == 2 ? cm[2] : cm[3]));
             if (!__any_sync(BFS_FULL, c != 0u)) continue;
