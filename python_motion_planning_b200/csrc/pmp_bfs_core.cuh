@@ -532,6 +532,47 @@ __device__ __forceinline__ u32 bfs_rel(const u32 c, const u32 base, u32 &far, u3
     return r;
 }
 
+// The eight candidates of one y / z face (face F: 0 = y-, 1 = y+, 2 = z-, 3 = z+; index = z for y faces, y for z
+// faces) -> seed planes.  Packed as bytes: level relative to the base, saturated at 0x80 (= no candidate); a byte
+// with bit 6 set is a candidate beyond the seed planes (`farw` collects the bytes).
+//   y faces: cell (y, z) of word z >> 2 sits at bit (z & 3) * 8 + y -- the packed bytes line up (y = 0 / 7);
+//   z faces: cell (y, z = 0) is bit y of word 0, (y, z = 7) bit 24 + y of word 1 -- an 8 x 8 bit transpose of the
+//   eight bytes yields the planes as bytes.
+template <int F>
+__device__ __forceinline__ void bfs_seed_face(const u32 (&c)[8], const u32 base, BfsSeeds &S, u32 &farw) {
+    u32 p0 = 0, p1 = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const u32 d = c[i] - base; // >= 0; an absent candidate gives a huge value
+        const u32 r = (d < 0x80u ? d : 0x80u) << ((i & 3) * 8);
+        if (i < 4) p0 |= r; else p1 |= r;
+    }
+    farw |= p0 | p1;
+    if (F < 2) {
+        constexpr u32 sh = F ? 7u : 0u;
+        const u32 v0 = (~(p0 | (p0 << 1)) >> 7) & 0x01010101u, v1 = (~(p1 | (p1 << 1)) >> 7) & 0x01010101u; // bits 6, 7 clear
+        S.sv[0] |= v0 << sh; S.sv[1] |= v1 << sh;
+#pragma unroll
+        for (int b = 0; b < 6; ++b) {
+            S.sp[b][0] |= ((p0 >> b) & v0) << sh;
+            S.sp[b][1] |= ((p1 >> b) & v1) << sh;
+        }
+    } else {
+        u32 lo = p0, hi = p1;
+        bfs_transpose8(lo, hi); // byte b of hi:lo = bit b of the eight bytes: planes 0..3 in lo, 4, 5 in hi, then "far", "none"
+        const u32 v = ~((hi >> 16) | (hi >> 24)) & 0xFFu;
+        if (F == 2) {
+            S.sv[0] |= v;
+#pragma unroll
+            for (int b = 0; b < 6; ++b) S.sp[b][0] |= ((b < 4 ? lo : hi) >> ((b & 3) * 8)) & v;
+        } else {
+            S.sv[1] |= v << 24;
+#pragma unroll
+            for (int b = 0; b < 6; ++b) S.sp[b][1] |= (((b < 4 ? lo : hi) >> ((b & 3) * 8)) & v) << 24;
+        }
+    }
+}
+
 // ---- one tile activation -----------------------------------------------------------------------
 // SYNC: the phase-locked kernel (CTA barriers at the phase boundaries); false: free-running warps
 template <bool SYNC, bool MULTI>
@@ -679,14 +720,18 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         if (lane == sx) { if (sz < 4) init0 = 1u << (sz * 8 + sy); else init1 = 1u << ((sz - 4) * 8 + sy); }
     }
 
-    // ---- pass base = smallest candidate ----
+    // ---- pass base = smallest candidate; the largest one bounds the last seed level ----
+    // (an absent candidate is all-ones: the largest unsigned and, read as signed, the smallest value)
     u32 base;
+    int maxA = -1;
     {
         u32 m = BFS_CINV;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             m = cYm[i] < m ? cYm[i] : m; m = cYp[i] < m ? cYp[i] : m;
             m = cZm[i] < m ? cZm[i] : m; m = cZp[i] < m ? cZp[i] : m;
+            maxA = (int)cYm[i] > maxA ? (int)cYm[i] : maxA; maxA = (int)cYp[i] > maxA ? (int)cYp[i] : maxA;
+            maxA = (int)cZm[i] > maxA ? (int)cZm[i] : maxA; maxA = (int)cZp[i] > maxA ? (int)cZp[i] : maxA;
         }
         m = cXm[0] < m ? cXm[0] : m; m = cXm[1] < m ? cXm[1] : m;
         m = cXp[0] < m ? cXp[0] : m; m = cXp[1] < m ? cXp[1] : m;
@@ -704,42 +749,15 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     SA.last = SB.last = -1;
     if (active) {
         // ---- bit-sliced seed levels ----
-        u32 far = 0, lastA = 0, lastB = 0, anyA = 0, anyB = 0;
-        // The four y / z faces through one loop body again (the candidate arrays are rotated through cYm):
-        // relative levels packed one byte per cell (bit 7 = "no seed"), then sliced into the six seed planes.
-        //   y faces: cell (y, z) of word z >> 2 sits at bit (z & 3) * 8 + y -- the packed bytes line up (y = 0 / 7);
-        //   z faces: cell (y, z = 0) at bit y of word 0, (y, z = 7) at bit 24 + y of word 1.
-    #pragma unroll 1
-        for (int f = 0; f < 4; ++f) {
-            u32 p0 = 0, p1 = 0;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const u32 r = bfs_rel(cYm[i], base, far, anyA, lastA) << ((i & 3) * 8);
-                if (i < 4) p0 |= r; else p1 |= r;
-            }
-            if (f < 2) {
-                const u32 sh = f ? 7u : 0u;
-                const u32 v0 = (~p0 >> 7) & 0x01010101u, v1 = (~p1 >> 7) & 0x01010101u;
-                SA.sv[0] |= v0 << sh; SA.sv[1] |= v1 << sh;
-#pragma unroll
-                for (int b = 0; b < 6; ++b) {
-                    SA.sp[b][0] |= ((p0 >> b) & v0) << sh;
-                    SA.sp[b][1] |= ((p1 >> b) & v1) << sh;
-                }
-            } else {
-                const u32 v = bfs_compress4(~p0 >> 7) | (bfs_compress4(~p1 >> 7) << 4);
-                const u32 m0 = f == 2 ? BFS_FULL : 0u; // z-: word 0, bits 0..7; z+: word 1, bits 24..31
-                SA.sv[0] |= v & m0; SA.sv[1] |= (v << 24) & ~m0;
-#pragma unroll
-                for (int b = 0; b < 6; ++b) {
-                    const u32 n = (bfs_compress4(p0 >> b) | (bfs_compress4(p1 >> b) << 4)) & v;
-                    SA.sp[b][0] |= n & m0;
-                    SA.sp[b][1] |= (n << 24) & ~m0;
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) { const u32 t0 = cYm[i]; cYm[i] = cYp[i]; cYp[i] = cZm[i]; cZm[i] = cZp[i]; cZp[i] = t0; }
-        }
+        // y / z faces: the eight candidates of a face become eight bytes (level relative to the base; 0x40..0x7F: beyond
+        // the six seed planes, left for a later activation; 0x80: no candidate) and the planes are cut from the packed
+        // words -- a few instructions per face instead of a dozen per candidate.
+        u32 farw = 0;
+        bfs_seed_face<0>(cYm, base, SA, farw);
+        bfs_seed_face<1>(cYp, base, SA, farw);
+        bfs_seed_face<2>(cZm, base, SA, farw);
+        bfs_seed_face<3>(cZp, base, SA, farw);
+        u32 far = farw & 0x40404040u, lastB = 0, anyB = 0;
         // x faces: the ballots assemble lane 0's (x-) and lane 31's (x+) words
 #pragma unroll
         for (int w = 0; w < 2; ++w) {
@@ -756,8 +774,11 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
             }
         }
         {
-            const u32 la = __reduce_max_sync(BFS_FULL, lastA), lb = __reduce_max_sync(BFS_FULL, lastB);
-            SA.last = __any_sync(BFS_FULL, anyA != 0u) ? (int)la : -1;
+            // last seed level of the y / z faces: exact unless some candidate lies beyond the planes (then 63, a bound)
+            const int ma = __reduce_max_sync(BFS_FULL, maxA);
+            const u32 la = (u32)ma - base;
+            const u32 lb = __reduce_max_sync(BFS_FULL, lastB);
+            SA.last = __any_sync(BFS_FULL, (SA.sv[0] | SA.sv[1]) != 0u) ? (int)(la < BFS_SEEDMAX ? la : BFS_SEEDMAX) : -1;
             SB.last = __any_sync(BFS_FULL, anyB != 0u) ? (int)lb : -1;
             if (__any_sync(BFS_FULL, far != 0u)) redo = dirty;
         }
