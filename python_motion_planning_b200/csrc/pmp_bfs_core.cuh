@@ -158,16 +158,23 @@ __device__ __forceinline__ u32 bfs_spread4(u32 n) { return ((n & 0xFu) * 0x00204
 __device__ __forceinline__ u32 bfs_compress4(u32 x) { return (((x & 0x01010101u) * 0x01020408u) >> 24) & 0xFu; }
 
 // 32 x 32 bit-matrix transpose across the warp: afterwards lane x holds the word whose bit l is
-// bit x of the word lane l passed in.
-__device__ __forceinline__ u32 bfs_transpose32(u32 v, const int lane) {
+// bit x of the word lane l passed in.  Three matrices at once (the tile's two occupancy words and
+// the rows behind its faces).  Butterfly step j: a lane with bit j set keeps its high j-blocks and
+// takes the partner's high blocks moved down, the others the mirror image; both are "rotate the
+// partner's word, then select by mask" -- the rotation count and the mask depend on the lane and the
+// step only, so the three words share them: shuffle + funnel shift + one LOP3 per word and step.
+__device__ __forceinline__ void bfs_transpose32x3(u32 &a, u32 &b, u32 &c, const int lane) {
 #pragma unroll
     for (int j = 16; j >= 1; j >>= 1) {
         const u32 m = j == 16 ? 0x0000FFFFu : (j == 8 ? 0x00FF00FFu : (j == 4 ? 0x0F0F0F0Fu : (j == 2 ? 0x33333333u : 0x55555555u)));
-        const u32 o = __shfl_xor_sync(BFS_FULL, v, j);
-        if (lane & j) v = (v & ~m) | ((o >> j) & m);
-        else v = (v & m) | ((o << j) & ~m);
+        const bool up = (lane & j) != 0;
+        const u32 keep = up ? ~m : m;          // bits of the own word that stay
+        const int rs = up ? j : 32 - j;        // rotate the partner's word right by this much
+        const u32 oa = __shfl_xor_sync(BFS_FULL, a, j), ob = __shfl_xor_sync(BFS_FULL, b, j), oc = __shfl_xor_sync(BFS_FULL, c, j);
+        a = (a & keep) | (((oa >> rs) | (oa << (32 - rs))) & ~keep);
+        b = (b & keep) | (((ob >> rs) | (ob << (32 - rs))) & ~keep);
+        c = (c & keep) | (((oc >> rs) | (oc << (32 - rs))) & ~keep);
     }
-    return v;
 }
 
 // 8 x 8 bit-matrix transpose of the 64-bit value hi:lo (row k = byte k).  The first two butterfly steps
@@ -532,6 +539,31 @@ __device__ __forceinline__ u32 bfs_rel(const u32 c, const u32 base, u32 &far, u3
     return r;
 }
 
+// Candidates read across one y / z face (F: 0 = y-, 1 = y+, 2 = z-, 3 = z+): for each of the eight boundary cells of
+// this lane's column the halo value + 1 if the cell is free and that beats its own value, else BFS_CINV.
+// hrow / orow: the first of the eight halo / own rows, `step` apart; fw_lo / fw_hi: the free-cell words holding the
+// boundary cells 0..3 / 4..7.  (An unreached halo word gives 0x80000000, above every own value: no explicit test.)
+template <int F>
+__device__ __forceinline__ void bfs_face_cand(u32 (&c)[8], const bool dirty, const u32 *hrow, const u32 *orow, const size_t step,
+                                              const bool peer, const bool inx, const bool touched, const u32 fw_lo, const u32 fw_hi) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) c[i] = BFS_CINV;
+    if (!dirty) return;
+    u32 h[8], o[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        h[i] = inx ? (peer ? bfs_ld_peer(hrow + (size_t)i * step) : __ldcg(hrow + (size_t)i * step)) : BFS_RAWINF;
+        o[i] = (touched && inx) ? __ldcg(orow + (size_t)i * step) : BFS_RAWINF;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const u32 cv = (h[i] >> 1) + 1u;
+        const u32 sh = F < 2 ? (u32)((i & 3) * 8) + (F ? 7u : 0u) : (u32)i + (F == 3 ? 24u : 0u);
+        const u32 fr = ((i < 4 ? fw_lo : fw_hi) >> sh) & 1u;
+        if (fr && cv < (o[i] >> 1)) c[i] = cv;
+    }
+}
+
 // The eight candidates of one y / z face (face F: 0 = y-, 1 = y+, 2 = z-, 3 = z+; index = z for y faces, y for z
 // faces) -> seed planes.  Packed as bytes: level relative to the base, saturated at 0x80 (= no candidate); a byte
 // with bit 6 set is a candidate beyond the seed planes (`farw` collects the bytes).
@@ -626,10 +658,11 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
 
     // ---- occupancy rows -> this lane's column bits; free cells on the far side of each face (a
     // neighbour tile is only armed through them) ----
-    const u32 free0 = ~bfs_transpose32(oc0, lane), free1 = ~bfs_transpose32(oc1, lane);
+    u32 free0 = oc0, free1 = oc1, nf = onb;
+    bfs_transpose32x3(free0, free1, nf, lane);
+    free0 = ~free0; free1 = ~free1; nf = ~nf;
     u32 ymf0, ymf1, ypf0, ypf1, zmf, zpf, xmf0, xmf1, xpf0, xpf1;
     {
-        const u32 nf = ~bfs_transpose32(onb, lane);
         ymf0 = bfs_spread4(nf); ymf1 = bfs_spread4(nf >> 4);
         ypf0 = bfs_spread4(nf >> 8) << 7; ypf1 = bfs_spread4(nf >> 12) << 7;
         zmf = (nf >> 16) & 0xFFu;
@@ -639,46 +672,18 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     }
 
     // ---- candidates across the dirty faces: halo + 1 where it beats the own boundary value ----
-    // The four y / z faces run through ONE loop body (runtime face index, results rotated through
-    // the four register arrays): a quarter of the code of four unrolled copies -- the kernel is
-    // instruction-cache sensitive.  Face f: 0 = y-, 1 = y+, 2 = z-, 3 = z+ (dirty bit 4 << f).
+    // Face 0 = y-, 1 = y+, 2 = z-, 3 = z+ (dirty bit 4 << f); a clean face costs one uniform branch.
     u32 cYm[8], cYp[8], cZm[8], cZp[8], cXm[2], cXp[2];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) cYm[i] = cYp[i] = cZm[i] = cZp[i] = BFS_CINV;
     cXm[0] = cXm[1] = cXp[0] = cXp[1] = BFS_CINV;
-#pragma unroll 1
-    for (int f = 0; f < 4; ++f) {
-        u32 tc[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) tc[i] = BFS_CINV;
-        if ((dirty >> (f + 2)) & 1u) {
-            const bool yface = f < 2, hiside = (f & 1) != 0;
-            const bool peer = f == 2 ? peer_lo : (f == 3 ? peer_hi : false);
-            const size_t step = yface ? sZ : sY; // between the 8 rows of the face
-            // halo rows: the neighbour's boundary rows (on the lowest / highest tile row of a slab the peer GPU's)
-            const u32 *hrow = yface ? (hiside ? cell0 + 8 * sY : cell0 - sY)
-                                    : (f == 2 ? (peer_lo ? A.lo.g + (size_t)A.lo.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 - sZ)
-                                              : (peer_hi ? A.hi.g + (size_t)A.hi.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 + 8 * sZ));
-            const u32 *orow = yface ? (hiside ? cell0 + 7 * sY : cell0) : (hiside ? cell0 + 7 * sZ : cell0);
-            const u32 shb = yface ? (hiside ? 7u : 0u) : (hiside ? 24u : 0u);
-            const u32 fw_lo = yface ? free0 : (hiside ? free1 : free0), fw_hi = yface ? free1 : fw_lo;
-            if (peer) cnt.peer_rows += 8;
-            u32 h[8], o[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                h[i] = inx ? (peer ? bfs_ld_peer(hrow + (size_t)i * step) : __ldcg(hrow + (size_t)i * step)) : BFS_RAWINF;
-                o[i] = (touched && inx) ? __ldcg(orow + (size_t)i * step) : BFS_RAWINF;
-            }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const u32 c = bfs_cand(h[i]);
-                const u32 sh = shb + (yface ? (u32)((i & 3) * 8) : (u32)i);
-                const u32 fr = ((i < 4 ? fw_lo : fw_hi) >> sh) & 1u;
-                tc[i] = (fr && c != BFS_CINV && c < (o[i] >> 1)) ? c : BFS_CINV;
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { cYm[i] = cYp[i]; cYp[i] = cZm[i]; cZm[i] = cZp[i]; cZp[i] = tc[i]; }
+    {
+        // halo rows: the neighbour's boundary rows (on the lowest / highest tile row of a slab the peer GPU's)
+        const u32 *zlo = peer_lo ? A.lo.g + (size_t)A.lo.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 - sZ;
+        const u32 *zhi = peer_hi ? A.hi.g + (size_t)A.hi.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 + 8 * sZ;
+        bfs_face_cand<0>(cYm, (dirty & 4u) != 0u, cell0 - sY, cell0, sZ, false, inx, touched, free0, free1);
+        bfs_face_cand<1>(cYp, (dirty & 8u) != 0u, cell0 + 8 * sY, cell0 + 7 * sY, sZ, false, inx, touched, free0, free1);
+        bfs_face_cand<2>(cZm, (dirty & 16u) != 0u, zlo, cell0, sY, peer_lo, inx, touched, free0, free0);
+        bfs_face_cand<3>(cZp, (dirty & 32u) != 0u, zhi, cell0 + 7 * sZ, sY, peer_hi, inx, touched, free1, free1);
+        if (MULTI) cnt.peer_rows += (((dirty & 16u) && peer_lo) ? 8u : 0u) + (((dirty & 32u) && peer_hi) ? 8u : 0u);
     }
     // x faces, row-distributed: this lane looks at the cells (y = ly, z = lzq + 4w)
     u32 *colrow = A.g + (size_t)(z0 + lzq) * sZ + (size_t)(y0 + ly) * sY + (size_t)x0;
