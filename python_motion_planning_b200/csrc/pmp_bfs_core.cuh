@@ -67,6 +67,9 @@
 #ifndef BFS_PHASE_SYNC
 #define BFS_PHASE_SYNC()
 #endif
+#ifndef BFS_VOTE_EACH
+#define BFS_VOTE_EACH 0 // 1: the sweep asks after every level whether the wave has died out (0: once per block of levels)
+#endif
 #ifndef BFS_SLEEP_CAP
 #define BFS_SLEEP_CAP 128 // longest back-off (ns) of a warp polling an empty ring slot (1024 -> 128: -3..6 % at 1536^3)
 #endif
@@ -452,8 +455,15 @@ __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const
             c0 = n0 & free0 & ~R0;
             c1 = n1 & free1 & ~R1;
             ++nlev;
+#if BFS_VOTE_EACH
             if (rb + k >= last && !__any_sync(BFS_FULL, (c0 | c1) != 0u)) { fin = true; break; }
+#endif
         }
+#if !BFS_VOTE_EACH
+        // the wave has died out (and no seed is left): asked once per block of levels -- a vote per level costs more
+        // than the up to BFS_UB - 1 empty levels swept past the end
+        if (rb + BFS_UB - 1 >= last && !__any_sync(BFS_FULL, (c0 | c1) != 0u)) fin = true;
+#endif
 #pragma unroll
         for (int b = BFS_LB; b < BFS_NREC; ++b)
             if ((rb >> b) & 1) { rec[b][0] |= bf0; rec[b][1] |= bf1; }
