@@ -70,6 +70,16 @@
 #ifndef BFS_VOTE_EACH
 #define BFS_VOTE_EACH 0 // 1: the sweep asks after every level whether the wave has died out (0: once per block of levels)
 #endif
+#ifndef BFS_CLAIM_FENCE
+#define BFS_CLAIM_FENCE 1 // experiment: 0 = no fence between the claim and the halo loads (single GPU)
+#endif
+#ifndef BFS_PAIR_FACES
+#define BFS_PAIR_FACES 1 // the halo rows of the three "minus" faces (then of the three "plus" faces) are requested together
+#endif
+#ifndef BFS_PROF
+#define BFS_PROF 0 // experiment builds: 1 / 2 = the phase counters [6], [11], [3], [0] hold four sub-phases of publish / setup instead
+#endif
+#define BFS_MARK(which, field) do { if (BFS_PROF == (which)) { const long long now_ = clock64(); cnt.field += (u64)(now_ - tmark); tmark = now_; } } while (0)
 #ifndef BFS_SLEEP_CAP
 #define BFS_SLEEP_CAP 128 // longest back-off (ns) of a warp polling an empty ring slot (1024 -> 128: -3..6 % at 1536^3)
 #endif
@@ -574,6 +584,51 @@ __device__ __forceinline__ void bfs_face_cand(u32 (&c)[8], const bool dirty, con
     }
 }
 
+// Two faces at once (a y face FA and a z face FB on the same side): the halo / own rows of both are requested before
+// either is used.
+template <int FA, int FB>
+__device__ __forceinline__ void bfs_face_cand2(u32 (&ca)[8], u32 (&cb)[8], const bool da, const bool db,
+                                               const u32 *hrowA, const u32 *orowA, const size_t stepA,
+                                               const u32 *hrowB, const u32 *orowB, const size_t stepB, const bool peerB,
+                                               const bool inx, const bool touched,
+                                               const u32 fa_lo, const u32 fa_hi, const u32 fb_lo, const u32 fb_hi) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ca[i] = cb[i] = BFS_CINV;
+    if (!(da || db)) return;
+    u32 ha[8], hb[8], oa[8], ob[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        ha[i] = (da && inx) ? __ldcg(hrowA + (size_t)i * stepA) : BFS_RAWINF;
+        hb[i] = (db && inx) ? (peerB ? bfs_ld_peer(hrowB + (size_t)i * stepB) : __ldcg(hrowB + (size_t)i * stepB)) : BFS_RAWINF;
+    }
+    if (touched) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            oa[i] = (da && inx) ? __ldcg(orowA + (size_t)i * stepA) : BFS_RAWINF;
+            ob[i] = (db && inx) ? __ldcg(orowB + (size_t)i * stepB) : BFS_RAWINF;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) oa[i] = ob[i] = BFS_RAWINF;
+    }
+    if (da) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const u32 cv = (ha[i] >> 1) + 1u;
+            const u32 sh = (u32)((i & 3) * 8) + (FA ? 7u : 0u);
+            if ((((i < 4 ? fa_lo : fa_hi) >> sh) & 1u) && cv < (oa[i] >> 1)) ca[i] = cv;
+        }
+    }
+    if (db) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const u32 cv = (hb[i] >> 1) + 1u;
+            const u32 sh = (u32)i + (FB == 3 ? 24u : 0u);
+            if ((((i < 4 ? fb_lo : fb_hi) >> sh) & 1u) && cv < (ob[i] >> 1)) cb[i] = cv;
+        }
+    }
+}
+
 // The eight candidates of one y / z face (face F: 0 = y-, 1 = y+, 2 = z-, 3 = z+; index = z for y faces, y for z
 // faces) -> seed planes.  Packed as bytes: level relative to the base, saturated at 0x80 (= no candidate); a byte
 // with bit 6 set is a candidate beyond the seed planes (`farw` collects the bytes).
@@ -629,6 +684,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     const bool peer_lo = MULTI && bz == 0 && A.lo.g != nullptr, peer_hi = MULTI && bz == A.nbz - 1 && A.hi.g != nullptr;
 
     const long long tc0 = clock64();
+    long long tmark = tc0;
     if (Gd.ready && !cnt.all_up) cnt.all_up = bfs_wait_planes(A, z0 - 1, z0 + 8, lane) ? 1u : 0u; // occupancy still uploading (e2e overlap)
     // ---- occupancy words (read-only during a search): issued before the claim so that their
     // latency overlaps the claim's round trip ----
@@ -659,7 +715,8 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     old = __shfl_sync(BFS_FULL, old, 0);
     // acquire: the neighbours' rows written before they set our dirty bits (system scope where a
     // neighbour is another GPU)
-    if (peer_lo || peer_hi) __threadfence_system(); else bfs_fence();
+    if (peer_lo || peer_hi) __threadfence_system(); else if (BFS_CLAIM_FENCE) bfs_fence();
+    BFS_MARK(2, c_setup); // occupancy loads issued, claim, fence
     const u32 dirty = old & BFS_DIRTY;
     bool touched = (old & BFS_T) != 0u;
     if (MULTI && cnt.act == 0 && lane == 0 && A.stats && !__ldcg(&A.stats[18])) // [18]: when this rank started its first activation
@@ -681,22 +738,54 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         xpf0 = __ballot_sync(BFS_FULL, !(xb0 & 1u)); xpf1 = __ballot_sync(BFS_FULL, !(xb1 & 1u));
     }
 
+    BFS_MARK(2, c_sweep); // transposes, face masks
     // ---- candidates across the dirty faces: halo + 1 where it beats the own boundary value ----
     // Face 0 = y-, 1 = y+, 2 = z-, 3 = z+ (dirty bit 4 << f); a clean face costs one uniform branch.
     u32 cYm[8], cYp[8], cZm[8], cZp[8], cXm[2], cXp[2];
     cXm[0] = cXm[1] = cXp[0] = cXp[1] = BFS_CINV;
+    u32 *colrow = A.g + (size_t)(z0 + lzq) * sZ + (size_t)(y0 + ly) * sY + (size_t)x0; // x faces, row-distributed: cells (y = ly, z = lzq + 4w)
     {
         // halo rows: the neighbour's boundary rows (on the lowest / highest tile row of a slab the peer GPU's)
         const u32 *zlo = peer_lo ? A.lo.g + (size_t)A.lo.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 - sZ;
         const u32 *zhi = peer_hi ? A.hi.g + (size_t)A.hi.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 + 8 * sZ;
+#if BFS_PAIR_FACES
+        // A wave usually enters through the faces of one corner (x-, y-, z- far from the source's corner, ...):
+        // the halo words of the three "minus" faces are requested before the first is used, then those of the
+        // three "plus" faces -- one L2 round trip per group instead of one per dirty face.
+        u32 xh[2][2], xo[2][2];
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+            xh[0][w] = (dirty & 1u) ? __ldcg(colrow + (size_t)(4 * w) * sZ - 1) : BFS_RAWINF;
+            xo[0][w] = ((dirty & 1u) && touched) ? __ldcg(colrow + (size_t)(4 * w) * sZ) : BFS_RAWINF;
+        }
+        bfs_face_cand2<0, 2>(cYm, cZm, (dirty & 4u) != 0u, (dirty & 16u) != 0u, cell0 - sY, cell0, sZ, zlo, cell0, sY, peer_lo, inx, touched,
+                             free0, free1, free0, free0);
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+            xh[1][w] = (dirty & 2u) ? __ldcg(colrow + (size_t)(4 * w) * sZ + 32) : BFS_RAWINF;
+            xo[1][w] = ((dirty & 2u) && touched) ? __ldcg(colrow + (size_t)(4 * w) * sZ + 31) : BFS_RAWINF;
+        }
+        bfs_face_cand2<1, 3>(cYp, cZp, (dirty & 8u) != 0u, (dirty & 32u) != 0u, cell0 + 8 * sY, cell0 + 7 * sY, sZ, zhi, cell0 + 7 * sZ, sY, peer_hi,
+                             inx, touched, free0, free1, free1, free1);
+        if (dirty & 3u) { // x-: halo column x0 - 1, own column x0 (lane 0's cells); x+: x0 + 32 / x0 + 31 (lane 31's)
+            const u32 fm0 = __shfl_sync(BFS_FULL, free0, 0), fm1 = __shfl_sync(BFS_FULL, free1, 0);
+            const u32 fp0 = __shfl_sync(BFS_FULL, free0, 31), fp1 = __shfl_sync(BFS_FULL, free1, 31);
+#pragma unroll
+            for (int w = 0; w < 2; ++w) {
+                const u32 cm = (xh[0][w] >> 1) + 1u, cp = (xh[1][w] >> 1) + 1u;
+                if ((((w ? fm1 : fm0) >> lane) & 1u) && cm < (xo[0][w] >> 1)) cXm[w] = cm;
+                if ((((w ? fp1 : fp0) >> lane) & 1u) && cp < (xo[1][w] >> 1)) cXp[w] = cp;
+            }
+        }
+#else
         bfs_face_cand<0>(cYm, (dirty & 4u) != 0u, cell0 - sY, cell0, sZ, false, inx, touched, free0, free1);
         bfs_face_cand<1>(cYp, (dirty & 8u) != 0u, cell0 + 8 * sY, cell0 + 7 * sY, sZ, false, inx, touched, free0, free1);
         bfs_face_cand<2>(cZm, (dirty & 16u) != 0u, zlo, cell0, sY, peer_lo, inx, touched, free0, free0);
         bfs_face_cand<3>(cZp, (dirty & 32u) != 0u, zhi, cell0 + 7 * sZ, sY, peer_hi, inx, touched, free1, free1);
+#endif
         if (MULTI) cnt.peer_rows += (((dirty & 16u) && peer_lo) ? 8u : 0u) + (((dirty & 32u) && peer_hi) ? 8u : 0u);
     }
-    // x faces, row-distributed: this lane looks at the cells (y = ly, z = lzq + 4w)
-    u32 *colrow = A.g + (size_t)(z0 + lzq) * sZ + (size_t)(y0 + ly) * sY + (size_t)x0;
+#if !BFS_PAIR_FACES
     if (dirty & 1u) { // x-: halo column x0 - 1, own column x0 (lane 0's cells)
         const u32 fw0 = __shfl_sync(BFS_FULL, free0, 0), fw1 = __shfl_sync(BFS_FULL, free1, 0);
 #pragma unroll
@@ -717,6 +806,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
             cXp[w] = (fr && c != BFS_CINV && c < (o >> 1)) ? c : BFS_CINV;
         }
     }
+#endif
     // corner cells of the y / z faces have two candidates: keep the smaller one in the y array
     {
         u32 m;
@@ -735,6 +825,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         if (lane == sx) { if (sz < 4) init0 = 1u << (sz * 8 + sy); else init1 = 1u << ((sz - 4) * 8 + sy); }
     }
 
+    BFS_MARK(2, c_extract); // candidates of all faces
     // ---- pass base = smallest candidate; the largest one bounds the last seed level ----
     // (an absent candidate is all-ones: the largest unsigned and, read as signed, the smallest value)
     u32 base;
@@ -799,7 +890,8 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         }
 
     }
-    cnt.c_setup += (u64)(clock64() - tc0);
+    BFS_MARK(2, c_publish); // base + seed planes
+    if (!BFS_PROF) cnt.c_setup += (u64)(clock64() - tc0);
 
     // ---- sweep, extract, store; continuation passes if a wave outlives the recordable range ----
     // (BFS_PHASE_SYNC: in the phase-locked kernel all warps of the CTA enter each phase together, so
@@ -832,12 +924,12 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     }
     if (active) cnt.lowered += (u32)(__popc(low0) + __popc(low1));
     else ++cnt.idle;
-    cnt.c_sweep += (u64)tsw;
-    cnt.c_extract += (u64)(clock64() - tc1 - tsw);
+    if (!BFS_PROF) { cnt.c_sweep += (u64)tsw; cnt.c_extract += (u64)(clock64() - tc1 - tsw); }
     if (SYNC && (BFS_SYNC_MASK & 4)) { BFS_PHASE_SYNC(); }
 
     // ---- publish: every store above is visible before a neighbour is armed ----
     const long long tc3 = clock64();
+    tmark = tc3;
     if (peer_lo || peer_hi) __threadfence_system(); else bfs_fence();
     __syncwarp();
     // Which neighbours can use what this activation lowered?  Across a face that was NOT read in
@@ -846,6 +938,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     // the neighbour's current value by more than the step, checked against the neighbour's
     // boundary cells (re-read: they can only have become smaller, so "no" stays "no").  Without
     // this every tile would re-activate its upstream neighbours for nothing.
+    BFS_MARK(1, c_setup); // fence
     u32 arms = 0;
     {
         // x faces, row-distributed: this lane looks at the cells (y = ly, z = lzq + 4w) of lane 0 / 31
@@ -908,6 +1001,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         }
     }
 
+    BFS_MARK(1, c_sweep); // arming checks
     // sequence number of everything this activation queues: the entries pushed so far on all ranks
     u32 seq_out = 0;
     if (MULTI && A.pace_window) {
@@ -957,6 +1051,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         }
     }
     const u32 pushes = __ballot_sync(BFS_FULL, need_push || requeue);
+    BFS_MARK(1, c_extract); // arming atomics + release
     const int np = __popc(pushes);
     if (np >= 2) {
         if (lane == 0) { atomicAdd(&A.ctr[BFS_C_INFLIGHT], (u32)(np - 1)); bfs_fence(); }
@@ -971,7 +1066,8 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         if (atomicSub(&A.ctr[BFS_C_INFLIGHT], 1u) == 1u) bfs_rank_idle(A);
     }
     __syncwarp();
-    cnt.c_publish += (u64)(clock64() - tc3);
+    BFS_MARK(1, c_publish); // pushes
+    if (!BFS_PROF) cnt.c_publish += (u64)(clock64() - tc3);
     // [16]: when this rank finished its last activation (its busy span = [16] - [9]; the kernel itself runs
     // until the LAST rank is done)
     if (MULTI && lane == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[16], (unsigned long long)bfs_now_ns());
