@@ -67,9 +67,6 @@
 #ifndef BFS_PHASE_SYNC
 #define BFS_PHASE_SYNC()
 #endif
-#ifndef BFS_VOTE_EACH
-#define BFS_VOTE_EACH 0 // 1: the sweep asks after every level whether the wave has died out (0: once per block of levels)
-#endif
 #ifndef BFS_CLAIM_FENCE
 #define BFS_CLAIM_FENCE 1 // experiment: 0 = no fence between the claim and the halo loads (single GPU)
 #endif
@@ -167,6 +164,9 @@ static inline u32 bfs_ld_acquire_sys(const u32 *p) { return *(const volatile u32
 static inline u32 bfs_byte_sign(u32 v, int k) { return ((v >> (8 * k)) & 0x80u) ? 0xFFFFFFFFu : 0u; }
 #endif
 
+// the 64-bit value hi:lo shifted right / left by s (0 < s < 32): its low / high word
+__device__ __forceinline__ u32 bfs_funnel_r(u32 lo, u32 hi, int s) { return (lo >> s) | (hi << (32 - s)); }
+__device__ __forceinline__ u32 bfs_funnel_l(u32 lo, u32 hi, int s) { return (hi << s) | (lo >> (32 - s)); }
 __device__ __forceinline__ u32 bfs_spread4(u32 n) { return ((n & 0xFu) * 0x00204081u) & 0x01010101u; }
 __device__ __forceinline__ u32 bfs_compress4(u32 x) { return (((x & 0x01010101u) * 0x01020408u) >> 24) & 0xFu; }
 
@@ -393,6 +393,77 @@ struct BfsSeeds {
     int last; // largest seed level (uniform), -1: none
 };
 
+// one block of BFS_UB levels starting at level rb.  (A second copy without the seed injection for the blocks beyond
+// the last seed level was slower: +0.6 ms at 1536^3 -- code size.)
+__device__ __forceinline__ void bfs_sweep_block(const int rb, const u32 free0, const u32 free1, const BfsSeeds &SA, const BfsSeeds &SB,
+                                                u32 &c0, u32 &c1, u32 &R0, u32 &R1, u32 (&rec)[BFS_NREC][2]) {
+    // seeds of this block: the high bits of their level equal those of rb
+    u32 ha0 = 0, ha1 = 0, hb0 = 0, hb1 = 0;
+    const bool useA = rb <= SA.last, useB = rb <= SB.last;
+    if (useA) {
+        ha0 = SA.sv[0]; ha1 = SA.sv[1];
+#pragma unroll
+        for (int b = BFS_LB; b < 6; ++b) {
+            const u32 flip = ((rb >> b) & 1) ? 0u : BFS_FULL;
+            ha0 &= SA.sp[b][0] ^ flip;
+            ha1 &= SA.sp[b][1] ^ flip;
+        }
+    }
+    if (useB) {
+        hb0 = SB.sv[0]; hb1 = SB.sv[1];
+#pragma unroll
+        for (int b = BFS_LB; b < 6; ++b) {
+            const u32 flip = ((rb >> b) & 1) ? 0u : BFS_FULL;
+            hb0 &= SB.sp[b][0] ^ flip;
+            hb1 &= SB.sp[b][1] ^ flip;
+        }
+    }
+    const u32 rb0 = R0, rb1 = R1; // reached before this block
+#pragma unroll
+    for (int k = 0; k < BFS_UB; ++k) {
+        u32 f0 = c0, f1 = c1;
+        if (useA) {
+            u32 m0 = ha0, m1 = ha1;
+#pragma unroll
+            for (int b = 0; b < BFS_LB; ++b) {
+                m0 &= ((k >> b) & 1) ? SA.sp[b][0] : ~SA.sp[b][0];
+                m1 &= ((k >> b) & 1) ? SA.sp[b][1] : ~SA.sp[b][1];
+            }
+            f0 |= m0 & ~R0;
+            f1 |= m1 & ~R1;
+        }
+        if (useB) {
+            u32 m0 = hb0, m1 = hb1;
+#pragma unroll
+            for (int b = 0; b < BFS_LB; ++b) {
+                m0 &= ((k >> b) & 1) ? SB.sp[b][0] : ~SB.sp[b][0];
+                m1 &= ((k >> b) & 1) ? SB.sp[b][1] : ~SB.sp[b][1];
+            }
+            f0 |= m0 & ~R0;
+            f1 |= m1 & ~R1;
+        }
+        R0 |= f0; R1 |= f1;
+#pragma unroll
+        for (int b = 0; b < BFS_LB; ++b)
+            if ((k >> b) & 1) { rec[b][0] |= f0; rec[b][1] |= f1; }
+        // neighbours of the frontier: y +- 1 inside a byte, z +- 1 = byte shifts across the two
+        // words, x +- 1 = the adjacent lanes
+        u32 n0 = ((f0 << 1) & 0xFEFEFEFEu) | ((f0 >> 1) & 0x7F7F7F7Fu) | (f0 << 8) | bfs_funnel_r(f0, f1, 8);
+        u32 n1 = ((f1 << 1) & 0xFEFEFEFEu) | ((f1 >> 1) & 0x7F7F7F7Fu) | (f1 >> 8) | bfs_funnel_l(f0, f1, 8);
+        const u32 u0 = __shfl_up_sync(BFS_FULL, f0, 1), u1 = __shfl_up_sync(BFS_FULL, f1, 1);
+        const u32 d0 = __shfl_down_sync(BFS_FULL, f0, 1), d1 = __shfl_down_sync(BFS_FULL, f1, 1);
+        // (lane 0 / 31 get their own word back from the shuffle: those cells are in R already)
+        n0 |= u0 | d0;
+        n1 |= u1 | d1;
+        c0 = n0 & free0 & ~R0;
+        c1 = n1 & free1 & ~R1;
+    }
+    const u32 bf0 = R0 & ~rb0, bf1 = R1 & ~rb1; // cells that got a level inside this block
+#pragma unroll
+    for (int b = BFS_LB; b < BFS_NREC; ++b)
+        if ((rb >> b) & 1) { rec[b][0] |= bf0; rec[b][1] |= bf1; }
+}
+
 __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const BfsSeeds &SA, const BfsSeeds &SB,
                                          const u32 init0, const u32 init1, u32 &R0, u32 &R1, u32 (&rec)[BFS_NREC][2],
                                          u32 &carry0, u32 &carry1, const int lane) {
@@ -403,80 +474,11 @@ __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const
     u32 nlev = 0;
     bool fin = false;
     for (int rb = 0; rb < BFS_LIM && !fin; rb += BFS_UB) {
-        // seeds of this block of BFS_UB levels: the high bits of their level equal those of rb
-        u32 ha0 = 0, ha1 = 0, hb0 = 0, hb1 = 0;
-        const bool useA = rb <= SA.last, useB = rb <= SB.last;
-        if (useA) {
-            ha0 = SA.sv[0]; ha1 = SA.sv[1];
-#pragma unroll
-            for (int b = BFS_LB; b < 6; ++b) {
-                const u32 flip = ((rb >> b) & 1) ? 0u : BFS_FULL;
-                ha0 &= SA.sp[b][0] ^ flip;
-                ha1 &= SA.sp[b][1] ^ flip;
-            }
-        }
-        if (useB) {
-            hb0 = SB.sv[0]; hb1 = SB.sv[1];
-#pragma unroll
-            for (int b = BFS_LB; b < 6; ++b) {
-                const u32 flip = ((rb >> b) & 1) ? 0u : BFS_FULL;
-                hb0 &= SB.sp[b][0] ^ flip;
-                hb1 &= SB.sp[b][1] ^ flip;
-            }
-        }
-        u32 bf0 = 0, bf1 = 0; // cells that got a level inside this block
-#pragma unroll
-        for (int k = 0; k < BFS_UB; ++k) {
-            u32 f0 = c0, f1 = c1;
-            if (useA) {
-                u32 m0 = ha0, m1 = ha1;
-#pragma unroll
-                for (int b = 0; b < BFS_LB; ++b) {
-                    m0 &= ((k >> b) & 1) ? SA.sp[b][0] : ~SA.sp[b][0];
-                    m1 &= ((k >> b) & 1) ? SA.sp[b][1] : ~SA.sp[b][1];
-                }
-                f0 |= m0 & ~R0;
-                f1 |= m1 & ~R1;
-            }
-            if (useB) {
-                u32 m0 = hb0, m1 = hb1;
-#pragma unroll
-                for (int b = 0; b < BFS_LB; ++b) {
-                    m0 &= ((k >> b) & 1) ? SB.sp[b][0] : ~SB.sp[b][0];
-                    m1 &= ((k >> b) & 1) ? SB.sp[b][1] : ~SB.sp[b][1];
-                }
-                f0 |= m0 & ~R0;
-                f1 |= m1 & ~R1;
-            }
-            R0 |= f0; R1 |= f1;
-            bf0 |= f0; bf1 |= f1;
-#pragma unroll
-            for (int b = 0; b < BFS_LB; ++b)
-                if ((k >> b) & 1) { rec[b][0] |= f0; rec[b][1] |= f1; }
-            // neighbours of the frontier: y +- 1 inside a byte, z +- 1 = byte shifts across the two
-            // words, x +- 1 = the adjacent lanes
-            u32 n0 = ((f0 << 1) & 0xFEFEFEFEu) | ((f0 >> 1) & 0x7F7F7F7Fu) | (f0 << 8) | (f0 >> 8) | (f1 << 24);
-            u32 n1 = ((f1 << 1) & 0xFEFEFEFEu) | ((f1 >> 1) & 0x7F7F7F7Fu) | (f1 << 8) | (f1 >> 8) | (f0 >> 24);
-            const u32 u0 = __shfl_up_sync(BFS_FULL, f0, 1), u1 = __shfl_up_sync(BFS_FULL, f1, 1);
-            const u32 d0 = __shfl_down_sync(BFS_FULL, f0, 1), d1 = __shfl_down_sync(BFS_FULL, f1, 1);
-            // (lane 0 / 31 get their own word back from the shuffle: those cells are in R already)
-            n0 |= u0 | d0;
-            n1 |= u1 | d1;
-            c0 = n0 & free0 & ~R0;
-            c1 = n1 & free1 & ~R1;
-            ++nlev;
-#if BFS_VOTE_EACH
-            if (rb + k >= last && !__any_sync(BFS_FULL, (c0 | c1) != 0u)) { fin = true; break; }
-#endif
-        }
-#if !BFS_VOTE_EACH
+        bfs_sweep_block(rb, free0, free1, SA, SB, c0, c1, R0, R1, rec);
+        nlev += BFS_UB;
         // the wave has died out (and no seed is left): asked once per block of levels -- a vote per level costs more
         // than the up to BFS_UB - 1 empty levels swept past the end
         if (rb + BFS_UB - 1 >= last && !__any_sync(BFS_FULL, (c0 | c1) != 0u)) fin = true;
-#endif
-#pragma unroll
-        for (int b = BFS_LB; b < BFS_NREC; ++b)
-            if ((rb >> b) & 1) { rec[b][0] |= bf0; rec[b][1] |= bf1; }
     }
     carry0 = fin ? 0u : c0;
     carry1 = fin ? 0u : c1;
