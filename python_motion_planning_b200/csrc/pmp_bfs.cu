@@ -136,11 +136,19 @@ struct BfsLayout {
 
 static size_t bfs_align(size_t v) { return (v + 255) / 256 * 256; }
 
-static BfsLayout bfs_layout(const pmp_grid *g) {
+// ring capacity: tiles + slack, rounded up to a power of two where the caller's memory allows it (slot = ticket &
+// (cap - 1) instead of a 32-bit division on every poll of every warp); the static-workspace entry keeps the exact size
+static u32 bfs_ring_cap(u32 ntiles, bool pow2) {
+    u32 cap = ntiles + BFS_RING_SLACK;
+    if (pow2) { u32 p = 1u; while (p < cap) p <<= 1; cap = p; }
+    return cap;
+}
+
+static BfsLayout bfs_layout(const pmp_grid *g, bool pow2 = true) {
     BfsLayout L;
     L.nbx = g->d.wpr; L.nby = g->d.PY / 8; L.nbz = g->d.PZ / 8;
     L.ntiles = (u32)((size_t)L.nbx * L.nby * L.nbz);
-    L.ring_cap = L.ntiles + BFS_RING_SLACK;
+    L.ring_cap = bfs_ring_cap(L.ntiles, pow2);
     size_t o = 0;
     L.state = o; o = bfs_align(o + (size_t)L.ntiles * 4);
     L.ring = o; o = bfs_align(o + (size_t)L.ring_cap * 8);
@@ -323,7 +331,7 @@ extern "C" int pmp_cost_field_u32_static(pmp_grid *g, const int32_t *start_dev, 
     PMP_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev != g->device) { pmp_set_error("pmp_cost_field_u32_static: the grid lives on device %d, current device is %d", g->device, dev); return -1; }
     if (pmp_grid_upload_fence(g, (cudaStream_t)stream)) return -2;
-    const BfsLayout L = bfs_layout(g);
+    const BfsLayout L = bfs_layout(g, false);
     if (L.total > (size_t)PMP_STATIC_WS_BYTES) {
         pmp_set_error("pmp_cost_field_u32_static: grid of %u tiles needs %zu B of workspace, the static array holds %u B "
                       "(use pmp_sssp with caller memory)", L.ntiles, L.total, PMP_STATIC_WS_BYTES);
@@ -376,7 +384,7 @@ static BfsLayout bfs_layout_tiles(int nbx, int nby, int nbz) {
     BfsLayout L;
     L.nbx = nbx; L.nby = nby; L.nbz = nbz;
     L.ntiles = (u32)((size_t)nbx * nby * nbz);
-    L.ring_cap = L.ntiles + BFS_RING_SLACK;
+    L.ring_cap = bfs_ring_cap(L.ntiles, true);
     size_t o = 0;
     L.state = o; o = bfs_align(o + (size_t)L.ntiles * 4);
     L.ring = o; o = bfs_align(o + (size_t)L.ring_cap * 8);

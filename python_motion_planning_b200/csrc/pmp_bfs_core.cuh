@@ -206,9 +206,12 @@ __device__ __forceinline__ void bfs_transpose8(u32 &lo, u32 &hi) {
 }
 
 // ---- ring ------------------------------------------------------------------------------------
+// slot of a ticket: the capacity is a power of two wherever the host sized the ring itself (a mask instead of a
+// 32-bit division on every poll); any capacity works
+__device__ __forceinline__ u32 bfs_ring_slot(u32 ticket, u32 cap) { return (cap & (cap - 1u)) == 0u ? (ticket & (cap - 1u)) : ticket % cap; }
 __device__ static inline void bfs_push(u64 *ring, u32 cap, u32 *ctr, u32 tile, u32 level) {
     const u32 ticket = atomicAdd(&ctr[BFS_C_TAIL], 1u);
-    *(volatile u64 *)&ring[ticket % cap] = ((u64)level << 32) | (u64)(tile + 1u);
+    *(volatile u64 *)&ring[bfs_ring_slot(ticket, cap)] = ((u64)level << 32) | (u64)(tile + 1u);
 }
 
 // ---- multi-GPU: one FIFO served by all GPUs --------------------------------------------------------
@@ -313,7 +316,7 @@ __device__ static inline u64 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int
                 }
             }
             const u32 idx = P.ticket - 31u + (u32)lane; // lane 31: my own slot
-            u64 *slot = &A.ring[idx % A.ring_cap];
+            u64 *slot = &A.ring[bfs_ring_slot(idx, A.ring_cap)];
             const u64 v = (int)idx >= 0 ? __ldcg(slot) : 0ull;
             const u32 own_lo = __shfl_sync(BFS_FULL, (u32)v, 31), own_hi = __shfl_sync(BFS_FULL, (u32)(v >> 32), 31);
             if ((own_lo & own_hi) == 0xFFFFFFFFu) { // my item went to another warp: clear the slot, draw a new ticket
@@ -382,8 +385,8 @@ __device__ __noinline__ static void bfs_rank_idle(const BfsArgs &A) {
 
 // ---- the sweep ---------------------------------------------------------------------------------
 // Multi-source BFS on the tile's bit lanes.  Seeds are given bit-sliced (6 planes: level relative
-// to the pass base, valid mask sv) in two sets: A (y / z faces, every lane) and B (x faces, lanes
-// 0 and 31); `init` cells start at level 0; `R` enters as the cells that must not be entered
+// to the pass base, valid mask sv; the candidates of all six faces merged, the smaller level where an
+// edge cell has two); `init` cells start at level 0; `R` enters as the cells that must not be entered
 // (blocked by an earlier pass) and returns with the cells reached added.  Levels are recorded
 // bit-sliced in rec[7][2].  Returns in `carry` the cells that would get level BFS_LIM (0 if the
 // wave died out), and the number of levels swept.
@@ -395,11 +398,11 @@ struct BfsSeeds {
 
 // one block of BFS_UB levels starting at level rb.  (A second copy without the seed injection for the blocks beyond
 // the last seed level was slower: +0.6 ms at 1536^3 -- code size.)
-__device__ __forceinline__ void bfs_sweep_block(const int rb, const u32 free0, const u32 free1, const BfsSeeds &SA, const BfsSeeds &SB,
+__device__ __forceinline__ void bfs_sweep_block(const int rb, const u32 free0, const u32 free1, const BfsSeeds &SA,
                                                 u32 &c0, u32 &c1, u32 &R0, u32 &R1, u32 (&rec)[BFS_NREC][2]) {
     // seeds of this block: the high bits of their level equal those of rb
-    u32 ha0 = 0, ha1 = 0, hb0 = 0, hb1 = 0;
-    const bool useA = rb <= SA.last, useB = rb <= SB.last;
+    u32 ha0 = 0, ha1 = 0;
+    const bool useA = rb <= SA.last;
     if (useA) {
         ha0 = SA.sv[0]; ha1 = SA.sv[1];
 #pragma unroll
@@ -407,15 +410,6 @@ __device__ __forceinline__ void bfs_sweep_block(const int rb, const u32 free0, c
             const u32 flip = ((rb >> b) & 1) ? 0u : BFS_FULL;
             ha0 &= SA.sp[b][0] ^ flip;
             ha1 &= SA.sp[b][1] ^ flip;
-        }
-    }
-    if (useB) {
-        hb0 = SB.sv[0]; hb1 = SB.sv[1];
-#pragma unroll
-        for (int b = BFS_LB; b < 6; ++b) {
-            const u32 flip = ((rb >> b) & 1) ? 0u : BFS_FULL;
-            hb0 &= SB.sp[b][0] ^ flip;
-            hb1 &= SB.sp[b][1] ^ flip;
         }
     }
     const u32 rb0 = R0, rb1 = R1; // reached before this block
@@ -428,16 +422,6 @@ __device__ __forceinline__ void bfs_sweep_block(const int rb, const u32 free0, c
             for (int b = 0; b < BFS_LB; ++b) {
                 m0 &= ((k >> b) & 1) ? SA.sp[b][0] : ~SA.sp[b][0];
                 m1 &= ((k >> b) & 1) ? SA.sp[b][1] : ~SA.sp[b][1];
-            }
-            f0 |= m0 & ~R0;
-            f1 |= m1 & ~R1;
-        }
-        if (useB) {
-            u32 m0 = hb0, m1 = hb1;
-#pragma unroll
-            for (int b = 0; b < BFS_LB; ++b) {
-                m0 &= ((k >> b) & 1) ? SB.sp[b][0] : ~SB.sp[b][0];
-                m1 &= ((k >> b) & 1) ? SB.sp[b][1] : ~SB.sp[b][1];
             }
             f0 |= m0 & ~R0;
             f1 |= m1 & ~R1;
@@ -464,17 +448,17 @@ __device__ __forceinline__ void bfs_sweep_block(const int rb, const u32 free0, c
         if ((rb >> b) & 1) { rec[b][0] |= bf0; rec[b][1] |= bf1; }
 }
 
-__device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const BfsSeeds &SA, const BfsSeeds &SB,
+__device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const BfsSeeds &SA,
                                          const u32 init0, const u32 init1, u32 &R0, u32 &R1, u32 (&rec)[BFS_NREC][2],
                                          u32 &carry0, u32 &carry1, const int lane) {
 #pragma unroll
     for (int b = 0; b < BFS_NREC; ++b) rec[b][0] = rec[b][1] = 0u;
     u32 c0 = init0, c1 = init1;
-    const int last = SA.last > SB.last ? SA.last : SB.last;
+    const int last = SA.last;
     u32 nlev = 0;
     bool fin = false;
     for (int rb = 0; rb < BFS_LIM && !fin; rb += BFS_UB) {
-        bfs_sweep_block(rb, free0, free1, SA, SB, c0, c1, R0, R1, rec);
+        bfs_sweep_block(rb, free0, free1, SA, c0, c1, R0, R1, rec);
         nlev += BFS_UB;
         // the wave has died out (and no seed is left): asked once per block of levels -- a vote per level costs more
         // than the up to BFS_UB - 1 empty levels swept past the end
@@ -501,12 +485,13 @@ __device__ __forceinline__ u32 bfs_extract8(const u32 r0, const u32 r1, const u3
     const u32 nb = (Nw >> (zb * 8u)) & 0xFFu; // cells of this group reached in this pass
     u32 low = 0;
     u32 *p = pz;
+    const u32 lo2 = (lo << 1) & 0xFEFEFEFEu, hi2 = (hi << 1) & 0xFEFEFEFEu; // the level bytes doubled (one shift per four cells)
 #pragma unroll
     for (int y = 0; y < 8; ++y) {
         const u32 src = y < 4 ? lo : hi;
-        const u32 lv = __byte_perm(src, 0u, 0x4440u | (u32)(y & 3));
+        const u32 lv2 = __byte_perm(y < 4 ? lo2 : hi2, 0u, 0x4440u | (u32)(y & 3));
         // a cell that was not reached has bit 7 of its byte set -> an all-ones word ("unreached")
-        const u32 word = bfs_byte_sign(src, y & 3) | (base2 + (lv << 1));
+        const u32 word = bfs_byte_sign(src, y & 3) | (base2 + lv2);
         if (TOUCHED) {
             // min-merge: only reached cells can be lower (they are free cells, hence inside the row)
             if ((nb >> y) & 1u) {
@@ -850,11 +835,11 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     u32 low0 = 0, low1 = 0; // cells lowered by this activation
     u32 redo = 0;           // dirty faces to look at again (seeds beyond the range of one pass)
     const bool active = base != BFS_CINV; // uniform: something to sweep from
-    BfsSeeds SA, SB;
+    BfsSeeds SA;
 #pragma unroll
-    for (int b = 0; b < 6; ++b) SA.sp[b][0] = SA.sp[b][1] = SB.sp[b][0] = SB.sp[b][1] = 0u;
-    SA.sv[0] = SA.sv[1] = SB.sv[0] = SB.sv[1] = 0u;
-    SA.last = SB.last = -1;
+    for (int b = 0; b < 6; ++b) SA.sp[b][0] = SA.sp[b][1] = 0u;
+    SA.sv[0] = SA.sv[1] = 0u;
+    SA.last = -1;
     if (active) {
         // ---- bit-sliced seed levels ----
         // y / z faces: the eight candidates of a face become eight bytes (level relative to the base; 0x40..0x7F: beyond
@@ -866,28 +851,44 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         bfs_seed_face<2>(cZm, base, SA, farw);
         bfs_seed_face<3>(cZp, base, SA, farw);
         u32 far = farw & 0x40404040u, lastB = 0, anyB = 0;
-        // x faces: the ballots assemble lane 0's (x-) and lane 31's (x+) words
+        const bool anyA = __any_sync(BFS_FULL, (SA.sv[0] | SA.sv[1]) != 0u); // any y / z seed within the planes
+        // x faces: the ballots assemble lane 0's (x-) and lane 31's (x+) words, which are then merged into the same
+        // planes.  An edge cell of those two columns can have a candidate from either side: the smaller level stays
+        // (a bit-sliced compare, run only when there are x candidates at all) -- one seed set for the sweep.
 #pragma unroll
         for (int w = 0; w < 2; ++w) {
             const u32 rm = bfs_rel(cXm[w], base, far, anyB, lastB), rp = bfs_rel(cXp[w], base, far, anyB, lastB);
             const bool any_x = __any_sync(BFS_FULL, (rm & rp & 0x80u) == 0u);
             if (any_x) {
                 const u32 vm = __ballot_sync(BFS_FULL, !(rm & 0x80u)), vp = __ballot_sync(BFS_FULL, !(rp & 0x80u));
-                SB.sv[w] = lane == 0 ? vm : (lane == 31 ? vp : 0u);
+                const u32 vb = lane == 0 ? vm : (lane == 31 ? vp : 0u);
+                u32 xb[6];
 #pragma unroll
                 for (int b = 0; b < 6; ++b) {
                     const u32 bm = __ballot_sync(BFS_FULL, (rm >> b) & 1u & ~(rm >> 7)), bp = __ballot_sync(BFS_FULL, (rp >> b) & 1u & ~(rp >> 7));
-                    SB.sp[b][w] = lane == 0 ? bm : (lane == 31 ? bp : 0u);
+                    xb[b] = lane == 0 ? bm : (lane == 31 ? bp : 0u);
                 }
+                const u32 both = SA.sv[w] & vb;
+                u32 lt = 0u, eq = both; // cells where the y / z candidate is below / equal to the x candidate so far (from the top bit down)
+#pragma unroll
+                for (int b = 5; b >= 0; --b) {
+                    lt |= eq & ~SA.sp[b][w] & xb[b];
+                    eq &= ~(SA.sp[b][w] ^ xb[b]);
+                }
+                const u32 take = vb & ~(lt | eq); // the x candidate wins: alone, or strictly smaller
+#pragma unroll
+                for (int b = 0; b < 6; ++b) SA.sp[b][w] = (SA.sp[b][w] & ~take) | (xb[b] & take);
+                SA.sv[w] |= vb;
             }
         }
         {
-            // last seed level of the y / z faces: exact unless some candidate lies beyond the planes (then 63, a bound)
+            // last seed level: exact unless some y / z candidate lies beyond the planes (then 63, a bound)
             const int ma = __reduce_max_sync(BFS_FULL, maxA);
             const u32 la = (u32)ma - base;
             const u32 lb = __reduce_max_sync(BFS_FULL, lastB);
-            SA.last = __any_sync(BFS_FULL, (SA.sv[0] | SA.sv[1]) != 0u) ? (int)(la < BFS_SEEDMAX ? la : BFS_SEEDMAX) : -1;
-            SB.last = __any_sync(BFS_FULL, anyB != 0u) ? (int)lb : -1;
+            const int lastA = anyA ? (int)(la < BFS_SEEDMAX ? la : BFS_SEEDMAX) : -1;
+            const int lastX = __any_sync(BFS_FULL, anyB != 0u) ? (int)lb : -1;
+            SA.last = lastA > lastX ? lastA : lastX;
             if (__any_sync(BFS_FULL, far != 0u)) redo = dirty;
         }
 
@@ -911,7 +912,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         const u32 P0 = R0, P1 = R1;
         const long long ta = clock64();
         if (active) {
-            cnt.levels += bfs_sweep(free0, free1, SA, SB, init0, init1, R0, R1, rec, carry0, carry1, lane);
+            cnt.levels += bfs_sweep(free0, free1, SA, init0, init1, R0, R1, rec, carry0, carry1, lane);
             ++cnt.passes;
         }
         tsw += clock64() - ta;
@@ -922,7 +923,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         if (!__any_sync(BFS_FULL, (carry0 | carry1) != 0u)) break;
         init0 = carry0; init1 = carry1;
         pbase += BFS_LIM;
-        SA.last = -1; SB.last = -1;
+        SA.last = -1;
     }
     if (active) cnt.lowered += (u32)(__popc(low0) + __popc(low1));
     else ++cnt.idle;

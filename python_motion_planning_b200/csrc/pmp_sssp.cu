@@ -1124,6 +1124,8 @@ static WsLayout ws_layout(const pmp_grid *g, int64_t nq) {
     return L;
 }
 
+size_t pmp_bfs_ws_bytes(const pmp_grid *g);
+
 extern "C" int pmp_sssp_sizes(const pmp_grid *g, int64_t nq, int weight, int64_t *g_bytes_per_query,
                               int64_t *ws_bytes) {
     if (!g || nq < 1 || (weight != PMP_W_F64 && weight != PMP_W_U32)) {
@@ -1135,7 +1137,14 @@ extern "C" int pmp_sssp_sizes(const pmp_grid *g, int64_t nq, int weight, int64_t
         return -1;
     }
     if (g_bytes_per_query) *g_bytes_per_query = (int64_t)(g->d.pcells * (weight == PMP_W_F64 ? 8 : 4));
-    if (ws_bytes) *ws_bytes = (int64_t)ws_layout(g, nq).total;
+    if (ws_bytes) {
+        size_t need = ws_layout(g, nq).total;
+        if (g->d.ndim == 3 && weight == PMP_W_U32) { // a full unit-weight field is routed to k_bfs, which lays the workspace out itself
+            const size_t b = pmp_bfs_ws_bytes(g);
+            need = b > need ? b : need;
+        }
+        *ws_bytes = (int64_t)need;
+    }
     return 0;
 }
 
