@@ -42,7 +42,7 @@
 #define BFS_NREC 7
 #define BFS_LIM 128      // levels one pass can record (2^BFS_NREC)
 #ifndef BFS_LB
-#define BFS_LB 2      // the level loop is unrolled 2^BFS_LB times (code size vs. static low level bits)
+#define BFS_LB 3      // the level loop is unrolled 2^BFS_LB times (code size vs. static low level bits; 2 -> 3 after the per-block overheads were trimmed: 17.2 -> 16.8 ms)
 #endif
 #define BFS_UB (1 << BFS_LB)
 #define BFS_SEEDMAX 63u  // largest seed level relative to the pass base (6 seed planes)
