@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(BFS_SYNC_NT, BFS_SYNC_MINB) k_bfs(const __grid
     BfsPop P;
     P.ticket = 0; P.have = 0; P.t0 = 0; P.held = 0; P.held_polls = 0;
     for (;;) {
-        const long long tp = clock64();
+        const long long tp = BFS_NOW();
         bool done = false;
         const u64 item = bfs_pop_warp<MULTI>(A, P, lane, BFS_TRY_POLLS, done);
         if (!__syncthreads_or(item != 0ull)) {          // nobody in the CTA has work
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(BFS_SYNC_NT, BFS_SYNC_MINB) k_bfs(const __grid
             continue;
         }
         if (item) {
-            cnt.c_pop += (u64)(clock64() - tp);
+            cnt.c_pop += (u64)(BFS_NOW() - tp);
             bfs_process_tile<true, MULTI>(A, item, lane, cnt);
         } else {
             if (BFS_SYNC_MASK & 1) BFS_PHASE_SYNC(); // the phase boundaries of bfs_process_tile

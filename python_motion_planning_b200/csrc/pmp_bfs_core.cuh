@@ -76,6 +76,10 @@
 #ifndef BFS_PROF
 #define BFS_PROF 0 // experiment builds: 1 / 2 = the phase counters [6], [11], [3], [0] hold four sub-phases of publish / setup instead
 #endif
+#ifndef BFS_CLOCKS
+#define BFS_CLOCKS (BFS_PROF != 0) // 1: phase times per activation in stats [4], [6], [11], [3], [0] (experiment builds: ten registers and ~50 instructions per activation)
+#endif
+#define BFS_NOW() (BFS_CLOCKS ? clock64() : 0ll)
 #define BFS_MARK(which, field) do { if (BFS_PROF == (which)) { const long long now_ = clock64(); cnt.field += (u64)(now_ - tmark); tmark = now_; } } while (0)
 #ifndef BFS_SLEEP_CAP
 #define BFS_SLEEP_CAP 128 // longest back-off (ns) of a warp polling an empty ring slot (1024 -> 128: -3..6 % at 1536^3)
@@ -670,7 +674,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     u32 *cell0 = A.g + (size_t)z0 * sZ + (size_t)y0 * sY + (size_t)(x0 + lane);
     const bool peer_lo = MULTI && bz == 0 && A.lo.g != nullptr, peer_hi = MULTI && bz == A.nbz - 1 && A.hi.g != nullptr;
 
-    const long long tc0 = clock64();
+    const long long tc0 = BFS_NOW();
     long long tmark = tc0;
     if (Gd.ready && !cnt.all_up) cnt.all_up = bfs_wait_planes(A, z0 - 1, z0 + 8, lane) ? 1u : 0u; // occupancy still uploading (e2e overlap)
     // ---- occupancy words (read-only during a search): issued before the claim so that their
@@ -894,7 +898,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
 
     }
     BFS_MARK(2, c_publish); // base + seed planes
-    if (!BFS_PROF) cnt.c_setup += (u64)(clock64() - tc0);
+    if (!BFS_PROF) cnt.c_setup += (u64)(BFS_NOW() - tc0);
 
     // ---- sweep, extract, store; continuation passes if a wave outlives the recordable range ----
     // (BFS_PHASE_SYNC: in the phase-locked kernel all warps of the CTA enter each phase together, so
@@ -906,16 +910,16 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     u32 rec[BFS_NREC][2];
     u32 carry0 = 0, carry1 = 0;
     if (SYNC && (BFS_SYNC_MASK & 1)) { BFS_PHASE_SYNC(); }
-    const long long tc1 = clock64();
+    const long long tc1 = BFS_NOW();
     long long tsw = 0;
     for (int pass = 0;; ++pass) {
         const u32 P0 = R0, P1 = R1;
-        const long long ta = clock64();
+        const long long ta = BFS_NOW();
         if (active) {
             cnt.levels += bfs_sweep(free0, free1, SA, init0, init1, R0, R1, rec, carry0, carry1, lane);
             ++cnt.passes;
         }
-        tsw += clock64() - ta;
+        tsw += BFS_NOW() - ta;
         if (SYNC && (BFS_SYNC_MASK & 2) && pass == 0) { BFS_PHASE_SYNC(); }
         if (!active) break;
         bfs_extract(rec, R0 & ~P0, R1 & ~P1, pbase, cell0, inx, sY, sZ, touched, low0, low1);
@@ -927,11 +931,11 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     }
     if (active) cnt.lowered += (u32)(__popc(low0) + __popc(low1));
     else ++cnt.idle;
-    if (!BFS_PROF) { cnt.c_sweep += (u64)tsw; cnt.c_extract += (u64)(clock64() - tc1 - tsw); }
+    if (!BFS_PROF) { cnt.c_sweep += (u64)tsw; cnt.c_extract += (u64)(BFS_NOW() - tc1 - tsw); }
     if (SYNC && (BFS_SYNC_MASK & 4)) { BFS_PHASE_SYNC(); }
 
     // ---- publish: every store above is visible before a neighbour is armed ----
-    const long long tc3 = clock64();
+    const long long tc3 = BFS_NOW();
     tmark = tc3;
     if (peer_lo || peer_hi) __threadfence_system(); else bfs_fence();
     __syncwarp();
@@ -1070,7 +1074,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
     }
     __syncwarp();
     BFS_MARK(1, c_publish); // pushes
-    if (!BFS_PROF) cnt.c_publish += (u64)(clock64() - tc3);
+    if (!BFS_PROF) cnt.c_publish += (u64)(BFS_NOW() - tc3);
     // [16]: when this rank finished its last activation (its busy span = [16] - [9]; the kernel itself runs
     // until the LAST rank is done)
     if (MULTI && lane == 0 && A.stats) atomicMax((unsigned long long *)&A.stats[16], (unsigned long long)bfs_now_ns());
@@ -1123,11 +1127,11 @@ __device__ static inline void bfs_warp_main(const BfsArgs &A, const int lane, co
     BfsPop P;
     P.ticket = 0; P.have = 0; P.t0 = 0; P.held = 0; P.held_polls = 0;
     for (;;) {
-        const long long tp = clock64();
+        const long long tp = BFS_NOW();
         bool done = false;
         const u64 item = bfs_pop_warp<MULTI>(A, P, lane, 0xFFFFFFFFu, done);
         if (item == 0ull) break;
-        cnt.c_pop += (u64)(clock64() - tp);
+        cnt.c_pop += (u64)(BFS_NOW() - tp);
         bfs_process_tile<false, MULTI>(A, item, lane, cnt);
     }
     bfs_count_flush(A, cnt, lane);

@@ -73,7 +73,7 @@ def main():
         ks = sorted(kms[1:] or kms)
         print(f"c5 {n}^3: {dt*1e3:.2f} ms wall, kernel {s[8]/1e6:.2f} ms (median {ks[len(ks)//2]:.2f} min {ks[0]:.2f} of {len(ks)}), certificate violations {bad}, reached {reached}, pending {pend}, "
               f"activations {s[1]} (idle {s[13]}) lowered {s[2]} levels {s[12]} passes {s[14]} requeues {s[5]} err {s[15]} "
-              f"status {ws.status.cpu().tolist()} us/activation/warp {ph}", flush=True)
+              f"status {ws.status.cpu().tolist()} us/activation/warp {ph if any(ph.values()) else '(build with -DBFS_CLOCKS=1)'}", flush=True)
         ok &= bad == 0 and pend == 0 and s[15] == 0
     print("ALL OK" if ok else "FAILED")
     return 0 if ok else 1
