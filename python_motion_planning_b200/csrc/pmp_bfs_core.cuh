@@ -250,34 +250,32 @@ __device__ __noinline__ static void bfs_fail(const BfsArgs &A, u32 code) {
     for (int r = 0; r < A.world; ++r) bfs_store_volatile(&A.peer_ctr[r][BFS_C_DONE], 1u);
 }
 
-// Streamed occupancy upload (GridDev.ready): wait until the planes [zlo, zhi] of the bitmask have arrived.
-// Lanes 0 and 1 poll the flags of the first and the last chunk involved (chunks arrive in z order, and a
-// tile's rows span at most two) with acquire loads -- no fence, this sits on every activation's critical
-// path; lane 2 looks at the very last chunk: once that is there the caller stops asking (returns true).
-// Bounded by the kernel's time-out.
-__device__ __noinline__ static bool bfs_wait_planes(const BfsArgs &A, int zlo, int zhi, const int lane) {
+// Streamed occupancy upload (GridDev.ready): have the planes [zlo, zhi] of the bitmask arrived?  Lanes 0 and 1 look
+// at the flags of the first and the last chunk involved (chunks arrive in z order, and a tile's rows span at most
+// two) with acquire loads -- no fence, this sits on every activation's path; lane 2 looks at the very last chunk.
+// Returns 0: not yet (the caller puts the tile back into the ring: the tip of the wave runs along the z axis far
+// ahead of the upload, and a warp that waited here would hold up its whole CTA at the next phase barrier), 1: there,
+// 2: there and the upload is complete (the caller stops asking).
+__device__ __noinline__ static u32 bfs_planes_there(const BfsArgs &A, int zlo, int zhi, const int lane) {
     const GridDev &Gd = A.G;
-    u32 last = 0;
+    u32 v = 1u;
     if (lane < 3) {
         zlo = zlo < 0 ? 0 : zlo;
         zhi = zhi > Gd.PZ - 1 ? Gd.PZ - 1 : zhi;
-        const u32 *f = Gd.ready + ((lane == 0 ? zlo : (lane == 1 ? zhi : Gd.PZ - 1)) >> Gd.ready_shift);
-        if (lane == 2) last = bfs_ld_acquire_sys(f);
-        else {
-            unsigned polls = 0;
-            u64 t0 = 0;
-            while (bfs_ld_acquire_sys(f) == 0u) {
-                __nanosleep(200);
-                if (A.timeout_ns && (++polls & 1023u) == 0u) {
-                    const u64 now = bfs_now_ns();
-                    if (!t0) t0 = now;
-                    else if (now - t0 > A.timeout_ns) { bfs_fail(A, BFS_ERR_TIMEOUT); break; }
-                }
-                if (__ldcg(&A.ctr[BFS_C_DONE])) break;
-            }
-        }
+        v = bfs_ld_acquire_sys(Gd.ready + ((lane == 0 ? zlo : (lane == 1 ? zhi : Gd.PZ - 1)) >> Gd.ready_shift));
     }
-    return __shfl_sync(BFS_FULL, last, 2) != 0u;
+    const u32 m = __ballot_sync(BFS_FULL, v != 0u);
+    return (m & 3u) != 3u ? 0u : ((m & 4u) ? 2u : 1u);
+}
+// the tile's occupancy has not arrived: back into the ring with it (state untouched: it is still queued and counted
+// in flight), after a short pause -- early in an upload the ring holds little else.  Bounded by the kernel's time-out.
+__device__ __noinline__ static void bfs_put_back(const BfsArgs &A, const u64 entry, const int lane) {
+    if (lane == 0) {
+        __nanosleep(400);
+        if (A.timeout_ns && A.stats && bfs_now_ns() - __ldcg(&A.stats[9]) > A.timeout_ns) bfs_fail(A, BFS_ERR_TIMEOUT);
+        bfs_push(A.ring, A.ring_cap, A.ctr, (u32)entry - 1u, (u32)(entry >> 32));
+    }
+    __syncwarp();
 }
 
 // A warp's position in the ring: the ticket stays valid across calls of bfs_pop_warp until it is
@@ -676,7 +674,17 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
 
     const long long tc0 = BFS_NOW();
     long long tmark = tc0;
-    if (Gd.ready && !cnt.all_up) cnt.all_up = bfs_wait_planes(A, z0 - 1, z0 + 8, lane) ? 1u : 0u; // occupancy still uploading (e2e overlap)
+    if (Gd.ready && !cnt.all_up) { // occupancy still uploading (e2e overlap)
+        const u32 there = bfs_planes_there(A, z0 - 1, z0 + 8, lane);
+        if (there == 0u) {
+            bfs_put_back(A, entry, lane);
+            if (SYNC && (BFS_SYNC_MASK & 1)) { BFS_PHASE_SYNC(); } // the phase boundaries the CTA's other warps take
+            if (SYNC && (BFS_SYNC_MASK & 2)) { BFS_PHASE_SYNC(); }
+            if (SYNC && (BFS_SYNC_MASK & 4)) { BFS_PHASE_SYNC(); }
+            return;
+        }
+        cnt.all_up = there == 2u ? 1u : 0u;
+    }
     // ---- occupancy words (read-only during a search): issued before the claim so that their
     // latency overlaps the claim's round trip ----
     const int ly = lane & 7, lzq = lane >> 3; // the (y, z & 3) this lane handles in row-distributed steps
