@@ -70,9 +70,6 @@
 #ifndef BFS_CLAIM_FENCE
 #define BFS_CLAIM_FENCE 1 // experiment: 0 = no fence between the claim and the halo loads (single GPU)
 #endif
-#ifndef BFS_PAIR_FACES
-#define BFS_PAIR_FACES 1 // the halo rows of the three "minus" faces (then of the three "plus" faces) are requested together
-#endif
 #ifndef BFS_PROF
 #define BFS_PROF 0 // experiment builds: 1 / 2 = the phase counters [6], [11], [3], [0] hold four sub-phases of publish / setup instead
 #endif
@@ -534,8 +531,6 @@ __device__ __forceinline__ void bfs_extract(const u32 (&rec)[BFS_NREC][2], const
     // (a lane whose column lies outside the box has no free cell: N = 0, nothing lowered)
 }
 
-// candidate value read across a face: halo + 1, or BFS_CINV if the halo cell is unreached
-__device__ __forceinline__ u32 bfs_cand(u32 raw) { return raw == BFS_RAWINF ? BFS_CINV : (raw >> 1) + 1u; }
 
 // level of a candidate relative to the pass base as a byte (0x80: no seed in this pass); seeds
 // beyond the six seed planes are left for a later activation (`far`)
@@ -548,33 +543,11 @@ __device__ __forceinline__ u32 bfs_rel(const u32 c, const u32 base, u32 &far, u3
     return r;
 }
 
-// Candidates read across one y / z face (F: 0 = y-, 1 = y+, 2 = z-, 3 = z+): for each of the eight boundary cells of
-// this lane's column the halo value + 1 if the cell is free and that beats its own value, else BFS_CINV.
-// hrow / orow: the first of the eight halo / own rows, `step` apart; fw_lo / fw_hi: the free-cell words holding the
-// boundary cells 0..3 / 4..7.  (An unreached halo word gives 0x80000000, above every own value: no explicit test.)
-template <int F>
-__device__ __forceinline__ void bfs_face_cand(u32 (&c)[8], const bool dirty, const u32 *hrow, const u32 *orow, const size_t step,
-                                              const bool peer, const bool inx, const bool touched, const u32 fw_lo, const u32 fw_hi) {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) c[i] = BFS_CINV;
-    if (!dirty) return;
-    u32 h[8], o[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        h[i] = inx ? (peer ? bfs_ld_peer(hrow + (size_t)i * step) : __ldcg(hrow + (size_t)i * step)) : BFS_RAWINF;
-        o[i] = (touched && inx) ? __ldcg(orow + (size_t)i * step) : BFS_RAWINF;
-    }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const u32 cv = (h[i] >> 1) + 1u;
-        const u32 sh = F < 2 ? (u32)((i & 3) * 8) + (F ? 7u : 0u) : (u32)i + (F == 3 ? 24u : 0u);
-        const u32 fr = ((i < 4 ? fw_lo : fw_hi) >> sh) & 1u;
-        if (fr && cv < (o[i] >> 1)) c[i] = cv;
-    }
-}
-
-// Two faces at once (a y face FA and a z face FB on the same side): the halo / own rows of both are requested before
-// either is used.
+// Candidates read across a y face FA and a z face FB on the same side (0 = y-, 1 = y+, 2 = z-, 3 = z+): for each of the
+// eight boundary cells of this lane's column the halo value + 1 if the cell is free and that beats its own value, else
+// BFS_CINV.  hrow / orow: the first of the eight halo / own rows, `step` apart; f*_lo / f*_hi: the free-cell words holding
+// the boundary cells 0..3 / 4..7.  The rows of both faces are requested before either is used.  (An unreached halo word
+// gives 0x80000000, above every own value: no explicit test.)
 template <int FA, int FB>
 __device__ __forceinline__ void bfs_face_cand2(u32 (&ca)[8], u32 (&cb)[8], const bool da, const bool db,
                                                const u32 *hrowA, const u32 *orowA, const size_t stepA,
@@ -747,7 +720,6 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         // halo rows: the neighbour's boundary rows (on the lowest / highest tile row of a slab the peer GPU's)
         const u32 *zlo = peer_lo ? A.lo.g + (size_t)A.lo.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 - sZ;
         const u32 *zhi = peer_hi ? A.hi.g + (size_t)A.hi.zadj * sZ + (size_t)y0 * sY + (size_t)(x0 + lane) : cell0 + 8 * sZ;
-#if BFS_PAIR_FACES
         // A wave usually enters through the faces of one corner (x-, y-, z- far from the source's corner, ...):
         // the halo words of the three "minus" faces are requested before the first is used, then those of the
         // three "plus" faces -- one L2 round trip per group instead of one per dirty face.
@@ -776,36 +748,8 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
                 if ((((w ? fp1 : fp0) >> lane) & 1u) && cp < (xo[1][w] >> 1)) cXp[w] = cp;
             }
         }
-#else
-        bfs_face_cand<0>(cYm, (dirty & 4u) != 0u, cell0 - sY, cell0, sZ, false, inx, touched, free0, free1);
-        bfs_face_cand<1>(cYp, (dirty & 8u) != 0u, cell0 + 8 * sY, cell0 + 7 * sY, sZ, false, inx, touched, free0, free1);
-        bfs_face_cand<2>(cZm, (dirty & 16u) != 0u, zlo, cell0, sY, peer_lo, inx, touched, free0, free0);
-        bfs_face_cand<3>(cZp, (dirty & 32u) != 0u, zhi, cell0 + 7 * sZ, sY, peer_hi, inx, touched, free1, free1);
-#endif
         if (MULTI) cnt.peer_rows += (((dirty & 16u) && peer_lo) ? 8u : 0u) + (((dirty & 32u) && peer_hi) ? 8u : 0u);
     }
-#if !BFS_PAIR_FACES
-    if (dirty & 1u) { // x-: halo column x0 - 1, own column x0 (lane 0's cells)
-        const u32 fw0 = __shfl_sync(BFS_FULL, free0, 0), fw1 = __shfl_sync(BFS_FULL, free1, 0);
-#pragma unroll
-        for (int w = 0; w < 2; ++w) {
-            const u32 c = bfs_cand(__ldcg(colrow + (size_t)(4 * w) * sZ - 1));
-            const u32 o = touched ? __ldcg(colrow + (size_t)(4 * w) * sZ) : BFS_RAWINF;
-            const u32 fr = ((w ? fw1 : fw0) >> lane) & 1u;
-            cXm[w] = (fr && c != BFS_CINV && c < (o >> 1)) ? c : BFS_CINV;
-        }
-    }
-    if (dirty & 2u) { // x+: halo column x0 + 32, own column x0 + 31 (lane 31's cells)
-        const u32 fw0 = __shfl_sync(BFS_FULL, free0, 31), fw1 = __shfl_sync(BFS_FULL, free1, 31);
-#pragma unroll
-        for (int w = 0; w < 2; ++w) {
-            const u32 c = bfs_cand(__ldcg(colrow + (size_t)(4 * w) * sZ + 32));
-            const u32 o = touched ? __ldcg(colrow + (size_t)(4 * w) * sZ + 31) : BFS_RAWINF;
-            const u32 fr = ((w ? fw1 : fw0) >> lane) & 1u;
-            cXp[w] = (fr && c != BFS_CINV && c < (o >> 1)) ? c : BFS_CINV;
-        }
-    }
-#endif
     // corner cells of the y / z faces have two candidates: keep the smaller one in the y array
     {
         u32 m;
