@@ -145,7 +145,12 @@ int pmp_sssp_sizes(const pmp_grid *g, int64_t nq, int weight, int64_t *g_bytes_p
  *   stats_dev  : optional 16 x uint64: [0] rounds, [1] tile activations, [2] cells expanded,
  *                [3] edges relaxed, [4] worklist high-water, [5..7] SM cycles summed over tile
  *                activations in load / settle / publish, [8] kernel ns, [9..11] ns CTA 0 spent in
- *                scan / process / waiting at the round barrier, [12] in-tile sub-iterations
+ *                scan / process / waiting at the round barrier, [12] in-tile sub-iterations.
+ *                (A full unit-weight u32 field on a 3D grid with the six unit moves is computed by k_bfs,
+ *                csrc/pmp_bfs.cu: [1] tile activations, [2] cells lowered, [5] tiles re-queued, [7] entries
+ *                pushed into a neighbour GPU's ring, [8] kernel ns, [12] levels swept, [13] activations that
+ *                found nothing new, [14] sweep passes, [15] error bits; [4] [6] [11] [3] [0] = cycles per phase,
+ *                filled only by builds with -DBFS_CLOCKS=1.)
  * Fields are bit-exact to a sequential Dijkstra on the same directed graph: every value is the
  * minimum over in-edges of fl(g(u) + w). */
 int pmp_sssp(pmp_grid *g, const pmp_sssp_params *params, int64_t nq,
