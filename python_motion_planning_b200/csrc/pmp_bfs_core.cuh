@@ -78,6 +78,9 @@
 #endif
 #define BFS_NOW() (BFS_CLOCKS ? clock64() : 0ll)
 #define BFS_MARK(which, field) do { if (BFS_PROF == (which)) { const long long now_ = clock64(); cnt.field += (u64)(now_ - tmark); tmark = now_; } } while (0)
+#ifndef BFS_PUTBACK_NS
+#define BFS_PUTBACK_NS 400 // pause before a tile whose occupancy has not arrived goes back into the ring
+#endif
 #ifndef BFS_SLEEP_CAP
 #define BFS_SLEEP_CAP 128 // longest back-off (ns) of a warp polling an empty ring slot (1024 -> 128: -3..6 % at 1536^3)
 #endif
@@ -268,7 +271,7 @@ __device__ __noinline__ static u32 bfs_planes_there(const BfsArgs &A, int zlo, i
 // in flight), after a short pause -- early in an upload the ring holds little else.  Bounded by the kernel's time-out.
 __device__ __noinline__ static void bfs_put_back(const BfsArgs &A, const u64 entry, const int lane) {
     if (lane == 0) {
-        __nanosleep(400);
+        __nanosleep(BFS_PUTBACK_NS);
         if (A.timeout_ns && A.stats && bfs_now_ns() - __ldcg(&A.stats[9]) > A.timeout_ns) bfs_fail(A, BFS_ERR_TIMEOUT);
         bfs_push(A.ring, A.ring_cap, A.ctr, (u32)entry - 1u, (u32)(entry >> 32));
     }
