@@ -80,3 +80,22 @@ def test_interleavings(exe):
     """the same case under different warp interleavings (the seed drives the scheduler too)"""
     for seed in range(20, 28):
         run(exe, 64, 24, 24, seed, 25, 2, 3, 0)
+
+
+def test_edge_candidates_from_two_faces(exe):
+    """dense random obstacles on boxes one tile wide in y / z and several tiles long in x: most candidate cells of the
+    lane-0 / lane-31 columns sit on an edge and get a level from an x face AND from a y / z face -- the bit-sliced
+    min that merges the two seed sets (bfs_process_tile) decides every one of them"""
+    for seed, dens in ((41, 30), (42, 40), (43, 20), (44, 35)):
+        st = run(exe, 128, 8, 8, seed, dens, 1, 3, 0)
+        assert int(st["bad"]) == 0
+        st = run(exe, 96, 16, 8, seed, dens, 1, 4, 0)
+        assert int(st["bad"]) == 0
+
+
+def test_streamed_put_back_keeps_the_count(exe):
+    """a slow upload (small chunks) with several warps: tiles whose planes are missing go back into the ring many times;
+    the in-flight count must survive that (the search ends, nothing is left pending)"""
+    for seed in (51, 52):
+        st = run(exe, 64, 16, 96, seed, 15, 1, 4, 0, 2)
+        assert int(st["bad"]) == 0
