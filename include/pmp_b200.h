@@ -92,8 +92,8 @@ int pmp_grid_set_packed(pmp_grid *g, const uint32_t *rows_dev, void *stream);
  * on copy_stream (the copy engine) straight into the grid's bitmask, each chunk followed by a ready flag,
  * and the call returns at once.  A unit-weight field search (pmp_sssp full_field / PMP_W_U32 on the six
  * unit moves) launched on search_stream right after it starts while the upload is still running: its
- * kernel waits per tile for the chunks it needs.  Every other entry point first waits for the whole
- * upload.  Needs the rows to be the grid's own layout: 3D, X % 32 == 0, Y % 8 == 0, Z % 8 == 0 (else -1:
+ * kernel holds a tile back (re-queues it) until the chunks it needs are there.  Every other entry point
+ * first waits for the whole upload.  Needs the rows to be the grid's own layout: 3D, X % 32 == 0, Y % 8 == 0, Z % 8 == 0 (else -1:
  * upload to the device yourself and call pmp_grid_set_packed).  The host buffer must stay untouched
  * until the next operation on search_stream after the search has completed. */
 int pmp_grid_set_packed_host_streamed(pmp_grid *g, const uint32_t *rows_host_pinned, int planes_per_chunk,

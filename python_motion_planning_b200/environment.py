@@ -221,8 +221,8 @@ class DeviceGrid:
             if (not rows.is_cuda and rows.is_pinned() and rows.is_contiguous() and self.ndim == 3 and X % 32 == 0
                     and self.padded[1] == Y and self.padded[2] == Z and not os.environ.get("PMP_B200_NO_STREAMED_UPLOAD")):
                 # pinned host rows in the grid's own layout: streamed upload -- the copy engine fills the bitmask chunk
-                # by chunk while a unit-weight field search launched next already runs behind it (k_bfs waits per tile
-                # for the chunks it needs); every other entry point waits for the whole upload first
+                # by chunk while a unit-weight field search launched next already runs behind it (k_bfs re-queues a
+                # tile until the chunks it needs are there); every other entry point waits for the whole upload first
                 if getattr(self, "_copy_stream", None) is None:
                     self._copy_stream = t.cuda.Stream(device=self.device)
                 _lib.check(self.L.pmp_grid_set_packed_host_streamed(self.handle, rows.data_ptr(), 32, self.stream(),
