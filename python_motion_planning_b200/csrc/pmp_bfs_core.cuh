@@ -53,6 +53,7 @@
 #define BFS_C_INFLIGHT 64
 #define BFS_C_DONE 96
 #define BFS_C_ERR 97
+#define BFS_C_PUTBACK 98 // streamed upload: tiles put back into the ring because their occupancy had not arrived (not activations)
 #define BFS_C_ACTIVE 128 // ranks with work in flight (only rank 0's word is used)
 #define BFS_C_SRC 160    // local source cell x, y, z and a valid flag
 // multi-GPU pacing (bfs_seq_*): entries pushed / started on this rank, and the other ranks' counts as they
@@ -273,6 +274,7 @@ __device__ __noinline__ static void bfs_put_back(const BfsArgs &A, const u64 ent
     if (lane == 0) {
         __nanosleep(BFS_PUTBACK_NS);
         if (A.timeout_ns && A.stats && bfs_now_ns() - __ldcg(&A.stats[9]) > A.timeout_ns) bfs_fail(A, BFS_ERR_TIMEOUT);
+        atomicAdd(&A.ctr[BFS_C_PUTBACK], 1u);
         bfs_push(A.ring, A.ring_cap, A.ctr, (u32)entry - 1u, (u32)(entry >> 32));
     }
     __syncwarp();
@@ -311,7 +313,8 @@ __device__ static inline u64 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int
                 if (lane == 0) t = atomicAdd(&A.ctr[BFS_C_HEAD], 1u);
                 P.ticket = __shfl_sync(BFS_FULL, t, 0);
                 P.have = 1u;
-                if (A.max_pops && P.ticket > A.max_pops) {
+                if (A.max_pops && P.ticket > A.max_pops &&
+                    P.ticket - (A.G.ready ? __ldcg(&A.ctr[BFS_C_PUTBACK]) : 0u) > A.max_pops) { // (put-backs are not activations)
                     if (lane == 0) bfs_fail(A, BFS_ERR_BUDGET);
                     done = true;
                     return 0ull;

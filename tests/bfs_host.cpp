@@ -158,6 +158,7 @@ int main(int argc, char **argv) {
         A.stats = K.stats.data();
         A.rank = r; A.world = nr;
         A.timeout_ns = 0;
+        A.max_pops = 64u * A.ntiles; // the product's activation budget (tiles put back during a streamed upload do not count)
         A.pace_window = nr > 1 ? 8 : 0; // tight: entries are held often
         A.pace_hold_polls = 40;
     }
