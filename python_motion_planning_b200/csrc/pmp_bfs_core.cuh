@@ -313,11 +313,15 @@ __device__ static inline u64 bfs_pop_warp(const BfsArgs &A, BfsPop &P, const int
                 if (lane == 0) t = atomicAdd(&A.ctr[BFS_C_HEAD], 1u);
                 P.ticket = __shfl_sync(BFS_FULL, t, 0);
                 P.have = 1u;
-                if (A.max_pops && P.ticket > A.max_pops &&
-                    P.ticket - (A.G.ready ? __ldcg(&A.ctr[BFS_C_PUTBACK]) : 0u) > A.max_pops) { // (put-backs are not activations)
-                    if (lane == 0) bfs_fail(A, BFS_ERR_BUDGET);
-                    done = true;
-                    return 0ull;
+                if (A.max_pops && P.ticket > A.max_pops) {
+                    // tiles put back during a streamed upload are not activations (the count may have passed this
+                    // ticket meanwhile: a "negative" difference is within budget)
+                    const u32 used = P.ticket - (A.G.ready ? __ldcg(&A.ctr[BFS_C_PUTBACK]) : 0u);
+                    if ((int)used > 0 && used > A.max_pops) {
+                        if (lane == 0) bfs_fail(A, BFS_ERR_BUDGET);
+                        done = true;
+                        return 0ull;
+                    }
                 }
             }
             const u32 idx = P.ticket - 31u + (u32)lane; // lane 31: my own slot

@@ -207,7 +207,11 @@ int main(int argc, char **argv) {
     u64 act = 0, idle = 0, lowered = 0, levels = 0, passes = 0, redo = 0, remote = 0, tiles = 0, touched_tiles = 0;
     for (int r = 0; r < nr; ++r) {
         Rank &K = R[r];
-        if (K.ctr[BFS_C_ERR]) { printf("FAIL rank %d error flag %u\n", r, K.ctr[BFS_C_ERR]); return 1; }
+        if (K.ctr[BFS_C_ERR]) {
+            printf("FAIL rank %d error flag %u (tickets drawn %u, entries pushed %u, put back %u, activations %llu, budget %u)\n", r, K.ctr[BFS_C_ERR],
+                   K.ctr[BFS_C_HEAD], K.ctr[BFS_C_TAIL], K.ctr[BFS_C_PUTBACK], (unsigned long long)K.stats[1], K.A.max_pops);
+            return 1;
+        }
         if (K.ctr[BFS_C_INFLIGHT]) { printf("FAIL rank %d inflight %u at exit\n", r, K.ctr[BFS_C_INFLIGHT]); return 1; }
         for (u32 t = 0; t < K.A.ntiles; ++t) {
             ++tiles;

@@ -99,3 +99,12 @@ def test_streamed_put_back_keeps_the_count(exe):
     for seed in (51, 52):
         st = run(exe, 64, 16, 96, seed, 15, 1, 4, 0, 2)
         assert int(st["bad"]) == 0
+
+
+@pytest.mark.parametrize("cfg", [(40, 9, 8, 140, 5, 1, 4, 3, 4), (40, 8, 24, 143, 5, 1, 3, 2, 4)])
+def test_put_backs_are_not_activations(exe, cfg):
+    """tiny grids behind a slow upload: hundreds of put-backs for a handful of tiles.  The activation budget (64 x
+    tiles) must not count them -- and the put-back count can pass a ticket that was drawn earlier (found by fuzzing:
+    an unsigned difference wrapped and tripped PMP_ST_ERROR)"""
+    st = run(exe, *cfg)
+    assert int(st["bad"]) == 0
