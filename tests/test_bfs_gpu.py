@@ -57,6 +57,29 @@ def test_field_bit_exact_vs_oracle(shape, dens, seed):
         del os.environ["PMP_B200_OLD_BFS"]
 
 
+def test_field_with_shell_walls_and_update():
+    """Grid3D's own shell walls (env3d.py:72-103, with the reference's z - 1 quirk) as initialised, then two maps set through
+    env.update() on the same grid: a later field must not see anything of an earlier map (lazy tile initialisation,
+    workspace reuse)"""
+    rng = np.random.default_rng(77)
+    env = pmp.Grid3D(50, 30, 20)               # walls=True
+    env.motions = [m for m in env.motions if m.g == 1]
+    occ = np.asarray(env.occupancy()).astype(bool)
+    assert occ[0].all() and occ[:, :, 0].all() and not occ[5, 5, 5]
+    f = pmp.cost_field(env, (5, 5, 5), weight="u32")
+    assert np.array_equal(f, oracle_field(occ, (5, 5, 5)))
+    for k in range(2):
+        occ = rng.random((50, 30, 20)) < (0.15 + 0.1 * k)
+        occ[0, :, :] = occ[-1, :, :] = True
+        occ[:, 0, :] = occ[:, -1, :] = True
+        occ[:, :, 0] = occ[:, :, -1] = True
+        env.update(occ)
+        free = np.argwhere(~occ)
+        src = tuple(int(v) for v in free[rng.integers(0, len(free))])
+        f = pmp.cost_field(env, src, weight="u32")
+        assert np.array_equal(f, oracle_field(occ, src)), k
+
+
 def test_c5_block_128_bit_exact():
     """BASELINE.json config 5's parity statement: the full field bit-exact on the 128^3 copy"""
     blk, _ = workloads.replicated_boxes3d(base=128, reps=1)
