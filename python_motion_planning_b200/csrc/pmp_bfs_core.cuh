@@ -459,7 +459,7 @@ __device__ __forceinline__ void bfs_sweep_block(const int rb, const u32 free0, c
 
 __device__ __forceinline__ u32 bfs_sweep(const u32 free0, const u32 free1, const BfsSeeds &SA,
                                          const u32 init0, const u32 init1, u32 &R0, u32 &R1, u32 (&rec)[BFS_NREC][2],
-                                         u32 &carry0, u32 &carry1, const int lane) {
+                                         u32 &carry0, u32 &carry1) {
 #pragma unroll
     for (int b = 0; b < BFS_NREC; ++b) rec[b][0] = rec[b][1] = 0u;
     u32 c0 = init0, c1 = init1;
@@ -878,7 +878,7 @@ __device__ __forceinline__ void bfs_process_tile(const BfsArgs &A, const u64 ent
         const u32 P0 = R0, P1 = R1;
         const long long ta = BFS_NOW();
         if (active) {
-            cnt.levels += bfs_sweep(free0, free1, SA, init0, init1, R0, R1, rec, carry0, carry1, lane);
+            cnt.levels += bfs_sweep(free0, free1, SA, init0, init1, R0, R1, rec, carry0, carry1);
             ++cnt.passes;
         }
         tsw += BFS_NOW() - ta;
