@@ -225,7 +225,7 @@ class DeviceGrid:
                 # tile until the chunks it needs are there); every other entry point waits for the whole upload first
                 if getattr(self, "_copy_stream", None) is None:
                     self._copy_stream = t.cuda.Stream(device=self.device)
-                _lib.check(self.L.pmp_grid_set_packed_host_streamed(self.handle, rows.data_ptr(), 32, self.stream(),
+                _lib.check(self.L.pmp_grid_set_packed_host_streamed(self.handle, rows.data_ptr(), int(os.environ.get("PMP_B200_STREAM_PLANES", "32")), self.stream(),
                                                                     self._copy_stream.cuda_stream),
                            "pmp_grid_set_packed_host_streamed")
                 self.h2d_bytes = rows.numel() * 4
